@@ -1,0 +1,648 @@
+// K5 / K6 — attention over the paged KV cache.
+//
+// KV cache layer layout: [page][kv_head][K|V][64 tokens][D] bf16, one page = 64 tokens.  The
+// K and V slabs of a (page, head) are adjacent, so one attention tile is ONE contiguous
+// 2*64*D*2-byte block that a single bulk-TMA copy (cp.async.bulk, SASS UBLKCP) drops into a
+// shared-memory stage.  The 16-byte chunks of every token row are XOR-swizzled already in HBM
+// (rope_kv_append writes them that way), so ldmatrix reads the landed tile conflict-free
+// without a tensor map.
+//
+// K5 decode: persistent CTAs, stream-K over the flattened (sequence, kv head, tile) list so
+// every CTA streams the same number of 64-token tiles no matter how ragged the batch is.
+// A (sequence, head) whose tiles span several CTAs is finished by attn_decode_merge.
+// The math is mma.sync m16n8k16 with the GQA group (<= 8 q heads) in the M rows: decode
+// attention is HBM-bound (SURVEY.md §8a' a'5), tensor throughput is irrelevant here and
+// tcgen05's minimum M of 64 would be 94 % padding.
+#include "common.cuh"
+#include "ft_internal.h"
+
+namespace ft {
+
+constexpr int ATTN_COMPUTE_WARPS = 4;
+constexpr int ATTN_THREADS = (ATTN_COMPUTE_WARPS + 1) * 32;
+constexpr int ATTN_GMAX = 8;                       // q heads per kv head supported (rows 0..7)
+constexpr float LOG2E = 1.4426950408889634f;
+
+template <int D>
+struct AttnCfg {
+    static constexpr int SLAB_BYTES = kKvTile * D * 2;       // K (or V) of one page+head
+    static constexpr int TILE_BYTES = 2 * SLAB_BYTES;
+    static constexpr int STAGES = D == 64 ? 6 : 3;           // 96 KB in flight per CTA
+    static constexpr int REC = D + 2;                        // O[D], m, l  (floats per head row)
+    static constexpr size_t SMEM = (size_t)STAGES * TILE_BYTES + 2 * STAGES * 8 +
+                                   (size_t)ATTN_COMPUTE_WARPS * ATTN_GMAX * REC * 4 + 128;
+};
+
+__device__ __forceinline__ void compute_bar_sync() {
+    asm volatile("bar.sync 1, %0;" ::"n"(ATTN_COMPUTE_WARPS * 32) : "memory");
+}
+
+struct DecodeSeg {
+    int b, h, tile_begin, tile_end, tiles_b;
+};
+
+// Next (sequence, head) segment of the flat tile range [f, f_end).  tile_prefix[b] = number of
+// tiles of sequences < b; flat index = tile_prefix[b]*nkv + h*tiles_b + tile.
+__device__ __forceinline__ bool next_decode_seg(long long& f, long long f_end,
+                                                const int* __restrict__ tile_prefix, int B, int nkv,
+                                                int& b, DecodeSeg& s) {
+    if (f >= f_end) return false;
+    while (b < B && (long long)tile_prefix[b + 1] * nkv <= f) ++b;
+    const int base = tile_prefix[b];
+    const int tiles_b = tile_prefix[b + 1] - base;
+    const long long rem = f - (long long)base * nkv;
+    s.b = b;
+    s.h = (int)(rem / tiles_b);
+    s.tiles_b = tiles_b;
+    s.tile_begin = (int)(rem % tiles_b);
+    const long long seg_left = tiles_b - s.tile_begin;
+    const long long take = (f_end - f) < seg_left ? (f_end - f) : seg_left;
+    s.tile_end = s.tile_begin + (int)take;
+    f += take;
+    return true;
+}
+
+__device__ __forceinline__ int find_seq(const int* __restrict__ tile_prefix, int B, int nkv,
+                                        long long f) {
+    int lo = 0, hi = B - 1;      // largest b with tile_prefix[b]*nkv <= f
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if ((long long)tile_prefix[mid] * nkv <= f) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+__global__ void attn_decode_plan_kernel(const int* __restrict__ ctx_lens, int* __restrict__ tile_prefix,
+                                        int B) {
+    pdl_wait();
+    pdl_launch_dependents();
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        tile_prefix[0] = 0;
+        for (int b = 0; b < B; ++b) {
+            acc += (ctx_lens[b] + kKvTile - 1) / kKvTile;
+            tile_prefix[b + 1] = acc;
+        }
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(ATTN_THREADS)
+attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restrict__ kv_layer,
+                   const int* __restrict__ page_table, int max_pages, const int* __restrict__ ctx_lens,
+                   const int* __restrict__ tile_prefix, __nv_bfloat16* __restrict__ out,
+                   float* __restrict__ scratch, int B, int nq, int nkv, float scale_log2) {
+    using C = AttnCfg<D>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)C::STAGES * C::TILE_BYTES);
+    uint64_t* empty_bar = full_bar + C::STAGES;
+    float* merge_buf = reinterpret_cast<float*>(empty_bar + C::STAGES);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int G = nq / nkv;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < C::STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], ATTN_COMPUTE_WARPS);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+    pdl_wait();
+    pdl_launch_dependents();
+
+    const long long total = (long long)tile_prefix[B] * nkv;
+    const long long per = (total + gridDim.x - 1) / gridDim.x;
+    long long f = per * blockIdx.x;
+    long long f_end = f + per < total ? f + per : total;
+    if (f >= total) return;
+    int b_cur = find_seq(tile_prefix, B, nkv, f);
+    DecodeSeg seg;
+    int stage = 0;
+    uint32_t phase = 0;
+
+    if (warp == ATTN_COMPUTE_WARPS) {
+        // ---------------- producer warp: one bulk-TMA copy per tile
+        const uint64_t pol = policy_evict_first();       // every KV byte is read once per step
+        while (next_decode_seg(f, f_end, tile_prefix, B, nkv, b_cur, seg)) {
+            const int* pt = page_table + (size_t)seg.b * max_pages;
+            for (int t0 = seg.tile_begin; t0 < seg.tile_end; t0 += 32) {
+                const int mine = t0 + lane;
+                const int my_page = mine < seg.tile_end ? pt[mine] : 0;
+                const int n = seg.tile_end - t0 < 32 ? seg.tile_end - t0 : 32;
+                for (int i = 0; i < n; ++i) {
+                    const int page = __shfl_sync(0xffffffffu, my_page, i);
+                    if (lane == 0) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        mbar_expect_tx(&full_bar[stage], C::TILE_BYTES);
+                        tma_bulk_g2s(smem + (size_t)stage * C::TILE_BYTES,
+                                     kv_layer + ((size_t)page * nkv + seg.h) * C::TILE_BYTES,
+                                     C::TILE_BYTES, &full_bar[stage], pol);
+                    }
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        return;
+    }
+
+    // ---------------- compute warps: warp w owns token rows 16w..16w+15 of every tile
+    const int g = lane >> 2;        // mma row  = q head within the GQA group
+    const int tq = lane & 3;        // mma column pair
+    const int r0 = warp * 16;
+    const int cta_slot = blockIdx.x;
+
+    while (next_decode_seg(f, f_end, tile_prefix, B, nkv, b_cur, seg)) {
+        const int ctx = ctx_lens[seg.b];
+        // Q fragments (A operand, rows >= G are zero padding)
+        uint32_t qa[D / 16][2];
+        {
+            const __nv_bfloat16* qrow = q + ((size_t)seg.b * nq + (size_t)seg.h * G + g) * D;
+#pragma unroll
+            for (int ks = 0; ks < D / 16; ++ks) {
+                qa[ks][0] = g < G ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 2 * tq) : 0u;
+                qa[ks][1] = g < G ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8 + 2 * tq) : 0u;
+            }
+        }
+        float o[D / 8][4];
+#pragma unroll
+        for (int nt = 0; nt < D / 8; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
+        float m_run = -INFINITY, l_run = 0.f;
+
+        for (int tile = seg.tile_begin; tile < seg.tile_end; ++tile) {
+            mbar_wait(&full_bar[stage], phase);
+            const uint32_t kbase = smem_u32(smem + (size_t)stage * C::TILE_BYTES);
+            const uint32_t vbase = kbase + C::SLAB_BYTES;
+
+            // S[16 x 16 tokens] = Q K^T
+            float s[2][4];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+                const int row = r0 + 8 * j + (lane & 7);
+#pragma unroll
+                for (int kp = 0; kp < D / 32; ++kp) {
+                    uint32_t b0, b1, b2, b3;
+                    ldmatrix_x4(kbase + kv_swizzled_chunk<D>(row, kp * 4 + (lane >> 3)), b0, b1, b2, b3);
+                    mma_bf16_16816(s[j], qa[2 * kp][0], 0u, qa[2 * kp][1], 0u, b0, b1);
+                    mma_bf16_16816(s[j], qa[2 * kp + 1][0], 0u, qa[2 * kp + 1][1], 0u, b2, b3);
+                }
+            }
+            // mask + online softmax for row g (this lane: tokens 2tq, 2tq+1 of each 8-token group)
+            const int tok0 = tile * kKvTile + r0 + 2 * tq;
+            float p[2][2];
+            float tmax = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const float v = (tok0 + 8 * j + e < ctx) ? s[j][e] * scale_log2 : -INFINITY;
+                    p[j][e] = v;
+                    tmax = fmaxf(tmax, v);
+                }
+            tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, 1));
+            tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, 2));
+            const float m_new = fmaxf(m_run, tmax);
+            const float m_use = m_new == -INFINITY ? 0.f : m_new;
+            const float alpha = exp2f(m_run - m_use);
+            float psum = 0.f;
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    p[j][e] = exp2f(p[j][e] - m_use);
+                    psum += p[j][e];
+                }
+            l_run = l_run * alpha + psum;
+            m_run = m_new;
+            const uint32_t pa0 = pack_bf16(p[0][0], p[0][1]);
+            const uint32_t pa2 = pack_bf16(p[1][0], p[1][1]);
+
+            // O[16 x D] = alpha * O + P V
+#pragma unroll
+            for (int np = 0; np < D / 16; ++np) {
+                uint32_t b0, b1, b2, b3;
+                const int row = r0 + ((lane >> 3) & 1) * 8 + (lane & 7);
+                ldmatrix_x4_trans(vbase + kv_swizzled_chunk<D>(row, 2 * np + (lane >> 4)), b0, b1, b2, b3);
+                o[2 * np][0] *= alpha; o[2 * np][1] *= alpha;
+                o[2 * np + 1][0] *= alpha; o[2 * np + 1][1] *= alpha;
+                mma_bf16_16816(o[2 * np], pa0, 0u, pa2, 0u, b0, b1);
+                mma_bf16_16816(o[2 * np + 1], pa0, 0u, pa2, 0u, b2, b3);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);
+            if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+
+        // ---- combine the four warps' partial states for this (sequence, head) segment
+        l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+        l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+        if (g < G) {
+            float* rec = merge_buf + ((size_t)warp * ATTN_GMAX + g) * C::REC;
+#pragma unroll
+            for (int nt = 0; nt < D / 8; ++nt) {
+                rec[nt * 8 + 2 * tq] = o[nt][0];
+                rec[nt * 8 + 2 * tq + 1] = o[nt][1];
+            }
+            if (tq == 0) { rec[D] = m_run; rec[D + 1] = l_run; }
+        }
+        compute_bar_sync();
+        const bool whole = seg.tile_begin == 0 && seg.tile_end == seg.tiles_b;
+        const int seg_idx = seg.b * nkv + seg.h;
+        float* part = scratch + (size_t)(cta_slot + seg_idx) * ATTN_GMAX * C::REC;
+        for (int e = threadIdx.x; e < G * D; e += ATTN_COMPUTE_WARPS * 32) {
+            const int hg = e / D, dim = e % D;
+            float mw[ATTN_COMPUTE_WARPS], M = -INFINITY;
+#pragma unroll
+            for (int w = 0; w < ATTN_COMPUTE_WARPS; ++w) {
+                mw[w] = merge_buf[((size_t)w * ATTN_GMAX + hg) * C::REC + D];
+                M = fmaxf(M, mw[w]);
+            }
+            const float Mu = M == -INFINITY ? 0.f : M;
+            float L = 0.f, O = 0.f;
+#pragma unroll
+            for (int w = 0; w < ATTN_COMPUTE_WARPS; ++w) {
+                const float sc = exp2f(mw[w] - Mu);
+                const float* rec = merge_buf + ((size_t)w * ATTN_GMAX + hg) * C::REC;
+                L += rec[D + 1] * sc;
+                O += rec[dim] * sc;
+            }
+            if (whole) {
+                out[((size_t)seg.b * nq + (size_t)seg.h * G + hg) * D + dim] = __float2bfloat16(O / L);
+            } else {
+                part[(size_t)hg * C::REC + dim] = O;
+                if (dim == 0) { part[(size_t)hg * C::REC + D] = M; part[(size_t)hg * C::REC + D + 1] = L; }
+            }
+        }
+        compute_bar_sync();
+    }
+}
+
+// Finish the (sequence, head) pairs whose tiles were split over several CTAs.
+template <int D>
+__global__ void __launch_bounds__(128)
+attn_decode_merge_kernel(const int* __restrict__ tile_prefix, const float* __restrict__ scratch,
+                         __nv_bfloat16* __restrict__ out, int B, int nq, int nkv, int n_ctas) {
+    using C = AttnCfg<D>;
+    pdl_wait();
+    pdl_launch_dependents();
+    const int seg_idx = blockIdx.x;
+    const int b = seg_idx / nkv, h = seg_idx % nkv;
+    const int G = nq / nkv;
+    const int tiles_b = tile_prefix[b + 1] - tile_prefix[b];
+    if (tiles_b == 0) return;
+    const long long total = (long long)tile_prefix[B] * nkv;
+    const long long per = (total + n_ctas - 1) / n_ctas;
+    const long long F0 = (long long)tile_prefix[b] * nkv + (long long)h * tiles_b;
+    const int c_first = (int)(F0 / per), c_last = (int)((F0 + tiles_b - 1) / per);
+    if (c_first == c_last) return;          // the attention CTA already wrote the final output
+    for (int e = threadIdx.x; e < G * D; e += blockDim.x) {
+        const int hg = e / D, dim = e % D;
+        float M = -INFINITY;
+        for (int c = c_first; c <= c_last; ++c)
+            M = fmaxf(M, scratch[((size_t)(c + seg_idx) * ATTN_GMAX + hg) * C::REC + D]);
+        const float Mu = M == -INFINITY ? 0.f : M;
+        float L = 0.f, O = 0.f;
+        for (int c = c_first; c <= c_last; ++c) {
+            const float* rec = scratch + ((size_t)(c + seg_idx) * ATTN_GMAX + hg) * C::REC;
+            const float sc = exp2f(rec[D] - Mu);
+            L += rec[D + 1] * sc;
+            O += rec[dim] * sc;
+        }
+        out[((size_t)b * nq + (size_t)h * G + hg) * D + dim] = __float2bfloat16(O / L);
+    }
+}
+
+// ------------------------------------------------------------------ K6 chunked prefill
+// grid = (q tiles, q heads).  A q tile = 64 consecutive query tokens of one request; warp w
+// owns query rows 16w..16w+15 and walks every KV tile up to the causal diagonal.  Keys/values
+// come from the paged cache (the chunk's own K/V were appended by rope_kv_append before), so a
+// cached prefix and the new tokens take the same path.
+template <int D>
+__global__ void __launch_bounds__(ATTN_THREADS)
+attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restrict__ kv_layer,
+                    const int* __restrict__ page_table, int max_pages,
+                    const int* __restrict__ req_q_start, const int* __restrict__ req_slot,
+                    const int* __restrict__ req_pos0, const int* __restrict__ tile_req,
+                    const int* __restrict__ tile_q0, __nv_bfloat16* __restrict__ out, int nq, int nkv,
+                    float scale_log2) {
+    using C = AttnCfg<D>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)C::STAGES * C::TILE_BYTES);
+    uint64_t* empty_bar = full_bar + C::STAGES;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < C::STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], ATTN_COMPUTE_WARPS);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+    pdl_wait();
+    pdl_launch_dependents();
+
+    const int req = tile_req[blockIdx.x];
+    const int q0 = tile_q0[blockIdx.x];                       // first query of the tile, chunk-relative
+    const int q_len = req_q_start[req + 1] - req_q_start[req];
+    const int pos0 = req_pos0[req];                           // absolute position of chunk query 0
+    const int head = blockIdx.y;
+    const int kvh = head / (nq / nkv);
+    const int rows_here = q_len - q0 < 64 ? q_len - q0 : 64;
+    const int last_pos = pos0 + q0 + rows_here - 1;           // newest key any row of the tile sees
+    const int n_tiles = last_pos / kKvTile + 1;
+    const int* pt = page_table + (size_t)req_slot[req] * max_pages;
+
+    if (warp == ATTN_COMPUTE_WARPS) {
+        const uint64_t pol = policy_evict_last();             // re-read by the other heads / q tiles
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int t0 = 0; t0 < n_tiles; t0 += 32) {
+            const int mine = t0 + lane;
+            const int my_page = mine < n_tiles ? pt[mine] : 0;
+            const int n = n_tiles - t0 < 32 ? n_tiles - t0 : 32;
+            for (int i = 0; i < n; ++i) {
+                const int page = __shfl_sync(0xffffffffu, my_page, i);
+                if (lane == 0) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    mbar_expect_tx(&full_bar[stage], C::TILE_BYTES);
+                    tma_bulk_g2s(smem + (size_t)stage * C::TILE_BYTES,
+                                 kv_layer + ((size_t)page * nkv + kvh) * C::TILE_BYTES, C::TILE_BYTES,
+                                 &full_bar[stage], pol);
+                }
+                if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+        return;
+    }
+
+    const int g = lane >> 2, tq = lane & 3;
+    const int row_a = q0 + warp * 16 + g, row_b = row_a + 8;  // chunk-relative query rows
+    const int pos_a = pos0 + row_a, pos_b = pos0 + row_b;
+    const bool va = row_a < q_len, vb = row_b < q_len;
+    uint32_t qa[D / 16][4];
+    {
+        const __nv_bfloat16* qa_ptr = q + ((size_t)(req_q_start[req] + row_a) * nq + head) * D;
+        const __nv_bfloat16* qb_ptr = q + ((size_t)(req_q_start[req] + row_b) * nq + head) * D;
+#pragma unroll
+        for (int ks = 0; ks < D / 16; ++ks) {
+            qa[ks][0] = va ? *reinterpret_cast<const uint32_t*>(qa_ptr + ks * 16 + 2 * tq) : 0u;
+            qa[ks][1] = vb ? *reinterpret_cast<const uint32_t*>(qb_ptr + ks * 16 + 2 * tq) : 0u;
+            qa[ks][2] = va ? *reinterpret_cast<const uint32_t*>(qa_ptr + ks * 16 + 8 + 2 * tq) : 0u;
+            qa[ks][3] = vb ? *reinterpret_cast<const uint32_t*>(qb_ptr + ks * 16 + 8 + 2 * tq) : 0u;
+        }
+    }
+    float o[D / 8][4];
+#pragma unroll
+    for (int nt = 0; nt < D / 8; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
+    float m_a = -INFINITY, m_b = -INFINITY, l_a = 0.f, l_b = 0.f;
+
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = 0; tile < n_tiles; ++tile) {
+        mbar_wait(&full_bar[stage], phase);
+        const uint32_t kbase = smem_u32(smem + (size_t)stage * C::TILE_BYTES);
+        const uint32_t vbase = kbase + C::SLAB_BYTES;
+        float s[8][4];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+            const int row = 8 * j + (lane & 7);
+#pragma unroll
+            for (int kp = 0; kp < D / 32; ++kp) {
+                uint32_t b0, b1, b2, b3;
+                ldmatrix_x4(kbase + kv_swizzled_chunk<D>(row, kp * 4 + (lane >> 3)), b0, b1, b2, b3);
+                mma_bf16_16816(s[j], qa[2 * kp][0], qa[2 * kp][1], qa[2 * kp][2], qa[2 * kp][3], b0, b1);
+                mma_bf16_16816(s[j], qa[2 * kp + 1][0], qa[2 * kp + 1][1], qa[2 * kp + 1][2],
+                               qa[2 * kp + 1][3], b2, b3);
+            }
+        }
+        const int key0 = tile * kKvTile + 2 * tq;
+        float ta = -INFINITY, tb = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int key = key0 + 8 * j + e;
+                s[j][e] = key <= pos_a ? s[j][e] * scale_log2 : -INFINITY;
+                s[j][2 + e] = key <= pos_b ? s[j][2 + e] * scale_log2 : -INFINITY;
+                ta = fmaxf(ta, s[j][e]);
+                tb = fmaxf(tb, s[j][2 + e]);
+            }
+        ta = fmaxf(ta, __shfl_xor_sync(0xffffffffu, ta, 1));
+        ta = fmaxf(ta, __shfl_xor_sync(0xffffffffu, ta, 2));
+        tb = fmaxf(tb, __shfl_xor_sync(0xffffffffu, tb, 1));
+        tb = fmaxf(tb, __shfl_xor_sync(0xffffffffu, tb, 2));
+        const float na = fmaxf(m_a, ta), nb = fmaxf(m_b, tb);
+        const float ua = na == -INFINITY ? 0.f : na, ub = nb == -INFINITY ? 0.f : nb;
+        const float alpha_a = exp2f(m_a - ua), alpha_b = exp2f(m_b - ub);
+        float sa = 0.f, sb = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                s[j][e] = exp2f(s[j][e] - ua);
+                s[j][2 + e] = exp2f(s[j][2 + e] - ub);
+                sa += s[j][e];
+                sb += s[j][2 + e];
+            }
+        l_a = l_a * alpha_a + sa;
+        l_b = l_b * alpha_b + sb;
+        m_a = na;
+        m_b = nb;
+#pragma unroll
+        for (int nt = 0; nt < D / 8; ++nt) {
+            o[nt][0] *= alpha_a; o[nt][1] *= alpha_a;
+            o[nt][2] *= alpha_b; o[nt][3] *= alpha_b;
+        }
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {               // 16 keys per k-step
+            const uint32_t pa0 = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
+            const uint32_t pa1 = pack_bf16(s[2 * kk][2], s[2 * kk][3]);
+            const uint32_t pa2 = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+            const uint32_t pa3 = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+            const int row = kk * 16 + ((lane >> 3) & 1) * 8 + (lane & 7);
+#pragma unroll
+            for (int np = 0; np < D / 16; ++np) {
+                uint32_t b0, b1, b2, b3;
+                ldmatrix_x4_trans(vbase + kv_swizzled_chunk<D>(row, 2 * np + (lane >> 4)), b0, b1, b2, b3);
+                mma_bf16_16816(o[2 * np], pa0, pa1, pa2, pa3, b0, b1);
+                mma_bf16_16816(o[2 * np + 1], pa0, pa1, pa2, pa3, b2, b3);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[stage]);
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+    }
+    l_a += __shfl_xor_sync(0xffffffffu, l_a, 1);
+    l_a += __shfl_xor_sync(0xffffffffu, l_a, 2);
+    l_b += __shfl_xor_sync(0xffffffffu, l_b, 1);
+    l_b += __shfl_xor_sync(0xffffffffu, l_b, 2);
+    const float ia = 1.f / l_a, ib = 1.f / l_b;
+    __nv_bfloat16* oa = out + ((size_t)(req_q_start[req] + row_a) * nq + head) * D;
+    __nv_bfloat16* ob = out + ((size_t)(req_q_start[req] + row_b) * nq + head) * D;
+#pragma unroll
+    for (int nt = 0; nt < D / 8; ++nt) {
+        if (va) *reinterpret_cast<uint32_t*>(oa + nt * 8 + 2 * tq) = pack_bf16(o[nt][0] * ia, o[nt][1] * ia);
+        if (vb) *reinterpret_cast<uint32_t*>(ob + nt * 8 + 2 * tq) = pack_bf16(o[nt][2] * ib, o[nt][3] * ib);
+    }
+}
+
+// ------------------------------------------------------------------ launchers
+size_t attn_decode_scratch_floats(int B, int nkv, int group, int d, int n_ctas) {
+    (void)group;
+    return (size_t)(n_ctas + B * nkv) * ATTN_GMAX * (d + 2);
+}
+
+template <int D>
+static int decode_ctas_per_sm_d() {
+    using C = AttnCfg<D>;
+    FT_CHECK_CUDA(cudaFuncSetAttribute(attn_decode_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)C::SMEM));
+    int n = 0;
+    FT_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, attn_decode_kernel<D>, ATTN_THREADS,
+                                                                C::SMEM));
+    return n;
+}
+int attn_decode_ctas_per_sm(int d) {
+    if (d == 64) return decode_ctas_per_sm_d<64>();
+    if (d == 128) return decode_ctas_per_sm_d<128>();
+    set_last_error("attn_decode: head_dim %d not supported", d);
+    return -2;
+}
+
+static void fill_cfg(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr, dim3 grid, dim3 block,
+                     size_t smem, bool pdl, cudaStream_t stream) {
+    cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+}
+
+int launch_attn_decode_plan(const int* ctx_lens, int* tile_prefix, int B, bool pdl, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    fill_cfg(cfg, attr, dim3(1), dim3(32), 0, pdl, stream);
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_plan_kernel, ctx_lens, tile_prefix, B));
+    return 0;
+}
+
+template <int D>
+static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                                const int* ctx_lens, const int* tile_prefix, void* out, float* scratch,
+                                int B, int nq, int nkv, int n_ctas, bool pdl, cudaStream_t stream) {
+    using C = AttnCfg<D>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        FT_CHECK_CUDA(cudaFuncSetAttribute(attn_decode_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)C::SMEM));
+        attr_set = true;
+    }
+    const float scale_log2 = LOG2E / sqrtf((float)D);
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    fill_cfg(cfg, attr, dim3(n_ctas), dim3(ATTN_THREADS), C::SMEM, pdl, stream);
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_kernel<D>, (const __nv_bfloat16*)q,
+                                     (const uint8_t*)kv_layer, page_table, max_pages, ctx_lens, tile_prefix,
+                                     (__nv_bfloat16*)out, scratch, B, nq, nkv, scale_log2));
+    fill_cfg(cfg, attr, dim3(B * nkv), dim3(128), 0, pdl, stream);
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_merge_kernel<D>, tile_prefix, (const float*)scratch,
+                                     (__nv_bfloat16*)out, B, nq, nkv, n_ctas));
+    return 0;
+}
+
+int launch_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                       const int* ctx_lens, const int* tile_prefix, void* out, float* scratch, int B,
+                       int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream) {
+    FT_REQUIRE(d == 64 || d == 128, "attn_decode: head_dim %d not supported (64 or 128)", d);
+    FT_REQUIRE(nq % nkv == 0 && nq / nkv <= ATTN_GMAX, "attn_decode: GQA group %d/%d not supported", nq, nkv);
+    FT_REQUIRE(B >= 1 && n_ctas >= 1, "attn_decode: B=%d n_ctas=%d", B, n_ctas);
+    if (d == 64)
+        return launch_attn_decode_d<64>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out,
+                                        scratch, B, nq, nkv, n_ctas, pdl, stream);
+    return launch_attn_decode_d<128>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, scratch,
+                                     B, nq, nkv, n_ctas, pdl, stream);
+}
+
+template <int D>
+static int launch_attn_prefill_d(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                                 const int* req_q_start, const int* req_slot, const int* req_pos0,
+                                 const int* tile_req, const int* tile_q0, int n_tiles, void* out, int nq,
+                                 int nkv, bool pdl, cudaStream_t stream) {
+    using C = AttnCfg<D>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        FT_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)C::SMEM));
+        attr_set = true;
+    }
+    const float scale_log2 = LOG2E / sqrtf((float)D);
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    fill_cfg(cfg, attr, dim3(n_tiles, nq), dim3(ATTN_THREADS), C::SMEM, pdl, stream);
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_kernel<D>, (const __nv_bfloat16*)q,
+                                     (const uint8_t*)kv_layer, page_table, max_pages, req_q_start, req_slot,
+                                     req_pos0, tile_req, tile_q0, (__nv_bfloat16*)out, nq, nkv, scale_log2));
+    return 0;
+}
+
+int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                        const int* req_q_start, const int* req_slot, const int* req_pos0,
+                        const int* tile_req, const int* tile_q0, int n_tiles, void* out, int nq, int nkv,
+                        int d, bool pdl, cudaStream_t stream) {
+    FT_REQUIRE(d == 64 || d == 128, "attn_prefill: head_dim %d not supported (64 or 128)", d);
+    FT_REQUIRE(nq % nkv == 0, "attn_prefill: nq %% nkv != 0");
+    FT_REQUIRE(n_tiles >= 1, "attn_prefill: no tiles");
+    if (d == 64)
+        return launch_attn_prefill_d<64>(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
+                                         tile_req, tile_q0, n_tiles, out, nq, nkv, pdl, stream);
+    return launch_attn_prefill_d<128>(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
+                                      tile_req, tile_q0, n_tiles, out, nq, nkv, pdl, stream);
+}
+
+}  // namespace ft
+
+// ------------------------------------------------------------------ C ABI (kernel level)
+extern "C" int ft_attn_decode_default_ctas(int d) {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+        ft::set_last_error("ft_attn_decode_default_ctas: no CUDA device");
+        return -1;
+    }
+    const int per = ft::attn_decode_ctas_per_sm(d);
+    return per <= 0 ? per : per * sms;
+}
+
+extern "C" long long ft_attn_decode_scratch_bytes(int B, int nkv, int group, int d, int n_ctas) {
+    return (long long)ft::attn_decode_scratch_floats(B, nkv, group, d, n_ctas) * 4;
+}
+
+extern "C" int ft_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                              const int* ctx_lens, int* tile_prefix, void* out, float* scratch, int B, int nq,
+                              int nkv, int d, int n_ctas, void* stream) {
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (int r = ft::launch_attn_decode_plan(ctx_lens, tile_prefix, B, false, st)) return r;
+    return ft::launch_attn_decode(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, scratch, B,
+                                  nq, nkv, d, n_ctas, false, st);
+}
+
+extern "C" int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                               const int* req_q_start, const int* req_slot, const int* req_pos0,
+                               const int* tile_req, const int* tile_q0, int n_tiles, void* out, int nq,
+                               int nkv, int d, void* stream) {
+    return ft::launch_attn_prefill(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
+                                   tile_req, tile_q0, n_tiles, out, nq, nkv, d, false,
+                                   static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,762 @@
+// The engine: KV page allocator, session table with prefix reuse, continuous-batching
+// scheduler (decode rows + chunked-prefill rows in the same step) and the model forward that
+// strings the kernels together.  Host logic only — every FLOP runs in the kernels of
+// gemm.cu / elementwise.cu / attention.cu / sampling.cu.  There is no CPU fallback.
+#include "common.cuh"
+#include "ft_internal.h"
+#include "../../include/fasttalk_b200.h"
+
+#include <algorithm>
+#include <chrono>
+#include <deque>
+#include <mutex>
+#include <new>
+#include <string.h>
+#include <unordered_map>
+#include <vector>
+
+namespace ft {
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+struct Session {
+    unsigned long long key = 0;
+    std::vector<int> pages;      // KV pages in position order
+    std::vector<int> tokens;     // tokens whose K/V sit in the cache (positions 0..size-1)
+    bool busy = false;
+    long long last_used = 0;
+};
+
+enum ReqState { REQ_WAITING = 0, REQ_PREFILL = 1, REQ_DECODE = 2, REQ_DONE = 3 };
+
+struct Request {
+    long long id = 0;
+    Session* sess = nullptr;
+    std::vector<int> prompt;     // full token list of this turn
+    int prefill_pos = 0;         // next prompt index to run through the model
+    float temperature = 0.f, top_p = 1.f;
+    int top_k = 0, max_new = 0, n_generated = 0, ignore_eos = 0;
+    unsigned long long seed = 0;
+    int state = REQ_WAITING;
+    int last_token = -1;         // sampled but not yet fed back
+    int logits_row = -1;         // row of the logits buffer in the latest step
+};
+
+struct OutTok { long long req; int token; int finish; };
+
+// host-pinned + device mirror of everything a step's kernels index
+struct StepMeta {
+    int* h = nullptr;
+    int* d = nullptr;
+    size_t ints = 0;
+    // offsets (in ints).  Fixed-size arrays come first; the page table and the per-token arrays
+    // are packed behind them at per-step offsets so one H2D copy moves only what the step uses.
+    size_t o_ctx, o_qstart, o_rslot, o_rpos0, o_treq, o_tq0, o_lrow, o_temp, o_topk, o_topp, o_seed,
+        o_pt;                                     // fixed
+    size_t o_tokens, o_pos, o_rows, upload_ints;  // set by layout_step()
+    size_t o_tprefix, o_sampled;                  // device-side work areas (never uploaded)
+};
+
+static inline size_t align4(size_t n) { return (n + 3) & ~size_t(3); }
+static void layout_step(StepMeta& m, int n_req, int max_pages, int T) {
+    m.o_tokens = m.o_pt + align4((size_t)n_req * max_pages);
+    m.o_pos = m.o_tokens + align4(T);
+    m.o_rows = m.o_pos + align4(T);
+    m.upload_ints = m.o_rows + align4(T);
+}
+
+struct Engine {
+    ft_engine_config cfg;
+    ft_weights w;
+    int dev = 0, sms = 148;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+
+    int q_dim, kv_dim, qkv_dim, group, max_pages, t_max, r_max, logit_rows;
+    int attn_ctas = 0;
+    size_t kv_layer_bytes = 0;
+
+    // device buffers
+    uint8_t* kv = nullptr;
+    float* resid = nullptr;
+    float* part = nullptr;
+    size_t part_floats = 0;
+    void *xn = nullptr, *q = nullptr, *attn_out = nullptr, *act = nullptr, *xn_last = nullptr;
+    float* logits = nullptr;
+    float* attn_scratch = nullptr;
+    StepMeta meta;
+
+    // tensor maps: weights per layer, activations per BN
+    std::vector<CUtensorMap> m_wqkv, m_wo, m_wgu, m_wd;
+    CUtensorMap m_lm;
+    CUtensorMap m_xn[5], m_attn[5], m_act[5], m_last[5];
+
+    // scheduler state
+    std::vector<int> free_pages;
+    std::unordered_map<unsigned long long, Session*> sessions;
+    std::unordered_map<long long, Request*> requests;
+    std::deque<Request*> waiting;
+    std::vector<Request*> active;
+    std::deque<OutTok> out;
+    long long next_req = 0, clock = 0;
+    ft_engine_stats st = {};
+    bool pdl = false;
+};
+
+static int bn_index(int bn) { return bn == 16 ? 0 : bn == 32 ? 1 : bn == 64 ? 2 : bn == 128 ? 3 : 4; }
+static const int kBns[5] = {16, 32, 64, 128, 256};
+
+// ------------------------------------------------------------------ pages / sessions
+static void release_pages_beyond(Engine* e, Session* s, int keep_tokens) {
+    const int keep = ceil_div(keep_tokens, kKvTile);
+    while ((int)s->pages.size() > keep) {
+        e->free_pages.push_back(s->pages.back());
+        s->pages.pop_back();
+    }
+    if ((int)s->tokens.size() > keep_tokens) s->tokens.resize(keep_tokens);
+}
+
+static void drop_session(Engine* e, Session* s) {
+    release_pages_beyond(e, s, 0);
+    e->sessions.erase(s->key);
+    delete s;
+}
+
+// Free pages by evicting idle sessions, least recently used first.
+static bool reclaim_pages(Engine* e, int need) {
+    while ((int)e->free_pages.size() < need) {
+        Session* victim = nullptr;
+        for (auto& kv : e->sessions)
+            if (!kv.second->busy && !kv.second->pages.empty() &&
+                (!victim || kv.second->last_used < victim->last_used))
+                victim = kv.second;
+        if (!victim) return false;
+        release_pages_beyond(e, victim, 0);
+    }
+    return true;
+}
+
+static bool ensure_pages(Engine* e, Session* s, int n_tokens) {
+    const int need = ceil_div(n_tokens, kKvTile) - (int)s->pages.size();
+    if (need <= 0) return true;
+    if ((int)e->free_pages.size() < need && !reclaim_pages(e, need)) return false;
+    for (int i = 0; i < need; ++i) {
+        s->pages.push_back(e->free_pages.back());
+        e->free_pages.pop_back();
+    }
+    return true;
+}
+
+static void finish_request(Engine* e, Request* r, int reason, int token) {
+    e->out.push_back({r->id, token, reason});
+    r->state = REQ_DONE;
+    if (r->sess) {
+        r->sess->busy = false;
+        r->sess->last_used = ++e->clock;
+    }
+}
+
+// ------------------------------------------------------------------ forward
+struct Batch {
+    int n_decode = 0;                 // rows [0, n_decode): one token per sequence
+    int T = 0;                        // total token rows
+    int n_req = 0;                    // page-table rows (decode first, then prefill requests)
+    int n_prefill_req = 0;
+    int n_tiles = 0;                  // prefill attention q tiles
+    int n_logit_rows = 0;
+};
+
+#define FT_TRY(x)                                   \
+    do {                                            \
+        int _r = (x);                               \
+        if (_r) return _r;                          \
+    } while (0)
+
+static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, int T, int n_out, int K,
+                    void* out, int* splits_out) {
+    const int bn = gemm_pick_bn(T);
+    const int splits = gemm_pick_splits(n_out, T, K, e->sms);
+    *splits_out = splits;
+    e->st.kernel_launches++;
+    return launch_gemm(mw, xmaps[bn_index(bn)], bn, out, n_out, T, K, splits, 0, e->pdl, e->stream);
+}
+
+static int forward(Engine* e, const Batch& b) {
+    const ft_engine_config& c = e->cfg;
+    StepMeta& m = e->meta;
+    int* d = m.d;
+    const int T = b.T;
+    const size_t H = c.hidden;
+    auto bf16_off = [](const void* p, size_t elems) {
+        return (const void*)((const uint8_t*)p + elems * 2);
+    };
+    FT_TRY(launch_add_rmsnorm(e->resid, nullptr, 0, 0, d + m.o_tokens, e->w.embed, e->w.attn_norm, e->xn,
+                              nullptr, T, c.hidden, c.rms_eps, e->pdl, e->stream));
+    e->st.kernel_launches++;
+    if (b.n_decode > 0) {
+        FT_TRY(launch_attn_decode_plan(d + m.o_ctx, d + m.o_tprefix, b.n_decode, e->pdl, e->stream));
+        e->st.kernel_launches++;
+    }
+    int s = 0;
+    for (int l = 0; l < c.layers; ++l) {
+        uint8_t* kv_l = e->kv + (size_t)l * e->kv_layer_bytes;
+        FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, T, e->qkv_dim, c.hidden, e->part, &s));
+        FT_TRY(launch_rope_kv_append(e->part, s, (size_t)T * e->qkv_dim, e->w.rope_cos, e->w.rope_sin,
+                                     d + m.o_pos, d + m.o_rows, d + m.o_pt, e->max_pages, e->q, kv_l, T,
+                                     c.n_q_heads, c.n_kv_heads, c.head_dim, e->pdl, e->stream));
+        e->st.kernel_launches++;
+        if (b.n_decode > 0) {
+            FT_TRY(launch_attn_decode(e->q, kv_l, d + m.o_pt, e->max_pages, d + m.o_ctx, d + m.o_tprefix,
+                                      e->attn_out, e->attn_scratch, b.n_decode, c.n_q_heads, c.n_kv_heads,
+                                      c.head_dim, e->attn_ctas, e->pdl, e->stream));
+            e->st.kernel_launches += 2;
+        }
+        if (b.n_tiles > 0) {
+            FT_TRY(launch_attn_prefill(e->q, kv_l, d + m.o_pt, e->max_pages, d + m.o_qstart, d + m.o_rslot,
+                                       d + m.o_rpos0, d + m.o_treq, d + m.o_tq0, b.n_tiles, e->attn_out,
+                                       c.n_q_heads, c.n_kv_heads, c.head_dim, e->pdl, e->stream));
+            e->st.kernel_launches++;
+        }
+        FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, T, c.hidden, e->q_dim, e->part, &s));
+        FT_TRY(launch_add_rmsnorm(e->resid, e->part, s, (size_t)T * H, nullptr, nullptr,
+                                  bf16_off(e->w.mlp_norm, (size_t)l * H), e->xn, nullptr, T, c.hidden,
+                                  c.rms_eps, e->pdl, e->stream));
+        e->st.kernel_launches++;
+        FT_TRY(run_gemm(e, e->m_wgu[l], e->m_xn, T, 2 * c.ffn, c.hidden, e->part, &s));
+        FT_TRY(launch_silu_mul(e->part, s, (size_t)T * 2 * c.ffn, e->act, T, c.ffn, e->pdl, e->stream));
+        e->st.kernel_launches++;
+        FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, T, c.hidden, c.ffn, e->part, &s));
+        if (l + 1 < c.layers) {
+            FT_TRY(launch_add_rmsnorm(e->resid, e->part, s, (size_t)T * H, nullptr, nullptr,
+                                      bf16_off(e->w.attn_norm, (size_t)(l + 1) * H), e->xn, nullptr, T,
+                                      c.hidden, c.rms_eps, e->pdl, e->stream));
+            e->st.kernel_launches++;
+        }
+    }
+    if (b.n_logit_rows > 0) {
+        FT_TRY(launch_add_rmsnorm(e->resid, e->part, s, (size_t)T * H, nullptr, nullptr, e->w.final_norm,
+                                  e->xn_last, d + m.o_lrow, b.n_logit_rows, c.hidden, c.rms_eps, e->pdl,
+                                  e->stream));
+        e->st.kernel_launches++;
+        int s2 = 0;
+        const int bn = gemm_pick_bn(b.n_logit_rows);
+        e->st.kernel_launches++;
+        FT_TRY(launch_gemm(e->m_lm, e->m_last[bn_index(bn)], bn, e->logits, c.vocab, b.n_logit_rows,
+                           c.hidden, 1, 0, e->pdl, e->stream));
+        (void)s2;
+    }
+    return 0;
+}
+
+static int upload_meta(Engine* e) {
+    FT_CHECK_CUDA(cudaMemcpyAsync(e->meta.d, e->meta.h, e->meta.upload_ints * sizeof(int),
+                                  cudaMemcpyHostToDevice, e->stream));
+    return 0;
+}
+
+static unsigned long long mix64(unsigned long long x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+
+// ------------------------------------------------------------------ one scheduler step
+static int engine_step(Engine* e) {
+    const ft_engine_config& c = e->cfg;
+    StepMeta& m = e->meta;
+    const auto t_begin = std::chrono::steady_clock::now();
+
+    // retire finished requests from the active list
+    e->active.erase(std::remove_if(e->active.begin(), e->active.end(),
+                                   [&](Request* r) { return r->state == REQ_DONE; }),
+                    e->active.end());
+    // admit
+    while (!e->waiting.empty() && (int)e->active.size() < c.max_batch) {
+        Request* r = e->waiting.front();
+        if (r->state == REQ_DONE) { e->waiting.pop_front(); continue; }
+        if (!ensure_pages(e, r->sess, (int)r->prompt.size() + 1)) {
+            if (e->active.empty()) {            // nothing will ever free pages for it
+                e->waiting.pop_front();
+                finish_request(e, r, 4, -1);
+                continue;
+            }
+            break;
+        }
+        e->waiting.pop_front();
+        r->state = REQ_PREFILL;
+        e->active.push_back(r);
+    }
+    if (e->active.empty()) return 0;
+
+    // ---- build the batch: decode rows first, then prefill chunks up to the token budget
+    Batch b;
+    int* h = m.h;
+    std::vector<Request*> dec, pre;
+    std::vector<int> pre_len;
+    for (Request* r : e->active)
+        if (r->state == REQ_DECODE) dec.push_back(r);
+    int budget = c.max_batched_tokens - (int)dec.size();
+    for (Request* r : e->active) {
+        if (r->state != REQ_PREFILL || budget <= 0) continue;
+        const int remaining = (int)r->prompt.size() - r->prefill_pos;
+        const int take = std::min(remaining, budget);
+        pre.push_back(r);
+        pre_len.push_back(take);
+        budget -= take;
+    }
+    // page growth for decode rows (evicting idle sessions if needed)
+    for (size_t i = 0; i < dec.size();) {
+        Request* r = dec[i];
+        if (!ensure_pages(e, r->sess, (int)r->sess->tokens.size() + 1)) {
+            finish_request(e, r, 2, -1);
+            dec.erase(dec.begin() + i);
+        } else {
+            ++i;
+        }
+    }
+    b.n_decode = (int)dec.size();
+    b.n_prefill_req = (int)pre.size();
+    b.n_req = b.n_decode + b.n_prefill_req;
+    if (b.n_req == 0) return 0;
+    {
+        int total = b.n_decode;
+        for (int len : pre_len) total += len;
+        layout_step(m, b.n_req, e->max_pages, total);
+    }
+
+    int row = 0, lrow = 0;
+    for (int i = 0; i < b.n_decode; ++i, ++row) {
+        Request* r = dec[i];
+        Session* s = r->sess;
+        const int pos = (int)s->tokens.size();
+        h[m.o_tokens + row] = r->last_token;
+        h[m.o_pos + row] = pos;
+        h[m.o_rows + row] = i;
+        h[m.o_ctx + i] = pos + 1;
+        for (size_t p = 0; p < s->pages.size(); ++p) h[m.o_pt + (size_t)i * e->max_pages + p] = s->pages[p];
+        h[m.o_lrow + lrow] = row;
+        r->logits_row = lrow++;
+    }
+    int tiles = 0;
+    h[m.o_qstart] = row;
+    for (int j = 0; j < b.n_prefill_req; ++j) {
+        Request* r = pre[j];
+        Session* s = r->sess;
+        const int pt_row = b.n_decode + j;
+        const int pos0 = r->prefill_pos;
+        for (int k = 0; k < pre_len[j]; ++k, ++row) {
+            h[m.o_tokens + row] = r->prompt[pos0 + k];
+            h[m.o_pos + row] = pos0 + k;
+            h[m.o_rows + row] = pt_row;
+        }
+        h[m.o_qstart + j + 1] = row;
+        h[m.o_rslot + j] = pt_row;
+        h[m.o_rpos0 + j] = pos0;
+        for (size_t p = 0; p < s->pages.size(); ++p)
+            h[m.o_pt + (size_t)pt_row * e->max_pages + p] = s->pages[p];
+        for (int q0 = 0; q0 < pre_len[j]; q0 += 64, ++tiles) {
+            h[m.o_treq + tiles] = j;
+            h[m.o_tq0 + tiles] = q0;
+        }
+        r->logits_row = -1;
+        if (pos0 + pre_len[j] == (int)r->prompt.size()) {      // prompt complete: sample from last row
+            h[m.o_lrow + lrow] = row - 1;
+            r->logits_row = lrow++;
+        }
+    }
+    b.T = row;
+    b.n_tiles = tiles;
+    b.n_logit_rows = lrow;
+    // sampling parameters per logit row
+    float* hf = reinterpret_cast<float*>(h);
+    unsigned long long* hseed = reinterpret_cast<unsigned long long*>(h + m.o_seed);
+    auto put_sampling = [&](Request* r) {
+        const int lr = r->logits_row;
+        hf[m.o_temp + lr] = r->temperature;
+        h[m.o_topk + lr] = r->top_k;
+        hf[m.o_topp + lr] = r->top_p;
+        hseed[lr] = mix64(r->seed * 0x100000001B3ull + (unsigned long long)r->n_generated);
+    };
+    for (Request* r : dec) put_sampling(r);
+    for (Request* r : pre) if (r->logits_row >= 0) put_sampling(r);
+
+    FT_TRY(upload_meta(e));
+    FT_TRY(forward(e, b));
+    if (b.n_logit_rows > 0) {
+        const float* dtemp = reinterpret_cast<const float*>(m.d + m.o_temp);
+        const float* dtopp = reinterpret_cast<const float*>(m.d + m.o_topp);
+        const unsigned long long* dseed = reinterpret_cast<const unsigned long long*>(m.d + m.o_seed);
+        FT_TRY(launch_sample(e->logits, b.n_logit_rows, c.vocab, dtemp, m.d + m.o_topk, dtopp, dseed,
+                             m.d + m.o_sampled, e->pdl, e->stream));
+        e->st.kernel_launches++;
+        FT_CHECK_CUDA(cudaMemcpyAsync(h + m.o_sampled, m.d + m.o_sampled, b.n_logit_rows * sizeof(int),
+                                      cudaMemcpyDeviceToHost, e->stream));
+    }
+    FT_CHECK_CUDA(cudaStreamSynchronize(e->stream));
+
+    // ---- bookkeeping: the K/V of every token we just ran is now cached
+    int produced = 0;
+    auto emit = [&](Request* r) {
+        const int tok = h[m.o_sampled + r->logits_row];
+        r->last_token = tok;
+        r->n_generated++;
+        produced++;
+        bool is_eos = false;
+        if (!r->ignore_eos)
+            for (int k = 0; k < c.n_eos; ++k) is_eos |= tok == c.eos_ids[k];
+        const int ctx_after = (int)r->sess->tokens.size() + 1;      // if this token were fed back
+        if (is_eos) finish_request(e, r, 1, tok);
+        else if (r->n_generated >= r->max_new || ctx_after >= c.max_context) finish_request(e, r, 2, tok);
+        else e->out.push_back({r->id, tok, 0});
+    };
+    for (Request* r : dec) {
+        r->sess->tokens.push_back(r->last_token);
+        emit(r);
+    }
+    for (int j = 0; j < b.n_prefill_req; ++j) {
+        Request* r = pre[j];
+        Session* s = r->sess;
+        s->tokens.insert(s->tokens.end(), r->prompt.begin() + r->prefill_pos,
+                         r->prompt.begin() + r->prefill_pos + pre_len[j]);
+        r->prefill_pos += pre_len[j];
+        e->st.prefill_tokens += pre_len[j];
+        if (r->logits_row >= 0) {
+            r->state = REQ_DECODE;
+            emit(r);
+        }
+    }
+    e->st.steps++;
+    if (b.n_decode > 0) e->st.decode_steps++;
+    e->st.decode_tokens += b.n_decode;
+    e->st.last_batch = b.n_req;
+    e->st.last_prefill_tokens = b.T - b.n_decode;
+    e->st.last_step_ms =
+        std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+    return produced;
+}
+
+// ------------------------------------------------------------------ construction
+static int engine_init(Engine* e) {
+    const ft_engine_config& c = e->cfg;
+    FT_REQUIRE(c.head_dim == 64 || c.head_dim == 128, "engine: head_dim %d not supported", c.head_dim);
+    FT_REQUIRE(c.n_q_heads % c.n_kv_heads == 0 && c.n_q_heads / c.n_kv_heads <= 8,
+               "engine: GQA group must divide and be <= 8");
+    FT_REQUIRE(c.hidden % 128 == 0 && c.ffn % 128 == 0 && c.vocab % 128 == 0,
+               "engine: hidden/ffn/vocab must be multiples of 128");
+    FT_REQUIRE(c.max_batch >= 1 && c.max_batched_tokens >= c.max_batch, "engine: bad batch limits");
+    FT_REQUIRE(c.max_context >= 64 && c.num_pages >= 1, "engine: bad context/page limits");
+    FT_CHECK_CUDA(cudaGetDevice(&e->dev));
+    FT_CHECK_CUDA(cudaDeviceGetAttribute(&e->sms, cudaDevAttrMultiProcessorCount, e->dev));
+    int cc_major = 0;
+    FT_CHECK_CUDA(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, e->dev));
+    FT_REQUIRE(cc_major == 10, "engine: needs an sm_100 GPU (found compute capability %d.x)", cc_major);
+    FT_CHECK_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+
+    e->q_dim = c.n_q_heads * c.head_dim;
+    e->kv_dim = c.n_kv_heads * c.head_dim;
+    e->qkv_dim = e->q_dim + 2 * e->kv_dim;
+    FT_REQUIRE(e->qkv_dim % 128 == 0 && e->q_dim % 64 == 0, "engine: projection dims must tile");
+    e->group = c.n_q_heads / c.n_kv_heads;
+    e->max_pages = ceil_div(c.max_context, kKvTile);
+    e->t_max = c.max_batched_tokens;
+    e->r_max = c.max_batch;
+    e->logit_rows = std::max(c.max_batch, c.debug_logit_rows);
+    e->pdl = c.use_pdl != 0;
+    e->kv_layer_bytes = (size_t)c.num_pages * c.n_kv_heads * 2 * kKvTile * c.head_dim * 2;
+
+    const size_t T = e->t_max;
+    FT_CHECK_CUDA(cudaMalloc(&e->kv, e->kv_layer_bytes * c.layers));
+    FT_CHECK_CUDA(cudaMemsetAsync(e->kv, 0, e->kv_layer_bytes * c.layers, e->stream));
+    FT_CHECK_CUDA(cudaMalloc(&e->resid, T * c.hidden * 4));
+    const size_t rows_last = std::max<size_t>(e->logit_rows, 256);
+    FT_CHECK_CUDA(cudaMalloc(&e->xn, T * c.hidden * 2));
+    FT_CHECK_CUDA(cudaMalloc(&e->q, T * e->q_dim * 2));
+    FT_CHECK_CUDA(cudaMalloc(&e->attn_out, T * e->q_dim * 2));
+    FT_CHECK_CUDA(cudaMalloc(&e->act, T * c.ffn * 2));
+    FT_CHECK_CUDA(cudaMalloc(&e->xn_last, rows_last * c.hidden * 2));
+    FT_CHECK_CUDA(cudaMalloc(&e->logits, (size_t)e->logit_rows * c.vocab * 4));
+    FT_CHECK_CUDA(cudaMemsetAsync(e->xn, 0, T * c.hidden * 2, e->stream));
+    FT_CHECK_CUDA(cudaMemsetAsync(e->attn_out, 0, T * e->q_dim * 2, e->stream));
+    FT_CHECK_CUDA(cudaMemsetAsync(e->act, 0, T * c.ffn * 2, e->stream));
+    FT_CHECK_CUDA(cudaMemsetAsync(e->xn_last, 0, rows_last * c.hidden * 2, e->stream));
+    // split-K partial sums: worst case over the four projections and every token count
+    size_t pf = 0;
+    const int widths[4] = {e->qkv_dim, c.hidden, 2 * c.ffn, c.hidden};
+    const int ks[4] = {c.hidden, e->q_dim, c.hidden, c.ffn};
+    for (int t = 1; t <= e->t_max; ++t)
+        for (int i = 0; i < 4; ++i)
+            pf = std::max(pf, (size_t)gemm_pick_splits(widths[i], t, ks[i], e->sms) * t * widths[i]);
+    e->part_floats = pf;
+    FT_CHECK_CUDA(cudaMalloc(&e->part, pf * 4));
+
+    // decode attention: persistent grid = SMs x resident CTAs
+    {
+        int per_sm = attn_decode_ctas_per_sm(c.head_dim);
+        FT_REQUIRE(per_sm >= 1, "engine: decode attention kernel does not fit on an SM (%s)", last_error());
+        e->attn_ctas = e->sms * per_sm;
+    }
+    FT_CHECK_CUDA(cudaMalloc(&e->attn_scratch,
+                             attn_decode_scratch_floats(e->r_max, c.n_kv_heads, e->group, c.head_dim,
+                                                        e->attn_ctas) * 4));
+
+    // step metadata block
+    StepMeta& m = e->meta;
+    size_t o = 0;
+    auto take = [&](size_t n) { size_t r = o; o += align4(n); return r; };
+    const size_t R = e->r_max, LR = rows_last;
+    const size_t max_tiles = T / 64 + R + 1;
+    m.o_ctx = take(R); m.o_qstart = take(R + 1); m.o_rslot = take(R); m.o_rpos0 = take(R);
+    m.o_treq = take(max_tiles); m.o_tq0 = take(max_tiles);
+    m.o_lrow = take(LR); m.o_temp = take(LR); m.o_topk = take(LR); m.o_topp = take(LR);
+    m.o_seed = take(2 * LR);
+    m.o_pt = take(0);
+    o += align4(R * e->max_pages) + 3 * align4(T);      // page table + tokens | positions | rows
+    m.o_tprefix = take(R + 1);
+    m.o_sampled = take(LR);
+    m.ints = o;
+    layout_step(m, (int)R, e->max_pages, (int)T);
+    FT_CHECK_CUDA(cudaMallocHost(&m.h, o * sizeof(int)));
+    FT_CHECK_CUDA(cudaMalloc(&m.d, o * sizeof(int)));
+    memset(m.h, 0, o * sizeof(int));
+    FT_CHECK_CUDA(cudaMemsetAsync(m.d, 0, o * sizeof(int), e->stream));
+
+    // tensor maps
+    const size_t L = c.layers;
+    e->m_wqkv.resize(L); e->m_wo.resize(L); e->m_wgu.resize(L); e->m_wd.resize(L);
+    auto at = [](const void* p, size_t elems) { return (const void*)((const uint8_t*)p + elems * 2); };
+    for (size_t l = 0; l < L; ++l) {
+        FT_TRY(make_tmap_bf16_k64(&e->m_wqkv[l], at(e->w.wqkv, l * e->qkv_dim * c.hidden), e->qkv_dim, c.hidden, 128));
+        FT_TRY(make_tmap_bf16_k64(&e->m_wo[l], at(e->w.wo, l * (size_t)c.hidden * e->q_dim), c.hidden, e->q_dim, 128));
+        FT_TRY(make_tmap_bf16_k64(&e->m_wgu[l], at(e->w.wgu, l * 2 * (size_t)c.ffn * c.hidden), 2 * c.ffn, c.hidden, 128));
+        FT_TRY(make_tmap_bf16_k64(&e->m_wd[l], at(e->w.wd, l * (size_t)c.hidden * c.ffn), c.hidden, c.ffn, 128));
+    }
+    FT_TRY(make_tmap_bf16_k64(&e->m_lm, e->w.lm_head, c.vocab, c.hidden, 128));
+    for (int i = 0; i < 5; ++i) {
+        // activation maps span the whole buffer; rows past the step's T hold stale (finite) data
+        // whose output columns the GEMM epilogue masks
+        FT_TRY(make_tmap_bf16_k64(&e->m_xn[i], e->xn, (int)T, c.hidden, kBns[i]));
+        FT_TRY(make_tmap_bf16_k64(&e->m_attn[i], e->attn_out, (int)T, e->q_dim, kBns[i]));
+        FT_TRY(make_tmap_bf16_k64(&e->m_act[i], e->act, (int)T, c.ffn, kBns[i]));
+        FT_TRY(make_tmap_bf16_k64(&e->m_last[i], e->xn_last, (int)rows_last, c.hidden, kBns[i]));
+    }
+    e->free_pages.reserve(c.num_pages);
+    for (int p = c.num_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
+    e->st.total_pages = c.num_pages;
+    FT_CHECK_CUDA(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+static void engine_free(Engine* e) {
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    for (auto& kv : e->sessions) delete kv.second;
+    for (auto& kv : e->requests) delete kv.second;
+    cudaFree(e->kv); cudaFree(e->resid); cudaFree(e->part); cudaFree(e->xn); cudaFree(e->q);
+    cudaFree(e->attn_out); cudaFree(e->act); cudaFree(e->xn_last); cudaFree(e->logits);
+    cudaFree(e->attn_scratch); cudaFree(e->meta.d);
+    if (e->meta.h) cudaFreeHost(e->meta.h);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+}  // namespace ft
+
+// ------------------------------------------------------------------ C ABI (engine level)
+using namespace ft;
+
+extern "C" ft_engine* ft_engine_create(const ft_engine_config* cfg, const ft_weights* w) {
+    if (!cfg || !w) { set_last_error("ft_engine_create: null argument"); return nullptr; }
+    Engine* e = new (std::nothrow) Engine();
+    if (!e) { set_last_error("ft_engine_create: out of host memory"); return nullptr; }
+    e->cfg = *cfg;
+    e->w = *w;
+    if (e->cfg.max_sessions < e->cfg.max_batch) e->cfg.max_sessions = e->cfg.max_batch * 4;
+    if (engine_init(e) != 0) { engine_free(e); return nullptr; }
+    return reinterpret_cast<ft_engine*>(e);
+}
+
+extern "C" void ft_engine_destroy(ft_engine* h) {
+    if (h) engine_free(reinterpret_cast<Engine*>(h));
+}
+
+extern "C" long long ft_engine_submit(ft_engine* h, unsigned long long key, const int* tokens, int n,
+                                      float temperature, int top_k, float top_p, int max_new,
+                                      unsigned long long seed, int ignore_eos) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e && tokens && n >= 1, "ft_engine_submit: bad arguments");
+    FT_REQUIRE(max_new >= 1, "ft_engine_submit: max_new_tokens must be >= 1");
+    FT_REQUIRE(n + 1 <= e->cfg.max_context, "ft_engine_submit: prompt of %d tokens does not fit the %d-token context window", n, e->cfg.max_context);
+    for (int i = 0; i < n; ++i)
+        FT_REQUIRE(tokens[i] >= 0 && tokens[i] < e->cfg.vocab, "ft_engine_submit: token %d out of range at %d", tokens[i], i);
+    std::lock_guard<std::mutex> lk(e->mu);
+    Session* s = nullptr;
+    auto it = e->sessions.find(key);
+    if (it != e->sessions.end()) {
+        s = it->second;
+        FT_REQUIRE(!s->busy, "ft_engine_submit: session %llu already has a generation in flight", key);
+    } else {
+        if ((int)e->sessions.size() >= e->cfg.max_sessions) {      // drop the stalest idle session
+            Session* victim = nullptr;
+            for (auto& kv : e->sessions)
+                if (!kv.second->busy && (!victim || kv.second->last_used < victim->last_used)) victim = kv.second;
+            FT_REQUIRE(victim, "ft_engine_submit: all %d sessions are busy", e->cfg.max_sessions);
+            drop_session(e, victim);
+        }
+        s = new Session();
+        s->key = key;
+        e->sessions[key] = s;
+    }
+    // longest common prefix with the cached conversation; at least one token must run
+    int lcp = 0;
+    const int lim = std::min((int)s->tokens.size(), n - 1);
+    while (lcp < lim && s->tokens[lcp] == tokens[lcp]) ++lcp;
+    release_pages_beyond(e, s, lcp);
+    e->st.prefix_hit_tokens += lcp;
+    s->busy = true;
+    s->last_used = ++e->clock;
+    Request* r = new Request();
+    r->id = e->next_req++;
+    r->sess = s;
+    r->prompt.assign(tokens, tokens + n);
+    r->prefill_pos = lcp;
+    r->temperature = temperature;
+    r->top_k = top_k;
+    r->top_p = top_p;
+    r->max_new = max_new;
+    r->seed = seed;
+    r->ignore_eos = ignore_eos;
+    e->requests[r->id] = r;
+    e->waiting.push_back(r);
+    return r->id;
+}
+
+extern "C" int ft_engine_step(ft_engine* h) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e, "ft_engine_step: null engine");
+    std::lock_guard<std::mutex> lk(e->mu);
+    return engine_step(e);
+}
+
+extern "C" int ft_engine_drain(ft_engine* h, long long* req_ids, int* tokens, int* finish, int cap) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e && req_ids && tokens && finish, "ft_engine_drain: bad arguments");
+    std::lock_guard<std::mutex> lk(e->mu);
+    int n = 0;
+    while (n < cap && !e->out.empty()) {
+        const OutTok& o = e->out.front();
+        req_ids[n] = o.req; tokens[n] = o.token; finish[n] = o.finish;
+        if (o.finish) {                 // the request is over: forget it
+            auto it = e->requests.find(o.req);
+            if (it != e->requests.end() && it->second->state == REQ_DONE) {
+                Request* r = it->second;
+                e->active.erase(std::remove(e->active.begin(), e->active.end(), r), e->active.end());
+                e->waiting.erase(std::remove(e->waiting.begin(), e->waiting.end(), r), e->waiting.end());
+                delete r;
+                e->requests.erase(it);
+            }
+        }
+        e->out.pop_front();
+        ++n;
+    }
+    return n;
+}
+
+extern "C" int ft_engine_cancel(ft_engine* h, long long req) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e, "ft_engine_cancel: null engine");
+    std::lock_guard<std::mutex> lk(e->mu);
+    auto it = e->requests.find(req);
+    if (it == e->requests.end() || it->second->state == REQ_DONE) return 1;    // nothing to cancel
+    finish_request(e, it->second, 3, -1);
+    return 0;
+}
+
+extern "C" int ft_engine_session_close(ft_engine* h, unsigned long long key) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e, "ft_engine_session_close: null engine");
+    std::lock_guard<std::mutex> lk(e->mu);
+    auto it = e->sessions.find(key);
+    if (it == e->sessions.end()) return 1;
+    Session* s = it->second;
+    if (s->busy)
+        for (auto& kv : e->requests)
+            if (kv.second->sess == s && kv.second->state != REQ_DONE) {
+                finish_request(e, kv.second, 3, -1);
+            }
+    for (auto& kv : e->requests)
+        if (kv.second->sess == s) kv.second->sess = nullptr;
+    drop_session(e, s);
+    return 0;
+}
+
+extern "C" int ft_engine_stats_get(ft_engine* h, ft_engine_stats* out) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e && out, "ft_engine_stats_get: bad arguments");
+    std::lock_guard<std::mutex> lk(e->mu);
+    e->st.active_requests = 0;
+    for (Request* r : e->active) e->st.active_requests += r->state != REQ_DONE;
+    e->st.waiting_requests = (int)e->waiting.size();
+    e->st.live_sessions = (int)e->sessions.size();
+    e->st.free_pages = (int)e->free_pages.size();
+    *out = e->st;
+    return 0;
+}
+
+extern "C" int ft_engine_get_logits(ft_engine* h, long long req, float* host_out) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e && host_out, "ft_engine_get_logits: bad arguments");
+    std::lock_guard<std::mutex> lk(e->mu);
+    auto it = e->requests.find(req);
+    FT_REQUIRE(it != e->requests.end() && it->second->logits_row >= 0,
+               "ft_engine_get_logits: request %lld has no logits from the last step", req);
+    FT_CHECK_CUDA(cudaMemcpy(host_out, e->logits + (size_t)it->second->logits_row * e->cfg.vocab,
+                             (size_t)e->cfg.vocab * 4, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int ft_debug_prefill_logits(ft_engine* h, const int* tokens, int n, int chunk, float* host_out) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e && tokens && host_out && n >= 1, "ft_debug_prefill_logits: bad arguments");
+    std::lock_guard<std::mutex> lk(e->mu);
+    FT_REQUIRE(e->active.empty() && e->waiting.empty(), "ft_debug_prefill_logits: engine must be idle");
+    FT_REQUIRE(chunk >= 1 && chunk <= e->logit_rows && chunk <= e->t_max,
+               "ft_debug_prefill_logits: chunk %d exceeds debug_logit_rows %d / max_batched_tokens %d", chunk,
+               e->logit_rows, e->t_max);
+    FT_REQUIRE(n + 1 <= e->cfg.max_context, "ft_debug_prefill_logits: too long");
+    Session tmp;
+    if (!ensure_pages(e, &tmp, n)) { set_last_error("ft_debug_prefill_logits: out of KV pages"); return -3; }
+    StepMeta& m = e->meta;
+    int* hh = m.h;
+    int rc = 0;
+    for (int p0 = 0; p0 < n && rc == 0; p0 += chunk) {
+        const int len = std::min(chunk, n - p0);
+        Batch b;
+        b.n_decode = 0; b.T = len; b.n_req = 1; b.n_prefill_req = 1; b.n_logit_rows = len;
+        layout_step(m, 1, e->max_pages, len);
+        for (int k = 0; k < len; ++k) {
+            hh[m.o_tokens + k] = tokens[p0 + k];
+            hh[m.o_pos + k] = p0 + k;
+            hh[m.o_rows + k] = 0;
+            hh[m.o_lrow + k] = k;
+        }
+        hh[m.o_qstart] = 0; hh[m.o_qstart + 1] = len;
+        hh[m.o_rslot] = 0; hh[m.o_rpos0] = p0;
+        for (size_t p = 0; p < tmp.pages.size(); ++p) hh[m.o_pt + p] = tmp.pages[p];
+        int tiles = 0;
+        for (int q0 = 0; q0 < len; q0 += 64, ++tiles) { hh[m.o_treq + tiles] = 0; hh[m.o_tq0 + tiles] = q0; }
+        b.n_tiles = tiles;
+        rc = upload_meta(e);
+        if (!rc) rc = forward(e, b);
+        if (!rc && cudaMemcpyAsync(host_out + (size_t)p0 * e->cfg.vocab, e->logits, (size_t)len * e->cfg.vocab * 4,
+                                   cudaMemcpyDeviceToHost, e->stream) != cudaSuccess) {
+            set_last_error("ft_debug_prefill_logits: logits copy failed");
+            rc = -1;
+        }
+        if (!rc && cudaStreamSynchronize(e->stream) != cudaSuccess) {
+            set_last_error("ft_debug_prefill_logits: %s", cudaGetErrorString(cudaGetLastError()));
+            rc = -1;
+        }
+    }
+    release_pages_beyond(e, &tmp, 0);
+    return rc;
+}

@@ -1,0 +1,50 @@
+// Internal (C++) declarations shared by the .cu translation units.  The public C ABI is
+// include/fasttalk_b200.h.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ft {
+
+constexpr int GEMM_MAX_SPLITS = 16;
+
+// ---- gemm.cu
+int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int box_rows);
+int gemm_pick_bn(int T);
+int gemm_pick_splits(int n_out, int T, int K, int num_sms);
+int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, int bn, void* out, int n_out, int T,
+                int K, int splits, int out_mode, bool pdl, cudaStream_t stream);
+
+// ---- elementwise.cu
+int launch_add_rmsnorm(float* resid, const float* partials, int n_splits, size_t split_stride,
+                       const int* embed_tokens, const void* embed_table, const void* norm_w,
+                       void* xn_out, const int* row_idx, int T, int h, float eps, bool pdl,
+                       cudaStream_t stream);
+int launch_rope_kv_append(const float* qkv, int n_splits, size_t split_stride, const float* cos_t,
+                          const float* sin_t, const int* positions, const int* seq_slots,
+                          const int* page_table, int max_pages, void* q_out, void* kv_layer, int T,
+                          int nq, int nkv, int d, bool pdl, cudaStream_t stream);
+int launch_silu_mul(const float* gu, int n_splits, size_t split_stride, void* act, int T, int f,
+                    bool pdl, cudaStream_t stream);
+
+// ---- attention.cu
+size_t attn_decode_scratch_floats(int B, int nkv, int group, int d, int n_ctas);
+int attn_decode_ctas_per_sm(int d);      // resident CTAs of the decode kernel per SM (<= 0: error)
+const char* last_error();
+int launch_attn_decode_plan(const int* ctx_lens, int* tile_prefix, int B, bool pdl,
+                            cudaStream_t stream);
+int launch_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                       const int* ctx_lens, const int* tile_prefix, void* out, float* scratch, int B,
+                       int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream);
+int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                        const int* req_q_start, const int* req_slot, const int* req_pos0,
+                        const int* tile_req, const int* tile_q0, int n_tiles, void* out, int nq,
+                        int nkv, int d, bool pdl, cudaStream_t stream);
+
+// ---- sampling.cu
+int launch_sample(const float* logits, int B, int V, const float* temperature, const int* top_k,
+                  const float* top_p, const unsigned long long* seeds, int* out_tokens, bool pdl,
+                  cudaStream_t stream);
+
+}  // namespace ft

@@ -1,0 +1,138 @@
+"""torch-tensor front ends of the kernel-level C ABI (include/fasttalk_b200.h).  PyTorch only
+supplies device memory and the stream; all arithmetic happens in the CUDA library."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import native as N
+
+KV_TILE = 64
+
+
+def _chk_bf16(t, name):
+    assert t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous(), f"{name}: need contiguous CUDA bf16"
+
+
+def gemm_bf16(w: torch.Tensor, x: torch.Tensor, n_splits: int = 0, out_bf16: bool = False) -> torch.Tensor:
+    """Y[t, n] = sum_k X[t, k] W[n, k].  Returns fp32 partials [S, T, n_out] or bf16 [T, n_out]."""
+    _chk_bf16(w, "w"); _chk_bf16(x, "x")
+    n_out, K = w.shape
+    T = x.shape[0]
+    assert x.shape[1] == K
+    lib = N.load()
+    if out_bf16:
+        out = torch.empty(T, n_out, device=x.device, dtype=torch.bfloat16)
+        N.check(lib.ft_gemm_bf16(N.ptr(w), N.ptr(x), N.ptr(out), n_out, T, K, 1, 1, N.cur_stream()), "ft_gemm_bf16")
+        return out
+    if n_splits <= 0:
+        n_splits = lib.ft_gemm_pick_splits(n_out, T, K)
+    out = torch.empty(n_splits, T, n_out, device=x.device, dtype=torch.float32)
+    N.check(lib.ft_gemm_bf16(N.ptr(w), N.ptr(x), N.ptr(out), n_out, T, K, n_splits, 0, N.cur_stream()), "ft_gemm_bf16")
+    return out
+
+
+def add_rmsnorm(resid: torch.Tensor, norm_w: torch.Tensor, eps: float, partials: Optional[torch.Tensor] = None,
+                embed_tokens: Optional[torch.Tensor] = None, embed_table: Optional[torch.Tensor] = None,
+                row_idx: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """In-place residual update + RMSNorm; returns bf16 xn [n_rows, h]."""
+    assert resid.dtype == torch.float32 and resid.is_contiguous()
+    h = resid.shape[1]
+    T = row_idx.numel() if row_idx is not None else resid.shape[0]
+    xn = torch.empty(T, h, device=resid.device, dtype=torch.bfloat16)
+    ns, stride = 0, 0
+    if partials is not None:
+        assert partials.dtype == torch.float32 and partials.is_contiguous()
+        ns, stride = partials.shape[0], partials.stride(0)
+    N.check(N.load().ft_add_rmsnorm(N.ptr(resid), N.ptr(partials), ns, stride, N.ptr(embed_tokens),
+                                    N.ptr(embed_table), N.ptr(norm_w), N.ptr(xn), N.ptr(row_idx), T, h,
+                                    eps, N.cur_stream()), "ft_add_rmsnorm")
+    return xn
+
+
+def kv_cache_alloc(num_pages: int, nkv: int, d: int, device) -> torch.Tensor:
+    """One layer of paged KV cache: [page][kv_head][K|V][64][d] bf16 (swizzled rows)."""
+    return torch.zeros(num_pages, nkv, 2, KV_TILE, d, device=device, dtype=torch.bfloat16)
+
+
+def rope_kv_append(qkv_partials: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, positions: torch.Tensor,
+                   seq_rows: torch.Tensor, page_table: torch.Tensor, kv_layer: torch.Tensor,
+                   nq: int, nkv: int, d: int) -> torch.Tensor:
+    S, T, _ = qkv_partials.shape
+    q = torch.empty(T, nq, d, device=qkv_partials.device, dtype=torch.bfloat16)
+    N.check(N.load().ft_rope_kv_append(N.ptr(qkv_partials), S, qkv_partials.stride(0), N.ptr(cos), N.ptr(sin),
+                                       N.ptr(positions), N.ptr(seq_rows), N.ptr(page_table),
+                                       page_table.shape[1], N.ptr(q), N.ptr(kv_layer), T, nq, nkv, d,
+                                       N.cur_stream()), "ft_rope_kv_append")
+    return q
+
+
+def silu_mul(gu_partials: torch.Tensor) -> torch.Tensor:
+    S, T, f2 = gu_partials.shape
+    act = torch.empty(T, f2 // 2, device=gu_partials.device, dtype=torch.bfloat16)
+    N.check(N.load().ft_silu_mul(N.ptr(gu_partials), S, gu_partials.stride(0), N.ptr(act), T, f2 // 2,
+                                 N.cur_stream()), "ft_silu_mul")
+    return act
+
+
+def attn_decode(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tensor, ctx_lens: torch.Tensor,
+                n_ctas: int = 0) -> torch.Tensor:
+    """q bf16 [B, nq, d] -> bf16 [B, nq*d]."""
+    B, nq, d = q.shape
+    nkv = kv_layer.shape[1]
+    lib = N.load()
+    if n_ctas <= 0:
+        n_ctas = N.check(lib.ft_attn_decode_default_ctas(d), "ft_attn_decode_default_ctas")
+    scratch = torch.empty(lib.ft_attn_decode_scratch_bytes(B, nkv, nq // nkv, d, n_ctas) // 4,
+                          device=q.device, dtype=torch.float32)
+    tile_prefix = torch.empty(B + 1, device=q.device, dtype=torch.int32)
+    out = torch.empty(B, nq * d, device=q.device, dtype=torch.bfloat16)
+    N.check(lib.ft_attn_decode(N.ptr(q), N.ptr(kv_layer), N.ptr(page_table), page_table.shape[1],
+                               N.ptr(ctx_lens), N.ptr(tile_prefix), N.ptr(out), N.ptr(scratch), B, nq, nkv, d,
+                               n_ctas, N.cur_stream()), "ft_attn_decode")
+    return out
+
+
+def attn_prefill(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tensor, req_q_start, req_slot,
+                 req_pos0) -> torch.Tensor:
+    """q bf16 [T, nq, d]; request r owns rows req_q_start[r]:req_q_start[r+1]."""
+    T, nq, d = q.shape
+    nkv = kv_layer.shape[1]
+    dev = q.device
+    tile_req, tile_q0 = [], []
+    for r in range(len(req_slot)):
+        for q0 in range(0, req_q_start[r + 1] - req_q_start[r], 64):
+            tile_req.append(r); tile_q0.append(q0)
+    i32 = lambda v: torch.tensor(v, device=dev, dtype=torch.int32)
+    t_qs, t_slot, t_pos0, t_treq, t_tq0 = i32(req_q_start), i32(req_slot), i32(req_pos0), i32(tile_req), i32(tile_q0)
+    out = torch.zeros(T, nq * d, device=dev, dtype=torch.bfloat16)
+    N.check(N.load().ft_attn_prefill(N.ptr(q), N.ptr(kv_layer), N.ptr(page_table), page_table.shape[1],
+                                     N.ptr(t_qs), N.ptr(t_slot), N.ptr(t_pos0), N.ptr(t_treq), N.ptr(t_tq0),
+                                     len(tile_req), N.ptr(out), nq, nkv, d, N.cur_stream()), "ft_attn_prefill")
+    return out
+
+
+def sample(logits: torch.Tensor, temperature=None, top_k=None, top_p=None, seeds=None) -> torch.Tensor:
+    B, V = logits.shape
+    assert logits.dtype == torch.float32 and logits.is_contiguous()
+    out = torch.empty(B, device=logits.device, dtype=torch.int32)
+    N.check(N.load().ft_sample(N.ptr(logits), B, V, N.ptr(temperature), N.ptr(top_k), N.ptr(top_p),
+                               N.ptr(seeds), N.ptr(out), N.cur_stream()), "ft_sample")
+    return out
+
+
+# ---- KV cache (un)swizzle helpers for tests: logical [tokens, d] <-> stored slab
+def kv_slab_logical(slab: torch.Tensor) -> torch.Tensor:
+    """slab [64, d] as stored -> logical [64, d] (undo the 16-byte chunk XOR swizzle)."""
+    rows, d = slab.shape
+    chunks = slab.reshape(rows, d // 8, 8)
+    r = torch.arange(rows, device=slab.device)[:, None]
+    c = torch.arange(d // 8, device=slab.device)[None, :]
+    src = c ^ (r & 7)
+    return torch.gather(chunks, 1, src[..., None].expand(-1, -1, 8)).reshape(rows, d)
+
+
+def kv_slab_store(logical: torch.Tensor) -> torch.Tensor:
+    """inverse of kv_slab_logical (the XOR is an involution)."""
+    return kv_slab_logical(logical)

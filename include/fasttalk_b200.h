@@ -1,0 +1,159 @@
+/* fasttalk_b200 — C ABI of the B200-native generation backend.
+ *
+ * The reference (Berkay2002/fasttalk-llm-microservice) has no FFI of its own: its hot path is
+ * an HTTP hop to Ollama (`app/core/ollama_handler.py:142-177`, POST /api/chat) or vLLM
+ * (`app/core/vllm_handler.py:177,271`, POST /v1/chat/completions).  This library replaces what
+ * sits behind that hop.  The Python class that binds it
+ * (`fasttalk_llm_microservice_b200/handler.py: NativeHandler`) duck-types
+ * `VLLMHandler` (`app/core/vllm_handler.py:24-338`) and `OllamaHandler`
+ * (`app/core/ollama_handler.py:24-458`); INTEGRATION.md shows the binding.
+ *
+ * Conventions: every function returns 0 (or a non-negative value where documented) on
+ * success and a negative value on error, with a message in ft_last_error() (thread local).
+ * No exceptions cross the ABI.  All `const void*` tensor arguments are DEVICE pointers to
+ * bf16 unless stated otherwise; `stream` is a cudaStream_t (0 = default stream).
+ * The library never falls back to the CPU.
+ */
+#ifndef FASTTALK_B200_H
+#define FASTTALK_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* ft_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Engine level — what replaces the engine behind `VLLMHandler.generate_stream_async`
+ * (vllm_handler.py:216-308) and `OllamaHandler.generate_stream` (ollama_handler.py:110-231):
+ * tokens in, sampled tokens out, continuous batching over concurrent sessions.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct ft_engine ft_engine;
+
+typedef struct {
+    int hidden, ffn, layers, n_q_heads, n_kv_heads, head_dim, vocab;
+    float rms_eps;
+    int max_batch;           /* sequences per step; vLLM --max-num-seqs (docker-compose.vllm.yml:47) */
+    int max_batched_tokens;  /* tokens per step; vLLM --max-num-batched-tokens (docker-compose.vllm.yml:48) */
+    int num_pages;           /* KV pages of 64 tokens */
+    int max_context;         /* context window in tokens; vLLM --max-model-len (docker-compose.vllm.yml:43) */
+    int max_sessions;        /* sessions whose KV may stay cached between turns */
+    int n_eos;
+    int eos_ids[4];          /* stop tokens (<|eot_id|> 128009, <|end_of_text|> 128001) */
+    int use_pdl;             /* programmatic dependent launch between the step's kernels */
+    int debug_logit_rows;    /* rows of the logits buffer (>= max_batch); more only for ft_debug_* */
+} ft_engine_config;
+
+typedef struct {
+    /* bf16, row-major [out, in]; per-layer tensors stacked on a leading L dimension */
+    const void* embed;       /* [vocab, hidden] */
+    const void* lm_head;     /* [vocab, hidden] (== embed when tied) */
+    const void* final_norm;  /* [hidden] */
+    const void* attn_norm;   /* [L, hidden] */
+    const void* wqkv;        /* [L, (nq + 2 nkv) * d, hidden]   rows: q | k | v */
+    const void* wo;          /* [L, hidden, nq * d] */
+    const void* mlp_norm;    /* [L, hidden] */
+    const void* wgu;         /* [L, 2 * ffn, hidden]            rows: gate | up */
+    const void* wd;          /* [L, hidden, ffn] */
+    const float* rope_cos;   /* fp32 [max_context, d/2] */
+    const float* rope_sin;   /* fp32 [max_context, d/2] */
+} ft_weights;
+
+typedef struct {
+    long long steps, decode_steps, prefill_tokens, decode_tokens, kernel_launches;
+    long long prefix_hit_tokens;      /* prompt tokens served from a session's cached KV */
+    int active_requests, waiting_requests, live_sessions, free_pages, total_pages;
+    int last_batch, last_prefill_tokens;
+    double last_step_ms;              /* host wall time of the last ft_engine_step */
+} ft_engine_stats;
+
+/* Weights stay owned by the caller and must outlive the engine. */
+ft_engine* ft_engine_create(const ft_engine_config* cfg, const ft_weights* w);
+void ft_engine_destroy(ft_engine* e);
+
+/* Queue one generation.  `tokens` is a HOST array: the whole templated conversation so far
+ * (the reference re-sends the full history every turn, conversation_manager.py:54-56).
+ * `session_key` identifies the conversation (the reference's request_id == session id,
+ * websocket_server_vllm.py:528-534); the longest common prefix with the KV cached for that key
+ * is reused and only the remainder is prefilled.  temperature <= 0 means greedy.
+ * top_k <= 0 and top_p >= 1 disable those filters.  Returns a request id >= 0. */
+long long ft_engine_submit(ft_engine* e, unsigned long long session_key, const int* tokens, int n_tokens,
+                           float temperature, int top_k, float top_p, int max_new_tokens,
+                           unsigned long long seed, int ignore_eos);
+
+/* One continuous-batching iteration (admit -> chunked prefill + decode -> sample).  Blocks until
+ * the step's tokens are on the host.  Returns the number of tokens produced (0 = idle). */
+int ft_engine_step(ft_engine* e);
+
+/* Drain the tokens produced since the last drain, over all requests: parallel HOST arrays of
+ * (request id, token, finish flag: 0 running, 1 stop token, 2 length, 3 cancelled, 4 error).
+ * Returns the number of entries written (<= cap). */
+int ft_engine_drain(ft_engine* e, long long* req_ids, int* tokens, int* finish, int cap);
+
+/* The reference's cancel_generation (vllm_handler.py:310-326).  Frees the batch slot; the
+ * session's KV stays cached. */
+int ft_engine_cancel(ft_engine* e, long long req);
+/* Forget a session and free its KV pages (session end / disconnect). */
+int ft_engine_session_close(ft_engine* e, unsigned long long session_key);
+int ft_engine_stats_get(ft_engine* e, ft_engine_stats* out);
+/* fp32 logits [vocab] of `req` from the most recent step it took part in -> HOST buffer. */
+int ft_engine_get_logits(ft_engine* e, long long req, float* host_out);
+/* Test hook: teacher-forced logits of every position of `tokens` (chunked prefill with chunk
+ * `chunk` tokens through the same kernels) -> HOST fp32 [n_tokens, vocab].  Engine must be idle. */
+int ft_debug_prefill_logits(ft_engine* e, const int* tokens, int n_tokens, int chunk, float* host_out);
+
+/* ------------------------------------------------------------------------------------------
+ * Kernel level — one entry point per kernel so each can be checked against the oracle.
+ * ---------------------------------------------------------------------------------------- */
+
+/* K3: Y[t, n] = sum_k X[t, k] W[n, k]  (tcgen05/TMEM, TMA-fed).  out_mode 0: fp32 partial sums
+ * out[split][T][n_out] (n_splits <= 0 picks a split count; ft_gemm_pick_splits tells which);
+ * out_mode 1: bf16 out[T][n_out].  n_out % 128 == 0, K % 64 == 0. */
+int ft_gemm_bf16(const void* w, const void* x, void* out, int n_out, int T, int K, int n_splits,
+                 int out_mode, void* stream);
+int ft_gemm_pick_splits(int n_out, int T, int K);
+
+/* K1+K2: resid[r] (fp32) = embed[token[r]]  or  resid[r] += sum_s partials[s][r];
+ * xn[i] = bf16(rmsnorm(resid[r]) * w), r = row_idx ? row_idx[i] : i. */
+int ft_add_rmsnorm(float* resid, const float* partials, int n_splits, long long split_stride,
+                   const int* embed_tokens, const void* embed_table, const void* norm_w, void* xn_out,
+                   const int* row_idx, int T, int h, float eps, void* stream);
+
+/* K4: split-K reduce of the fused QKV projection, RoPE on q and k (cos/sin tables fp32
+ * [pos][d/2]), q -> bf16 [T][nq][d], k/v -> paged cache layer
+ * [page][kv_head][K|V][64][d] bf16 with XOR-swizzled 16-byte chunks. */
+int ft_rope_kv_append(const float* qkv, int n_splits, long long split_stride, const float* cos_t,
+                      const float* sin_t, const int* positions, const int* seq_rows,
+                      const int* page_table, int max_pages, void* q_out, void* kv_layer, int T, int nq,
+                      int nkv, int d, void* stream);
+
+/* SwiGLU: act[t][j] = bf16(silu(sum_s gu[s][t][j]) * sum_s gu[s][t][f+j]). */
+int ft_silu_mul(const float* gu, int n_splits, long long split_stride, void* act, int T, int f, void* stream);
+
+/* K5: paged GQA decode attention, one query token per sequence.  q bf16 [B][nq][d],
+ * out bf16 [B][nq*d].  `tile_prefix` (int32 [B+1]) and `scratch`
+ * (ft_attn_decode_scratch_bytes) are device work buffers the call fills. */
+long long ft_attn_decode_scratch_bytes(int B, int nkv, int group, int d, int n_ctas);
+/* persistent grid size the engine uses: SM count x resident CTAs of the decode kernel */
+int ft_attn_decode_default_ctas(int d);
+int ft_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                   const int* ctx_lens, int* tile_prefix, void* out, float* scratch, int B, int nq, int nkv,
+                   int d, int n_ctas, void* stream);
+
+/* K6: causal chunked-prefill attention over the paged cache.  Request r owns query rows
+ * [req_q_start[r], req_q_start[r+1]) of q/out, page-table row req_slot[r], and its first query
+ * sits at absolute position req_pos0[r].  Tiles (tile_req, tile_q0) enumerate 64-query blocks. */
+int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                    const int* req_q_start, const int* req_slot, const int* req_pos0, const int* tile_req,
+                    const int* tile_q0, int n_tiles, void* out, int nq, int nkv, int d, void* stream);
+
+/* K7: per-row temperature / top-k / top-p sampling (argmax when temperature <= 0). */
+int ft_sample(const float* logits, int B, int V, const float* temperature, const int* top_k,
+              const float* top_p, const unsigned long long* seeds, int* out_tokens, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FASTTALK_B200_H */

@@ -49,8 +49,8 @@ def rope_cos_sin(spec, positions: torch.Tensor) -> Tuple[torch.Tensor, torch.Ten
     inv = rope_inv_freq(spec.head_dim, spec.rope_theta, spec.rope_factor,
                         spec.rope_low_freq_factor, spec.rope_high_freq_factor,
                         spec.rope_original_max_pos)
-    ang = torch.outer(positions.to(torch.float32), inv)      # [T, d/2]
-    return ang.cos(), ang.sin()
+    ang = torch.outer(positions.to(torch.float32).cpu(), inv)      # [T, d/2], always on the host
+    return ang.cos().to(positions.device), ang.sin().to(positions.device)
 
 
 def apply_rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:
@@ -76,8 +76,8 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, q_pos0: int) ->
     k = k.repeat_interleave(g, dim=1)
     v = v.repeat_interleave(g, dim=1)
     s = torch.einsum("qhd,khd->hqk", q, k) / math.sqrt(d)
-    qi = torch.arange(Tq)[:, None] + q_pos0
-    ki = torch.arange(Tk)[None, :]
+    qi = torch.arange(Tq, device=q.device)[:, None] + q_pos0
+    ki = torch.arange(Tk, device=q.device)[None, :]
     s = s.masked_fill((ki > qi)[None], float("-inf"))
     p = torch.softmax(s, dim=-1)
     return torch.einsum("hqk,khd->qhd", p, v).reshape(Tq, nq * d)
@@ -107,7 +107,9 @@ def forward(weights: Dict[str, torch.Tensor], spec, tokens: torch.Tensor,
     f32 = lambda t: t.to(torch.float32)
     T = tokens.numel()
     pos0 = state.len
-    cos, sin = rope_cos_sin(spec, torch.arange(pos0, pos0 + T))
+    dev = weights["embed"].device
+    tokens = tokens.to(dev)
+    cos, sin = rope_cos_sin(spec, torch.arange(pos0, pos0 + T, device=dev))
     x = f32(weights["embed"][tokens])
     for l in range(spec.layers):
         xn = rmsnorm(x, weights["attn_norm"][l], spec.rms_eps)
@@ -141,6 +143,7 @@ def greedy_generate(weights, spec, prompt: torch.Tensor, n_new: int,
         tok = int(torch.argmax(logits[0]))
         out.append(tok)
         logits = forward(weights, spec, torch.tensor([tok]), state, last_only=True)
+    all_logits = [l.cpu() for l in all_logits]
     if return_logits:
         return out, torch.stack(all_logits)
     return out
