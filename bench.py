@@ -1,0 +1,353 @@
+#!/usr/bin/env python
+"""bench.py — streamed tok/s of the B200-native generation backend on BASELINE.json's metric.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1]): Llama-3.2-1B bf16, 64 concurrent sessions per GPU,
+2k-token history, continuous batching.  A "step" is one decode step of the engine over the
+64-session batch at context ~2048 (one pass of the hot path over one batch).
+
+  value     K timed decode steps, CUDA events on the engine's stream, max over ranks;
+            KV cache and weights resident in HBM (the engine still uploads its ~2 KB of
+            per-step metadata and reads the 64 sampled token ids back every step).
+  e2e       one whole conversation turn per session through the public API
+            (Engine.submit / step / drain) with HOST token buffers: 64 sessions re-send a
+            ~2k-token history of which the last 224 tokens are new, prefill rides along with
+            decode (continuous batching), 32 tokens are generated per session; generated
+            tokens / wall time, with TTFT and inter-token latency percentiles.
+  roofline  the dominant kernel (paged decode attention): algorithmic KV bytes per launch /
+            its CUDA-event time, measured in a second pass over K more steps with events
+            around every launch (events break PDL overlap, so they stay out of `value`).
+  cpu_baseline / --impl reference   the oracle port of the same decode step on the host cores.
+
+N > 1: independent replicas (one engine + 64 sessions per GPU, no collective on the data
+path); torch.distributed only provides the barrier and the max-over-ranks reduction.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+MODEL = "llama-3.2-1b"
+SESSIONS = 64
+CTX = 2048
+TURN_NEW = 224          # new history tokens per turn (SURVEY.md §8d cfg 2)
+TURN_GEN = 32           # generated tokens per turn
+METRIC = "Llama-3.2-1B streamed tok/s at 64 sessions/GPU; p50 TTFT & inter-token latency"
+FALLBACK_HBM_GBS = 6650.0
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            with open(p) as fh:
+                return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index),
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            f = [x.strip() for x in s.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def pct(xs, q):
+    xs = sorted(xs)
+    return xs[min(len(xs) - 1, int(q * len(xs)))] if xs else None
+
+
+# ----------------------------------------------------------------------------- reference arm
+def run_reference(args, rank, world):
+    """The reference's CPU path (Ollama on host cores) cannot be installed here; this arm times
+    the oracle port of the same decode step on the host cores (oracle/cpu_baseline.py)."""
+    if rank != 0:
+        return
+    from fasttalk_llm_microservice_b200.model_spec import get_spec
+    from oracle import cpu_baseline as cb
+    spec = get_spec(MODEL)
+    budget_s = 150.0
+    batch = SESSIONS
+    wts = cb.make_weights(spec)
+    # bounded sample: the largest session count whose projected run fits the budget
+    for cand in (64, 16, 4, 1):
+        _, ms, _, _ = cb.run(spec, cand, CTX, 1, 1, weights=wts)
+        batch = cand
+        if ms * 1e-3 * (args.steps + args.warmup) <= budget_s:
+            break
+    tps, ms, cores, desc = cb.run(spec, batch, CTX, args.steps, args.warmup, weights=wts)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": tps, "unit": "tok/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{MODEL} decode step, {batch} of {SESSIONS} sessions at ctx {CTX} on host cores",
+                   "model": MODEL, "sessions": SESSIONS, "ctx": CTX},
+        "cpu_baseline": {"value": tps, "unit": "tok/s", "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": tps, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- our arm
+def run_native(args, rank, world, local_rank):
+    import torch
+    from fasttalk_llm_microservice_b200 import build
+    from fasttalk_llm_microservice_b200.engine import Engine, EngineLimits
+    from fasttalk_llm_microservice_b200.model_spec import get_spec
+    from fasttalk_llm_microservice_b200.weights import init_weights
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the native path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if rank == 0:
+        build.build()
+    if dist:
+        dist.barrier()
+    spec = get_spec(MODEL)
+    K, W = args.steps, args.warmup
+    w = init_weights(spec, seed=rank, device="cuda")
+    max_new_long = 2 * K + W + 96       # prefill steps + warm-up + timed pass + profiled pass
+    max_ctx = CTX + max_new_long + 128
+    eng = Engine(spec, w, EngineLimits(max_batch=SESSIONS, max_batched_tokens=8192, max_context=max_ctx),
+                 eos_ids=())
+    gens = [torch.Generator().manual_seed(1234 + rank * 1000 + i) for i in range(SESSIONS)]
+    rand_tokens = lambda i, n: torch.randint(0, 128000, (n,), generator=gens[i]).tolist()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if not dist:
+            return x
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- setup: 64 sessions prefilled to CTX tokens, all decoding (untimed)
+    hist = [rand_tokens(i, CTX) for i in range(SESSIONS)]
+    rids = [eng.submit(f"s{i}", hist[i], max_new_tokens=max_new_long, ignore_eos=True)
+            for i in range(SESSIONS)]
+    while eng.stats()["last_prefill_tokens"] > 0 or eng.stats()["steps"] == 0:
+        eng.step()
+    eng.drain()
+
+    # ---- value: K decode steps, CUDA events on the engine stream
+    for _ in range(W):
+        eng.step()
+    eng.drain()
+    st0 = eng.stats()
+    clocks = ClockSampler(local_rank)
+    barrier()
+    clocks.start()
+    eng.timer_start()
+    for _ in range(K):
+        eng.step()
+    ms = eng.timer_stop_ms()
+    barrier()
+    clk = clocks.stop()
+    st1 = eng.stats()
+    ms = max_over_ranks(ms)
+    tokens = st1["decode_tokens"] - st0["decode_tokens"]
+    assert tokens == SESSIONS * K, (tokens, SESSIONS, K)
+    value = world * tokens / (ms * 1e-3)
+    launches = st1["kernel_launches"] - st0["kernel_launches"]
+    ctx_tokens = st1["decode_ctx_tokens"] - st0["decode_ctx_tokens"]
+    step_bytes = spec.weight_bytes() + ctx_tokens / K * spec.kv_bytes_per_token()
+    peak, peak_src = measured_peaks()
+    step_achieved = step_bytes * K / (ms * 1e-3) / 1e9
+    eng.drain()
+
+    # ---- roofline of the dominant kernel: second pass, events around every launch
+    eng.set_profile(True)
+    p0 = eng.stats()
+    eng.timer_start()
+    for _ in range(K):
+        eng.step()
+    ms_prof = eng.timer_stop_ms()
+    p1 = eng.stats()
+    eng.set_profile(False)
+    eng.drain()
+    n_l = p1["attn_decode_launches"] - p0["attn_decode_launches"]
+    attn_ms = p1["attn_decode_ms"] - p0["attn_decode_ms"]
+    kv_tok = p1["attn_decode_kv_tokens"] - p0["attn_decode_kv_tokens"]
+    layer_kv_bytes = spec.kv_bytes_per_token() // spec.layers
+    attn_bytes_per_launch = kv_tok / max(n_l, 1) * layer_kv_bytes
+    attn_achieved = attn_bytes_per_launch / (attn_ms / max(n_l, 1) * 1e-3) / 1e9 if attn_ms > 0 else 0.0
+
+    # ---- finish the long requests, then e2e: one whole turn per session through the public API
+    for r in rids:
+        eng.cancel(r)
+    eng.step(); eng.drain()
+    # warm the sessions with a known history (prefix reuse needs the cached tokens == re-sent prefix)
+    for i in range(SESSIONS):
+        eng.close_session(f"s{i}")
+    base = [rand_tokens(i, CTX - TURN_NEW) for i in range(SESSIONS)]
+    rr = [eng.submit(f"t{i}", base[i], max_new_tokens=1, ignore_eos=True) for i in range(SESSIONS)]
+    live = set(rr)
+    while live:
+        eng.step()
+        for r, t, fin in eng.drain():
+            if fin:
+                live.discard(r)
+    e0 = eng.stats()
+    barrier()
+    t_start = time.perf_counter()
+    rid_of, first, last, gaps, n_out = {}, {}, {}, [], 0
+    for i in range(SESSIONS):          # host token buffers in; the engine uploads what it needs
+        full = base[i] + rand_tokens(i, TURN_NEW)
+        rid_of[eng.submit(f"t{i}", full, max_new_tokens=TURN_GEN, ignore_eos=True)] = i
+    live = set(rid_of)
+    while live:
+        eng.step()
+        now = time.perf_counter()
+        n, rq, tk, fn = eng.drain_arrays()
+        for j in range(n):
+            r = int(rq[j])
+            if int(tk[j]) >= 0:
+                n_out += 1
+                if r in last:
+                    gaps.append(now - last[r])
+                else:
+                    first[r] = now - t_start
+                last[r] = now
+            if int(fn[j]):
+                live.discard(r)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t_start
+    e2e_s = max_over_ranks(e2e_s)
+    e1 = eng.stats()
+    e_steps = e1["steps"] - e0["steps"]
+    e2e_value = world * n_out / e2e_s
+
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import cpu_baseline as cb
+        wts = cb.make_weights(spec)
+        _, ms1, _, _ = cb.run(spec, SESSIONS, CTX, 1, 1, weights=wts)
+        n_cpu = max(2, min(20, int(15000 / max(ms1, 1))))
+        tps, cms, cores, desc = cb.run(spec, SESSIONS, CTX, n_cpu, 1, weights=wts)
+        cpu_base = {"value": tps, "unit": "tok/s", "cores": cores, "kind": "port", "sample": desc,
+                    "ms_per_step": cms}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"{MODEL} bf16, {SESSIONS} sessions/GPU decoding at ctx {CTX}..{CTX + K + W}, "
+                                   "continuous batching (BASELINE configs[1])",
+                       "model": MODEL, "sessions_per_gpu": SESSIONS, "ctx": CTX, "parallelism": f"replicas x{world}",
+                       "l2": "no flush needed: each step streams 6.8 GB >> 126 MB L2",
+                       "weights": "random-init (seed per rank, std 0.02)", "sampling": "greedy, EOS ignored"},
+            "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel<64>", "achieved": attn_achieved, "peak": peak,
+                         "unit": "GB/s", "frac": attn_achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "launches_timed": n_l, "bytes_per_launch": attn_bytes_per_launch,
+                         "us_per_launch": 1e3 * attn_ms / max(n_l, 1),
+                         "pass": "second pass of K steps with CUDA events around each launch",
+                         "ms_per_step_profiled": ms_prof / K},
+            "step_roofline": {"bound": "hbm", "bytes_per_step": step_bytes, "achieved": step_achieved, "peak": peak,
+                              "unit": "GB/s", "frac": step_achieved / peak,
+                              "note": "whole decode step: weights + KV bytes (SURVEY.md §8d) / device time"},
+            "cpu_baseline": cpu_base,
+            "e2e": {"value": e2e_value, "unit": "tok/s",
+                    "h2d_bytes_per_step": (e1["h2d_bytes"] - e0["h2d_bytes"]) / max(e_steps, 1),
+                    "d2h_bytes_per_step": (e1["d2h_bytes"] - e0["d2h_bytes"]) / max(e_steps, 1),
+                    "what": f"one turn/session via Engine.submit/step/drain with host token lists: "
+                            f"{CTX}-token history ({TURN_NEW} new, rest prefix-cached), {TURN_GEN} generated",
+                    "steps": e_steps, "wall_s": e2e_s, "tokens": n_out,
+                    "ttft_ms_p50": 1e3 * pct(list(first.values()), 0.5), "ttft_ms_p99": 1e3 * pct(list(first.values()), 0.99),
+                    "itl_ms_p50": 1e3 * pct(gaps, 0.5), "itl_ms_p99": 1e3 * pct(gaps, 0.99),
+                    "prefix_hit_tokens": e1["prefix_hit_tokens"] - e0["prefix_hit_tokens"]},
+            "latency": {"itl_ms_p50_decode": ms / K},
+            "gpu_launches": launches,
+            "clocks": clk,
+        }
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if dist:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under it so `python bench.py --gpus N` works too
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29531", os.path.abspath(__file__),
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)]
+        raise SystemExit(subprocess.call(cmd))
+    run_native(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -541,7 +541,8 @@ int launch_attn_decode_plan(const int* ctx_lens, int* tile_prefix, int B, bool p
 template <int D>
 static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                                 const int* ctx_lens, const int* tile_prefix, void* out, float* scratch,
-                                int B, int nq, int nkv, int n_ctas, bool pdl, cudaStream_t stream) {
+                                int B, int nq, int nkv, int n_ctas, bool pdl, cudaStream_t stream,
+                                cudaEvent_t ev0, cudaEvent_t ev1) {
     using C = AttnCfg<D>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -552,10 +553,12 @@ static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* 
     const float scale_log2 = LOG2E / sqrtf((float)D);
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
-    fill_cfg(cfg, attr, dim3(n_ctas), dim3(ATTN_THREADS), C::SMEM, pdl, stream);
+    fill_cfg(cfg, attr, dim3(n_ctas), dim3(ATTN_THREADS), C::SMEM, pdl && !ev0, stream);
+    if (ev0) FT_CHECK_CUDA(cudaEventRecord(ev0, stream));
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_kernel<D>, (const __nv_bfloat16*)q,
                                      (const uint8_t*)kv_layer, page_table, max_pages, ctx_lens, tile_prefix,
                                      (__nv_bfloat16*)out, scratch, B, nq, nkv, scale_log2));
+    if (ev1) FT_CHECK_CUDA(cudaEventRecord(ev1, stream));
     fill_cfg(cfg, attr, dim3(B * nkv), dim3(128), 0, pdl, stream);
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_merge_kernel<D>, tile_prefix, (const float*)scratch,
                                      (__nv_bfloat16*)out, B, nq, nkv, n_ctas));
@@ -564,15 +567,16 @@ static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* 
 
 int launch_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                        const int* ctx_lens, const int* tile_prefix, void* out, float* scratch, int B,
-                       int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream) {
+                       int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream, cudaEvent_t ev0,
+                       cudaEvent_t ev1) {
     FT_REQUIRE(d == 64 || d == 128, "attn_decode: head_dim %d not supported (64 or 128)", d);
     FT_REQUIRE(nq % nkv == 0 && nq / nkv <= ATTN_GMAX, "attn_decode: GQA group %d/%d not supported", nq, nkv);
     FT_REQUIRE(B >= 1 && n_ctas >= 1, "attn_decode: B=%d n_ctas=%d", B, n_ctas);
     if (d == 64)
         return launch_attn_decode_d<64>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out,
-                                        scratch, B, nq, nkv, n_ctas, pdl, stream);
+                                        scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1);
     return launch_attn_decode_d<128>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, scratch,
-                                     B, nq, nkv, n_ctas, pdl, stream);
+                                     B, nq, nkv, n_ctas, pdl, stream, ev0, ev1);
 }
 
 template <int D>
@@ -635,7 +639,7 @@ extern "C" int ft_attn_decode(const void* q, const void* kv_layer, const int* pa
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (int r = ft::launch_attn_decode_plan(ctx_lens, tile_prefix, B, false, st)) return r;
     return ft::launch_attn_decode(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, scratch, B,
-                                  nq, nkv, d, n_ctas, false, st);
+                                  nq, nkv, d, n_ctas, false, st, nullptr, nullptr);
 }
 
 extern "C" int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,

@@ -101,6 +101,12 @@ struct Engine {
     long long next_req = 0, clock = 0;
     ft_engine_stats st = {};
     bool pdl = false;
+    // optional CUDA-event timing of the decode-attention kernel (bench roofline)
+    bool profile = false;
+    std::vector<cudaEvent_t> prof_ev;      // 2 per layer
+    int prof_used = 0;
+    long long prof_ctx_sum = 0;            // sum of context lengths of the step's decode rows
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
 };
 
 static int bn_index(int bn) { return bn == 16 ? 0 : bn == 32 ? 1 : bn == 64 ? 2 : bn == 128 ? 3 : 4; }
@@ -206,9 +212,15 @@ static int forward(Engine* e, const Batch& b) {
                                      c.n_q_heads, c.n_kv_heads, c.head_dim, e->pdl, e->stream));
         e->st.kernel_launches++;
         if (b.n_decode > 0) {
+            cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+            if (e->profile) {
+                ev0 = e->prof_ev[2 * l];
+                ev1 = e->prof_ev[2 * l + 1];
+                e->prof_used = l + 1;
+            }
             FT_TRY(launch_attn_decode(e->q, kv_l, d + m.o_pt, e->max_pages, d + m.o_ctx, d + m.o_tprefix,
                                       e->attn_out, e->attn_scratch, b.n_decode, c.n_q_heads, c.n_kv_heads,
-                                      c.head_dim, e->attn_ctas, e->pdl, e->stream));
+                                      c.head_dim, e->attn_ctas, e->pdl, e->stream, ev0, ev1));
             e->st.kernel_launches += 2;
         }
         if (b.n_tiles > 0) {
@@ -251,6 +263,7 @@ static int forward(Engine* e, const Batch& b) {
 static int upload_meta(Engine* e) {
     FT_CHECK_CUDA(cudaMemcpyAsync(e->meta.d, e->meta.h, e->meta.upload_ints * sizeof(int),
                                   cudaMemcpyHostToDevice, e->stream));
+    e->st.h2d_bytes += (long long)(e->meta.upload_ints * sizeof(int));
     return 0;
 }
 
@@ -326,6 +339,7 @@ static int engine_step(Engine* e) {
     }
 
     int row = 0, lrow = 0;
+    long long ctx_sum = 0;
     for (int i = 0; i < b.n_decode; ++i, ++row) {
         Request* r = dec[i];
         Session* s = r->sess;
@@ -334,10 +348,13 @@ static int engine_step(Engine* e) {
         h[m.o_pos + row] = pos;
         h[m.o_rows + row] = i;
         h[m.o_ctx + i] = pos + 1;
+        ctx_sum += pos + 1;
         for (size_t p = 0; p < s->pages.size(); ++p) h[m.o_pt + (size_t)i * e->max_pages + p] = s->pages[p];
         h[m.o_lrow + lrow] = row;
         r->logits_row = lrow++;
     }
+    e->prof_ctx_sum = ctx_sum;
+    e->st.decode_ctx_tokens += ctx_sum;
     int tiles = 0;
     h[m.o_qstart] = row;
     for (int j = 0; j < b.n_prefill_req; ++j) {
@@ -381,6 +398,7 @@ static int engine_step(Engine* e) {
     for (Request* r : dec) put_sampling(r);
     for (Request* r : pre) if (r->logits_row >= 0) put_sampling(r);
 
+    e->prof_used = 0;
     FT_TRY(upload_meta(e));
     FT_TRY(forward(e, b));
     if (b.n_logit_rows > 0) {
@@ -394,6 +412,15 @@ static int engine_step(Engine* e) {
                                       cudaMemcpyDeviceToHost, e->stream));
     }
     FT_CHECK_CUDA(cudaStreamSynchronize(e->stream));
+    e->st.d2h_bytes += (long long)b.n_logit_rows * sizeof(int);
+    for (int l = 0; l < e->prof_used; ++l) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e->prof_ev[2 * l], e->prof_ev[2 * l + 1]) == cudaSuccess) {
+            e->st.attn_decode_ms += ms;
+            e->st.attn_decode_launches++;
+            e->st.attn_decode_kv_tokens += b.n_decode > 0 ? e->prof_ctx_sum : 0;
+        }
+    }
 
     // ---- bookkeeping: the K/V of every token we just ran is now cached
     int produced = 0;
@@ -540,6 +567,10 @@ static int engine_init(Engine* e) {
         FT_TRY(make_tmap_bf16_k64(&e->m_act[i], e->act, (int)T, c.ffn, kBns[i]));
         FT_TRY(make_tmap_bf16_k64(&e->m_last[i], e->xn_last, (int)rows_last, c.hidden, kBns[i]));
     }
+    e->prof_ev.resize(2 * L);
+    for (auto& ev : e->prof_ev) FT_CHECK_CUDA(cudaEventCreate(&ev));
+    FT_CHECK_CUDA(cudaEventCreate(&e->t0));
+    FT_CHECK_CUDA(cudaEventCreate(&e->t1));
     e->free_pages.reserve(c.num_pages);
     for (int p = c.num_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
     e->st.total_pages = c.num_pages;
@@ -555,6 +586,9 @@ static void engine_free(Engine* e) {
     cudaFree(e->attn_out); cudaFree(e->act); cudaFree(e->xn_last); cudaFree(e->logits);
     cudaFree(e->attn_scratch); cudaFree(e->meta.d);
     if (e->meta.h) cudaFreeHost(e->meta.h);
+    for (auto ev : e->prof_ev) if (ev) cudaEventDestroy(ev);
+    if (e->t0) cudaEventDestroy(e->t0);
+    if (e->t1) cudaEventDestroy(e->t1);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -699,6 +733,29 @@ extern "C" int ft_engine_stats_get(ft_engine* h, ft_engine_stats* out) {
     e->st.live_sessions = (int)e->sessions.size();
     e->st.free_pages = (int)e->free_pages.size();
     *out = e->st;
+    return 0;
+}
+
+extern "C" int ft_engine_set_profile(ft_engine* h, int on) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e, "ft_engine_set_profile: null engine");
+    std::lock_guard<std::mutex> lk(e->mu);
+    e->profile = on != 0;
+    return 0;
+}
+
+extern "C" int ft_engine_timer(ft_engine* h, int stop, float* ms_out) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e, "ft_engine_timer: null engine");
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (!stop) {
+        FT_CHECK_CUDA(cudaEventRecord(e->t0, e->stream));
+        return 0;
+    }
+    FT_REQUIRE(ms_out, "ft_engine_timer: null output");
+    FT_CHECK_CUDA(cudaEventRecord(e->t1, e->stream));
+    FT_CHECK_CUDA(cudaEventSynchronize(e->t1));
+    FT_CHECK_CUDA(cudaEventElapsedTime(ms_out, e->t0, e->t1));
     return 0;
 }
 

@@ -141,6 +141,17 @@ class Engine:
         N.check(self.lib.ft_engine_stats_get(self._h, C.byref(st)), "ft_engine_stats_get")
         return {n: getattr(st, n) for n, _ in st._fields_}
 
+    def timer_start(self):
+        N.check(self.lib.ft_engine_timer(self._h, 0, None), "ft_engine_timer")
+
+    def timer_stop_ms(self) -> float:
+        ms = C.c_float(0)
+        N.check(self.lib.ft_engine_timer(self._h, 1, C.byref(ms)), "ft_engine_timer")
+        return float(ms.value)
+
+    def set_profile(self, on: bool):
+        N.check(self.lib.ft_engine_set_profile(self._h, int(on)), "ft_engine_set_profile")
+
     def logits(self, rid: int) -> torch.Tensor:
         out = np.empty(self.spec.vocab, dtype=np.float32)
         N.check(self.lib.ft_engine_get_logits(self._h, rid, out.ctypes.data), "ft_engine_get_logits")

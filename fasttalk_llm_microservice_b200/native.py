@@ -40,6 +40,9 @@ class EngineStats(C.Structure):
         ("steps", C.c_longlong), ("decode_steps", C.c_longlong), ("prefill_tokens", C.c_longlong),
         ("decode_tokens", C.c_longlong), ("kernel_launches", C.c_longlong),
         ("prefix_hit_tokens", C.c_longlong),
+        ("h2d_bytes", C.c_longlong), ("d2h_bytes", C.c_longlong), ("decode_ctx_tokens", C.c_longlong),
+        ("attn_decode_launches", C.c_longlong), ("attn_decode_kv_tokens", C.c_longlong),
+        ("attn_decode_ms", C.c_double),
         ("active_requests", C.c_int), ("waiting_requests", C.c_int), ("live_sessions", C.c_int),
         ("free_pages", C.c_int), ("total_pages", C.c_int), ("last_batch", C.c_int),
         ("last_prefill_tokens", C.c_int), ("last_step_ms", C.c_double),
@@ -59,6 +62,8 @@ SIGNATURES = {
     "ft_engine_session_close": (_I, [_VP, _ULL]),
     "ft_engine_stats_get": (_I, [_VP, C.POINTER(EngineStats)]),
     "ft_engine_get_logits": (_I, [_VP, _LL, _VP]),
+    "ft_engine_timer": (_I, [_VP, _I, _VP]),
+    "ft_engine_set_profile": (_I, [_VP, _I]),
     "ft_debug_prefill_logits": (_I, [_VP, _VP, _I, _I, _VP]),
     "ft_gemm_bf16": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
     "ft_gemm_pick_splits": (_I, [_I, _I, _I]),

@@ -64,6 +64,11 @@ typedef struct {
 typedef struct {
     long long steps, decode_steps, prefill_tokens, decode_tokens, kernel_launches;
     long long prefix_hit_tokens;      /* prompt tokens served from a session's cached KV */
+    long long h2d_bytes, d2h_bytes;   /* per-step metadata uploaded / sampled tokens read back */
+    long long decode_ctx_tokens;      /* sum over decode steps of the rows' context lengths */
+    long long attn_decode_launches;   /* decode-attention launches timed while profiling is on */
+    long long attn_decode_kv_tokens;  /* context tokens those launches streamed (per launch: one layer) */
+    double attn_decode_ms;            /* their summed CUDA-event time */
     int active_requests, waiting_requests, live_sessions, free_pages, total_pages;
     int last_batch, last_prefill_tokens;
     double last_step_ms;              /* host wall time of the last ft_engine_step */
@@ -98,6 +103,12 @@ int ft_engine_cancel(ft_engine* e, long long req);
 /* Forget a session and free its KV pages (session end / disconnect). */
 int ft_engine_session_close(ft_engine* e, unsigned long long session_key);
 int ft_engine_stats_get(ft_engine* e, ft_engine_stats* out);
+/* Measurement hooks (bench.py): CUDA events on the engine's own stream.  ft_engine_timer(e, 0, 0)
+ * records a start event; ft_engine_timer(e, 1, &ms) records a stop event, waits for it and returns
+ * the device time between the two.  With profiling on, every decode-attention launch is bracketed
+ * by events and accumulated into ft_engine_stats (this breaks PDL overlap around that kernel). */
+int ft_engine_timer(ft_engine* e, int stop, float* ms_out);
+int ft_engine_set_profile(ft_engine* e, int on);
 /* fp32 logits [vocab] of `req` from the most recent step it took part in -> HOST buffer. */
 int ft_engine_get_logits(ft_engine* e, long long req, float* host_out);
 /* Test hook: teacher-forced logits of every position of `tokens` (chunked prefill with chunk

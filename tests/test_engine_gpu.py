@@ -27,7 +27,36 @@ def make_engine(spec, w, **kw):
 
 
 def per_pos_rel(got, ref):
+    """north_star's "2e-2 relative": worst position of max|delta| / max|logit|."""
     return ((got - ref).abs().amax(-1) / ref.abs().amax(-1)).max().item()
+
+
+def describe_err(tag, got, ref):
+    e = (got - ref).abs().amax(-1) / ref.abs().amax(-1)
+    l2 = (got - ref).norm(dim=-1) / ref.norm(dim=-1)
+    print(f"\n[{tag}] logits rel err (max-norm) max {e.max():.3e} mean {e.mean():.3e}; "
+          f"L2-rel max {l2.max():.3e} mean {l2.mean():.3e}")
+
+
+def assert_greedy_parity(tag, out, ref_tokens, ref_logits):
+    """Greedy tokens must equal the fp32 oracle's.  Where they first differ, the oracle's own
+    top-1/top-2 margin must be inside the logit tolerance (a near-tie no bf16 path can
+    resolve) — anything else is a failure.  Tokens after a near-tie flip
+    follow a different history and are not compared."""
+    n = min(len(out), len(ref_tokens))
+    mism = [i for i in range(n) if out[i] != ref_tokens[i]]
+    print(f"\n[{tag}] greedy: {n} tokens, first mismatch {mism[0] if mism else None}, "
+          f"distinct oracle tokens {len(set(ref_tokens))}")
+    if not mism:
+        assert len(out) == len(ref_tokens)
+        return n
+    i = mism[0]
+    top2 = torch.topk(ref_logits[i], 2).values
+    margin = (top2[0] - top2[1]).item()
+    scale = ref_logits[i].abs().max().item()
+    print(f"[{tag}] step {i}: oracle margin {margin:.3e} = {margin / scale:.3e} of max|logit| (tol {LOGIT_TOL})")
+    assert margin < LOGIT_TOL * scale, f"{tag}: token {i} differs where the oracle's margin is decisive"
+    return i
 
 
 @pytest.fixture(scope="module", params=["tiny-d64", "tiny-d128"])
@@ -48,13 +77,18 @@ def test_prefill_logits_match_golden(tiny):
     gold = torch.from_numpy(g["logits"])
     for chunk in (64, 16, 7):
         got = eng.debug_prefill_logits(prompt, chunk=chunk)
+        describe_err(f"{spec.name} chunk {chunk}", got, gold)
         assert per_pos_rel(got, gold) < LOGIT_TOL, (chunk, per_pos_rel(got, gold))
 
 
 def test_greedy_matches_golden(tiny):
     spec, w, g, eng = tiny
-    out = eng.generate([g["prompt"].tolist()], max_new_tokens=len(g["greedy"]), ignore_eos=True)[0]
-    assert out == g["greedy"].tolist()
+    n = len(g["greedy"])
+    out = eng.generate([g["prompt"].tolist()], max_new_tokens=n, ignore_eos=True)[0]
+    with torch.no_grad():
+        ref_tokens, ref_logits = O.greedy_generate(w, spec, torch.from_numpy(g["prompt"]), n, return_logits=True)
+    assert ref_tokens == g["greedy"].tolist()
+    assert_greedy_parity(spec.name, out, ref_tokens, ref_logits)
 
 
 def test_long_prompt_chunked_and_decode_logits(tiny):
@@ -74,9 +108,10 @@ def test_long_prompt_chunked_and_decode_logits(tiny):
         for r, t, fin in eng.drain():
             toks.append(t)
             done = fin is not None
-    assert toks == ref_tokens
-    got = torch.stack(logits[:12])
-    assert per_pos_rel(got, ref_logits) < LOGIT_TOL
+    k = assert_greedy_parity(spec.name + " long", toks, ref_tokens, ref_logits)
+    got = torch.stack(logits[:k + 1]) if k < 12 else torch.stack(logits[:12])
+    describe_err(spec.name + " decode", got, ref_logits[:got.shape[0]])
+    assert per_pos_rel(got, ref_logits[:got.shape[0]]) < LOGIT_TOL
     assert eng.stats()["prefill_tokens"] >= 700
 
 
@@ -193,21 +228,11 @@ def test_llama1b_config1_greedy_and_logits(llama1b):
         ref_full = O.forward(w32, spec, prompt).cpu()
         ref_tokens, ref_logits = O.greedy_generate(w32, spec, prompt, 64, return_logits=True)
     got_full = eng.debug_prefill_logits(prompt.tolist(), chunk=128)
+    describe_err("1B cfg1 prefill", got_full, ref_full)
     err = per_pos_rel(got_full, ref_full)
     assert err < LOGIT_TOL, err
-
     out = eng.generate([prompt.tolist()], max_new_tokens=64, ignore_eos=True)[0]
-    mismatches = [i for i in range(64) if out[i] != ref_tokens[i]]
-    print(f"\n[1B cfg1] prefill logit rel err {err:.2e}; greedy mismatches at {mismatches}; "
-          f"distinct tokens {len(set(ref_tokens))}")
-    if mismatches:
-        i = mismatches[0]
-        top2 = torch.topk(ref_logits[i], 2).values
-        margin = (top2[0] - top2[1]).item()
-        scale = ref_logits[i].abs().max().item()
-        print(f"[1B cfg1] first mismatch at {i}: oracle margin {margin:.3e} vs tol {LOGIT_TOL * scale:.3e}")
-        assert margin < LOGIT_TOL * scale, "greedy token differs where the oracle's margin is decisive"
-    assert out[:mismatches[0]] == ref_tokens[:mismatches[0]] if mismatches else out == ref_tokens
+    assert_greedy_parity("1B cfg1", out, ref_tokens, ref_logits)
 
 
 def test_llama1b_batched_decode_matches_oracle_logits(llama1b):
