@@ -1,0 +1,212 @@
+"""Host logic of boundary A on CPU: tokenizer, chat template, NativeHandler streaming /
+cancel / stop / errors (engine replaced by tests/fake_engine.py), signature parity with the
+reference handlers, and the UNCHANGED reference WebSocket server driving NativeHandler."""
+import asyncio
+import inspect
+import os
+import sys
+
+import pytest
+
+from fasttalk_llm_microservice_b200.errors import LLMServiceError
+from fasttalk_llm_microservice_b200.handler import EngineRunner, NativeHandler
+from fasttalk_llm_microservice_b200.tokenizer import ByteTokenizer
+from tests.fake_engine import FakeEngine
+
+REF = os.environ.get("FASTTALK_REFERENCE_PATH", "/root/reference")
+HAVE_REF = os.path.exists(os.path.join(REF, "app", "core", "vllm_handler.py"))
+
+
+def make_handler(reply="Hello from the fake engine.", **kw):
+    tok = ByteTokenizer()
+    eng = FakeEngine(tok, reply, **kw)
+    h = NativeHandler(base_url="http://ignored/v1", model="llama3.2:1b", runner=EngineRunner(eng, tok))
+    return h, eng, tok
+
+
+# ------------------------------------------------------------------ tokenizer
+def test_byte_tokenizer_roundtrip_and_template():
+    tok = ByteTokenizer()
+    text = "héllo wörld ✓ 你好"
+    ids = tok.encode(text)
+    assert all(0 <= i < 256 for i in ids) and tok.decode(ids) == text
+    # ids >= 256 are a bijection with private-use code points: generated text re-encodes exactly
+    gen = [300, 65, 127999, 70000, 66, 128100]
+    s = tok.decode(gen)
+    assert tok.encode(s) == gen and len(s) == len(gen)
+    msgs = [{"role": "system", "content": "be brief"}, {"role": "user", "content": "hi"}]
+    t = tok.apply_chat_template(msgs)
+    assert t[0] == 128000 and t.count(128009) == 2 and t.count(128006) == 3
+    assert bytes(t[-2:]) == b"\n\n" and t[-3] == 128007
+    # a longer conversation keeps the earlier one as an exact token prefix (KV reuse relies on it)
+    t2 = tok.apply_chat_template(msgs + [{"role": "assistant", "content": s}, {"role": "user", "content": "more"}])
+    assert t2[:len(t)] == t
+    assert t2[len(t):len(t) + len(gen)] == gen
+
+
+def test_stream_decoder_multibyte():
+    tok = ByteTokenizer()
+    dec = tok.stream_decoder()
+    pieces = [dec.push(b) for b in "a✓b".encode()]
+    assert pieces == ["a", "", "", "✓", "b"]
+    assert dec.push(tok.eot) == ""
+    small = ByteTokenizer(1024)
+    assert small.eot == 1023 and small.decode(small.encode("ok")) == "ok"
+
+
+# ------------------------------------------------------------------ handler
+def test_sync_stream_one_chunk_per_token():
+    h, eng, tok = make_handler()
+    msgs = [{"role": "user", "content": "hi"}]
+    out = list(h.generate_stream(msgs, temperature=0.0, max_tokens=64, top_p=0.9, top_k=40, request_id="sess-1"))
+    assert "".join(out) == "Hello from the fake engine."
+    assert len(out) == len("Hello from the fake engine.")            # websocket_server_vllm.py:538 counts chunks
+    sess, tokens, kw = eng.submitted[0]
+    assert sess == "sess-1" and tokens == tok.apply_chat_template(msgs)
+    assert kw == dict(temperature=0.0, top_k=40, top_p=0.9, max_new_tokens=64)
+    assert h.get_active_requests() == {}
+
+
+def test_async_stream_concurrent_sessions():
+    h, eng, tok = make_handler(reply=lambda toks: f"reply-{len(toks)}")
+
+    async def one(i):
+        msgs = [{"role": "user", "content": "x" * i}]
+        return "".join([c async for c in h.generate_stream_async(msgs, max_tokens=50, request_id=f"s{i}")])
+
+    async def main():
+        return await asyncio.gather(*[one(i) for i in range(1, 9)])
+
+    outs = asyncio.run(main())
+    for i, o in enumerate(outs, start=1):
+        assert o == f"reply-{len(tok.apply_chat_template([{'role': 'user', 'content': 'x' * i}]))}"
+
+
+def test_max_tokens_and_stop_sequences():
+    h, eng, tok = make_handler(reply="one two three four")
+    assert "".join(h.generate_stream([{"role": "user", "content": "q"}], max_tokens=5)) == "one t"
+    assert "".join(h.generate_stream([{"role": "user", "content": "q"}], stop=["three"])) == "one two "
+    assert h.get_active_requests() == {}
+
+
+def test_cancel_and_generator_close_release_the_request():
+    h, eng, tok = make_handler(reply="x" * 1000)
+    gen = h.generate_stream([{"role": "user", "content": "q"}], request_id="c1")
+    assert next(gen) == "x"
+    assert list(h.get_active_requests()) == ["c1"]
+    assert h.cancel_generation("c1") is True
+    rest = list(gen)
+    assert len(rest) < 999 and h.get_active_requests() == {}
+    assert h.cancel_generation("c1") is False
+
+    async def disconnect():
+        agen = h.generate_stream_async([{"role": "user", "content": "q"}], request_id="c2")
+        assert await agen.__anext__() == "x"
+        await agen.aclose()                     # what a WebSocket disconnect does to the generator
+    asyncio.run(disconnect())
+    assert h.get_active_requests() == {} and not eng.reqs
+
+
+def test_errors_follow_the_reference_convention():
+    h, eng, tok = make_handler(max_context=32)
+    with pytest.raises(LLMServiceError) as ei:
+        list(h.generate_stream([{"role": "user", "content": "y" * 100}]))
+    d = ei.value.to_dict()
+    assert set(d) == {"message", "category", "severity", "recoverable", "retry_after"}
+
+    def boom(*a, **k):
+        raise RuntimeError("engine exploded")
+    eng.submit = boom
+    with pytest.raises(LLMServiceError) as ei:
+        list(h.generate_stream([{"role": "user", "content": "hi"}]))
+    assert ei.value.category.value == "processing" and ei.value.severity.value == "high"
+    assert h.check_connection() is True
+    info = h.get_model_info()
+    assert info["current_model"] == "llama3.2:1b" and info["models"] == ["llama3.2:1b"]
+
+
+# ------------------------------------------------------------------ against the reference itself
+@pytest.mark.skipif(not HAVE_REF, reason="reference checkout not on this box")
+def test_signature_parity_with_reference_handlers():
+    sys.path.insert(0, REF)
+    try:
+        from app.core.ollama_handler import OllamaHandler
+        from app.core.vllm_handler import VLLMHandler
+    finally:
+        sys.path.remove(REF)
+
+    def params(f):
+        return [p for p in inspect.signature(f).parameters if p != "self"]
+
+    for name in ("__init__", "generate_stream", "generate_stream_async", "check_connection", "get_model_info",
+                 "cancel_generation", "get_active_requests"):
+        theirs, ours = params(getattr(VLLMHandler, name)), params(getattr(NativeHandler, name))
+        assert set(theirs) <= set(ours), (name, theirs, ours)
+    for name in ("__init__", "generate_stream", "check_connection", "get_model_info", "cancel_generation",
+                 "get_active_requests", "cleanup_stale_requests", "close"):
+        theirs, ours = params(getattr(OllamaHandler, name)), params(getattr(NativeHandler, name))
+        assert set(theirs) <= set(ours), (name, theirs, ours)
+    assert inspect.isasyncgenfunction(NativeHandler.generate_stream_async)
+    assert inspect.isgeneratorfunction(NativeHandler.generate_stream)
+
+
+@pytest.mark.skipif(not HAVE_REF, reason="reference checkout not on this box")
+def test_unchanged_reference_server_drives_native_handler(monkeypatch):
+    """WebSocketLLMServer (websocket_server_vllm.py) is imported unmodified from the reference
+    checkout; only `app.core.vllm_handler.VLLMHandler` is swapped before construction."""
+    monkeypatch.syspath_prepend(REF)
+    monkeypatch.setenv("LLM_PROVIDER", "vllm")
+    monkeypatch.setenv("ENABLE_PYDANTIC_AI", "false")
+    monkeypatch.setenv("DEFAULT_TEMPERATURE", "0.0")
+    monkeypatch.setenv("DEFAULT_MAX_TOKENS", "64")
+    monkeypatch.setenv("LLM_MAX_CONNECTIONS", "64")
+    for m in [k for k in sys.modules if k == "app" or k.startswith("app.")]:
+        monkeypatch.delitem(sys.modules, m)
+    from starlette.testclient import TestClient
+    import app.core.vllm_handler as vh
+    from app.utils.config import Config
+
+    tok = ByteTokenizer()
+    eng = FakeEngine(tok, reply=lambda toks: f"echo {len(toks)} tokens")
+    runner = EngineRunner(eng, tok)
+    made = []
+
+    class Patched(NativeHandler):
+        def __init__(self, **kw):
+            super().__init__(runner=runner, **kw)
+            made.append(kw)
+
+    monkeypatch.setattr(vh, "VLLMHandler", Patched)
+    from app.core.websocket_server_vllm import WebSocketLLMServer
+    server = WebSocketLLMServer(Config())
+    assert set(made[0]) == {"base_url", "model", "api_key", "timeout"}
+    with TestClient(server.app) as client:
+        assert client.get("/health").status_code == 200
+        with client.websocket_connect("/ws/llm") as ws:
+            started = ws.receive_json()
+            assert started["type"] == "session_started"
+            sid = started["session_id"]
+            ws.send_json({"type": "start_session", "config": {"system_prompt": "be brief"}})
+            assert ws.receive_json()["type"] == "session_configured"
+            replies = []
+            for turn in ("hello", "and again"):
+                ws.send_json({"type": "user_message", "text": turn})
+                chunks = []
+                while True:
+                    msg = ws.receive_json()
+                    if msg["type"] == "token":
+                        chunks.append(msg["data"])
+                    else:
+                        break
+                assert msg["type"] == "response_complete", msg
+                assert msg["stats"]["tokens_generated"] == len(chunks)
+                replies.append("".join(chunks))
+            ws.send_json({"type": "end_session"})
+            assert ws.receive_json()["type"] == "session_ended"
+    # both turns reached the engine under the session id, with the default sampling knobs
+    assert [s for s, _, _ in eng.submitted] == [sid, sid]
+    t1, t2 = eng.submitted[0][1], eng.submitted[1][1]
+    assert replies[0] == f"echo {len(t1)} tokens"
+    # turn 2 re-sends the history: turn 1's prompt (minus the generation header) is its prefix
+    assert t2[:len(t1)] == t1
+    assert eng.submitted[0][2]["temperature"] == 0.0 and eng.submitted[0][2]["max_new_tokens"] == 64
