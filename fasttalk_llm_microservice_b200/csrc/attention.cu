@@ -9,7 +9,8 @@
 //
 // K5 decode: persistent CTAs, stream-K over the flattened (sequence, kv head, tile) list so
 // every CTA streams the same number of 64-token tiles no matter how ragged the batch is.
-// A (sequence, head) whose tiles span several CTAs is finished by attn_decode_merge.
+// A (sequence, head) whose tiles span several CTAs is finished inside the same launch by the
+// last of those CTAs to arrive (per-segment arrival counters in the scratch buffer).
 // The math is mma.sync m16n8k16 with the GQA group (<= 8 q heads) in the M rows: decode
 // attention is HBM-bound (SURVEY.md §8a' a'5), tensor throughput is irrelevant here and
 // tcgen05's minimum M of 64 would be 94 % padding.
@@ -73,9 +74,10 @@ __device__ __forceinline__ int find_seq(const int* __restrict__ tile_prefix, int
 }
 
 __global__ void attn_decode_plan_kernel(const int* __restrict__ ctx_lens, int* __restrict__ tile_prefix,
-                                        int B) {
+                                        int B, int* __restrict__ seg_counters, int n_counters) {
     pdl_wait();
     pdl_launch_dependents();
+    for (int i = threadIdx.x; i < n_counters; i += blockDim.x) seg_counters[i] = 0;
     if (threadIdx.x == 0) {
         int acc = 0;
         tile_prefix[0] = 0;
@@ -91,6 +93,7 @@ __global__ void __launch_bounds__(ATTN_THREADS)
 attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restrict__ kv_layer,
                    const int* __restrict__ page_table, int max_pages, const int* __restrict__ ctx_lens,
                    const int* __restrict__ tile_prefix, __nv_bfloat16* __restrict__ out,
+                   __nv_bfloat16* __restrict__ out_lo, int* __restrict__ seg_counters,
                    float* __restrict__ scratch, int B, int nq, int nkv, float scale_log2) {
     using C = AttnCfg<D>;
     extern __shared__ uint8_t smem_raw[];
@@ -98,6 +101,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)C::STAGES * C::TILE_BYTES);
     uint64_t* empty_bar = full_bar + C::STAGES;
     float* merge_buf = reinterpret_cast<float*>(empty_bar + C::STAGES);
+    __shared__ int s_last;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -253,6 +257,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
         const bool whole = seg.tile_begin == 0 && seg.tile_end == seg.tiles_b;
         const int seg_idx = seg.b * nkv + seg.h;
         float* part = scratch + (size_t)(cta_slot + seg_idx) * ATTN_GMAX * C::REC;
+        const size_t out_row = ((size_t)seg.b * nq + (size_t)seg.h * G) * D;
         for (int e = threadIdx.x; e < G * D; e += ATTN_COMPUTE_WARPS * 32) {
             const int hg = e / D, dim = e % D;
             float mw[ATTN_COMPUTE_WARPS], M = -INFINITY;
@@ -271,48 +276,51 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                 O += rec[dim] * sc;
             }
             if (whole) {
-                out[((size_t)seg.b * nq + (size_t)seg.h * G + hg) * D + dim] = __float2bfloat16(O / L);
+                const float r = O / L;
+                const __nv_bfloat16 hb = __float2bfloat16(r);
+                out[out_row + e] = hb;
+                if (out_lo) out_lo[out_row + e] = __float2bfloat16(r - __bfloat162float(hb));
             } else {
                 part[(size_t)hg * C::REC + dim] = O;
                 if (dim == 0) { part[(size_t)hg * C::REC + D] = M; part[(size_t)hg * C::REC + D + 1] = L; }
             }
         }
-        compute_bar_sync();
-    }
-}
-
-// Finish the (sequence, head) pairs whose tiles were split over several CTAs.
-template <int D>
-__global__ void __launch_bounds__(128)
-attn_decode_merge_kernel(const int* __restrict__ tile_prefix, const float* __restrict__ scratch,
-                         __nv_bfloat16* __restrict__ out, int B, int nq, int nkv, int n_ctas) {
-    using C = AttnCfg<D>;
-    pdl_wait();
-    pdl_launch_dependents();
-    const int seg_idx = blockIdx.x;
-    const int b = seg_idx / nkv, h = seg_idx % nkv;
-    const int G = nq / nkv;
-    const int tiles_b = tile_prefix[b + 1] - tile_prefix[b];
-    if (tiles_b == 0) return;
-    const long long total = (long long)tile_prefix[B] * nkv;
-    const long long per = (total + n_ctas - 1) / n_ctas;
-    const long long F0 = (long long)tile_prefix[b] * nkv + (long long)h * tiles_b;
-    const int c_first = (int)(F0 / per), c_last = (int)((F0 + tiles_b - 1) / per);
-    if (c_first == c_last) return;          // the attention CTA already wrote the final output
-    for (int e = threadIdx.x; e < G * D; e += blockDim.x) {
-        const int hg = e / D, dim = e % D;
-        float M = -INFINITY;
-        for (int c = c_first; c <= c_last; ++c)
-            M = fmaxf(M, scratch[((size_t)(c + seg_idx) * ATTN_GMAX + hg) * C::REC + D]);
-        const float Mu = M == -INFINITY ? 0.f : M;
-        float L = 0.f, O = 0.f;
-        for (int c = c_first; c <= c_last; ++c) {
-            const float* rec = scratch + ((size_t)(c + seg_idx) * ATTN_GMAX + hg) * C::REC;
-            const float sc = exp2f(rec[D] - Mu);
-            L += rec[D + 1] * sc;
-            O += rec[dim] * sc;
+        if (!whole) {
+            // The last CTA to deliver a part of this (sequence, head) merges all of them.
+            const long long F0 = (long long)tile_prefix[seg.b] * nkv + (long long)seg.h * seg.tiles_b;
+            const int c_first = (int)(F0 / per), c_last = (int)((F0 + seg.tiles_b - 1) / per);
+            __threadfence();
+            compute_bar_sync();
+            if (threadIdx.x == 0) {
+                const int old = atomicAdd(&seg_counters[seg_idx], 1);
+                const int last = old == c_last - c_first;
+                if (last) seg_counters[seg_idx] = 0;      // re-arm for the next layer's launch
+                s_last = last;
+            }
+            compute_bar_sync();
+            if (s_last) {
+                __threadfence();
+                for (int e = threadIdx.x; e < G * D; e += ATTN_COMPUTE_WARPS * 32) {
+                    const int hg = e / D, dim = e % D;
+                    float M = -INFINITY;
+                    for (int c = c_first; c <= c_last; ++c)
+                        M = fmaxf(M, __ldcg(scratch + ((size_t)(c + seg_idx) * ATTN_GMAX + hg) * C::REC + D));
+                    const float Mu = M == -INFINITY ? 0.f : M;
+                    float L = 0.f, O = 0.f;
+                    for (int c = c_first; c <= c_last; ++c) {
+                        const float* rec = scratch + ((size_t)(c + seg_idx) * ATTN_GMAX + hg) * C::REC;
+                        const float sc = exp2f(__ldcg(rec + D) - Mu);
+                        L += __ldcg(rec + D + 1) * sc;
+                        O += __ldcg(rec + dim) * sc;
+                    }
+                    const float r = O / L;
+                    const __nv_bfloat16 hb = __float2bfloat16(r);
+                    out[out_row + e] = hb;
+                    if (out_lo) out_lo[out_row + e] = __float2bfloat16(r - __bfloat162float(hb));
+                }
+            }
         }
-        out[((size_t)b * nq + (size_t)h * G + hg) * D + dim] = __float2bfloat16(O / L);
+        compute_bar_sync();
     }
 }
 
@@ -327,8 +335,8 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restri
                     const int* __restrict__ page_table, int max_pages,
                     const int* __restrict__ req_q_start, const int* __restrict__ req_slot,
                     const int* __restrict__ req_pos0, const int* __restrict__ tile_req,
-                    const int* __restrict__ tile_q0, __nv_bfloat16* __restrict__ out, int nq, int nkv,
-                    float scale_log2) {
+                    const int* __restrict__ tile_q0, __nv_bfloat16* __restrict__ out,
+                    __nv_bfloat16* __restrict__ out_lo, int nq, int nkv, float scale_log2) {
     using C = AttnCfg<D>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -485,19 +493,26 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restri
     l_b += __shfl_xor_sync(0xffffffffu, l_b, 1);
     l_b += __shfl_xor_sync(0xffffffffu, l_b, 2);
     const float ia = 1.f / l_a, ib = 1.f / l_b;
-    __nv_bfloat16* oa = out + ((size_t)(req_q_start[req] + row_a) * nq + head) * D;
-    __nv_bfloat16* ob = out + ((size_t)(req_q_start[req] + row_b) * nq + head) * D;
+    const size_t off_a = ((size_t)(req_q_start[req] + row_a) * nq + head) * D;
+    const size_t off_b = ((size_t)(req_q_start[req] + row_b) * nq + head) * D;
+    auto store = [&](size_t off, float x, float y) {
+        const uint32_t h = pack_bf16(x, y);
+        *reinterpret_cast<uint32_t*>(out + off) = h;
+        if (out_lo) *reinterpret_cast<uint32_t*>(out_lo + off) = pack_bf16(x - bf16_lo(h), y - bf16_hi(h));
+    };
 #pragma unroll
     for (int nt = 0; nt < D / 8; ++nt) {
-        if (va) *reinterpret_cast<uint32_t*>(oa + nt * 8 + 2 * tq) = pack_bf16(o[nt][0] * ia, o[nt][1] * ia);
-        if (vb) *reinterpret_cast<uint32_t*>(ob + nt * 8 + 2 * tq) = pack_bf16(o[nt][2] * ib, o[nt][3] * ib);
+        if (va) store(off_a + nt * 8 + 2 * tq, o[nt][0] * ia, o[nt][1] * ia);
+        if (vb) store(off_b + nt * 8 + 2 * tq, o[nt][2] * ib, o[nt][3] * ib);
     }
 }
 
 // ------------------------------------------------------------------ launchers
+// scratch = [B*nkv arrival counters (padded to 64 ints)] [partial records]
+static size_t counter_floats(int B, int nkv) { return (size_t)((B * nkv + 63) / 64) * 64; }
 size_t attn_decode_scratch_floats(int B, int nkv, int group, int d, int n_ctas) {
     (void)group;
-    return (size_t)(n_ctas + B * nkv) * ATTN_GMAX * (d + 2);
+    return counter_floats(B, nkv) + (size_t)(n_ctas + B * nkv) * ATTN_GMAX * (d + 2);
 }
 
 template <int D>
@@ -530,19 +545,21 @@ static void fill_cfg(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr, dim3 gr
     cfg.numAttrs = pdl ? 1 : 0;
 }
 
-int launch_attn_decode_plan(const int* ctx_lens, int* tile_prefix, int B, bool pdl, cudaStream_t stream) {
+int launch_attn_decode_plan(const int* ctx_lens, int* tile_prefix, int B, int nkv, float* scratch, bool pdl,
+                            cudaStream_t stream) {
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
-    fill_cfg(cfg, attr, dim3(1), dim3(32), 0, pdl, stream);
-    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_plan_kernel, ctx_lens, tile_prefix, B));
+    fill_cfg(cfg, attr, dim3(1), dim3(256), 0, pdl, stream);
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_plan_kernel, ctx_lens, tile_prefix, B,
+                                     reinterpret_cast<int*>(scratch), (int)counter_floats(B, nkv)));
     return 0;
 }
 
 template <int D>
 static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* page_table, int max_pages,
-                                const int* ctx_lens, const int* tile_prefix, void* out, float* scratch,
-                                int B, int nq, int nkv, int n_ctas, bool pdl, cudaStream_t stream,
-                                cudaEvent_t ev0, cudaEvent_t ev1) {
+                                const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo,
+                                float* scratch, int B, int nq, int nkv, int n_ctas, bool pdl,
+                                cudaStream_t stream, cudaEvent_t ev0, cudaEvent_t ev1) {
     using C = AttnCfg<D>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -557,33 +574,31 @@ static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* 
     if (ev0) FT_CHECK_CUDA(cudaEventRecord(ev0, stream));
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_kernel<D>, (const __nv_bfloat16*)q,
                                      (const uint8_t*)kv_layer, page_table, max_pages, ctx_lens, tile_prefix,
-                                     (__nv_bfloat16*)out, scratch, B, nq, nkv, scale_log2));
+                                     (__nv_bfloat16*)out, (__nv_bfloat16*)out_lo, reinterpret_cast<int*>(scratch),
+                                     scratch + counter_floats(B, nkv), B, nq, nkv, scale_log2));
     if (ev1) FT_CHECK_CUDA(cudaEventRecord(ev1, stream));
-    fill_cfg(cfg, attr, dim3(B * nkv), dim3(128), 0, pdl, stream);
-    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_merge_kernel<D>, tile_prefix, (const float*)scratch,
-                                     (__nv_bfloat16*)out, B, nq, nkv, n_ctas));
     return 0;
 }
 
 int launch_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
-                       const int* ctx_lens, const int* tile_prefix, void* out, float* scratch, int B,
-                       int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream, cudaEvent_t ev0,
-                       cudaEvent_t ev1) {
+                       const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo, float* scratch,
+                       int B, int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream,
+                       cudaEvent_t ev0, cudaEvent_t ev1) {
     FT_REQUIRE(d == 64 || d == 128, "attn_decode: head_dim %d not supported (64 or 128)", d);
     FT_REQUIRE(nq % nkv == 0 && nq / nkv <= ATTN_GMAX, "attn_decode: GQA group %d/%d not supported", nq, nkv);
     FT_REQUIRE(B >= 1 && n_ctas >= 1, "attn_decode: B=%d n_ctas=%d", B, n_ctas);
     if (d == 64)
-        return launch_attn_decode_d<64>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out,
+        return launch_attn_decode_d<64>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo,
                                         scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1);
-    return launch_attn_decode_d<128>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, scratch,
-                                     B, nq, nkv, n_ctas, pdl, stream, ev0, ev1);
+    return launch_attn_decode_d<128>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo,
+                                     scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1);
 }
 
 template <int D>
 static int launch_attn_prefill_d(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                                  const int* req_q_start, const int* req_slot, const int* req_pos0,
-                                 const int* tile_req, const int* tile_q0, int n_tiles, void* out, int nq,
-                                 int nkv, bool pdl, cudaStream_t stream) {
+                                 const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo,
+                                 int nq, int nkv, bool pdl, cudaStream_t stream) {
     using C = AttnCfg<D>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -597,22 +612,23 @@ static int launch_attn_prefill_d(const void* q, const void* kv_layer, const int*
     fill_cfg(cfg, attr, dim3(n_tiles, nq), dim3(ATTN_THREADS), C::SMEM, pdl, stream);
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_kernel<D>, (const __nv_bfloat16*)q,
                                      (const uint8_t*)kv_layer, page_table, max_pages, req_q_start, req_slot,
-                                     req_pos0, tile_req, tile_q0, (__nv_bfloat16*)out, nq, nkv, scale_log2));
+                                     req_pos0, tile_req, tile_q0, (__nv_bfloat16*)out, (__nv_bfloat16*)out_lo, nq,
+                                     nkv, scale_log2));
     return 0;
 }
 
 int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                         const int* req_q_start, const int* req_slot, const int* req_pos0,
-                        const int* tile_req, const int* tile_q0, int n_tiles, void* out, int nq, int nkv,
-                        int d, bool pdl, cudaStream_t stream) {
+                        const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq,
+                        int nkv, int d, bool pdl, cudaStream_t stream) {
     FT_REQUIRE(d == 64 || d == 128, "attn_prefill: head_dim %d not supported (64 or 128)", d);
     FT_REQUIRE(nq % nkv == 0, "attn_prefill: nq %% nkv != 0");
     FT_REQUIRE(n_tiles >= 1, "attn_prefill: no tiles");
     if (d == 64)
         return launch_attn_prefill_d<64>(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
-                                         tile_req, tile_q0, n_tiles, out, nq, nkv, pdl, stream);
+                                         tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, pdl, stream);
     return launch_attn_prefill_d<128>(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
-                                      tile_req, tile_q0, n_tiles, out, nq, nkv, pdl, stream);
+                                      tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, pdl, stream);
 }
 
 }  // namespace ft
@@ -634,19 +650,19 @@ extern "C" long long ft_attn_decode_scratch_bytes(int B, int nkv, int group, int
 }
 
 extern "C" int ft_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
-                              const int* ctx_lens, int* tile_prefix, void* out, float* scratch, int B, int nq,
-                              int nkv, int d, int n_ctas, void* stream) {
+                              const int* ctx_lens, int* tile_prefix, void* out, void* out_lo, float* scratch,
+                              int B, int nq, int nkv, int d, int n_ctas, void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (int r = ft::launch_attn_decode_plan(ctx_lens, tile_prefix, B, false, st)) return r;
-    return ft::launch_attn_decode(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, scratch, B,
-                                  nq, nkv, d, n_ctas, false, st, nullptr, nullptr);
+    if (int r = ft::launch_attn_decode_plan(ctx_lens, tile_prefix, B, nkv, scratch, false, st)) return r;
+    return ft::launch_attn_decode(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo,
+                                  scratch, B, nq, nkv, d, n_ctas, false, st, nullptr, nullptr);
 }
 
 extern "C" int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                                const int* req_q_start, const int* req_slot, const int* req_pos0,
-                               const int* tile_req, const int* tile_q0, int n_tiles, void* out, int nq,
-                               int nkv, int d, void* stream) {
+                               const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo,
+                               int nq, int nkv, int d, void* stream) {
     return ft::launch_attn_prefill(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
-                                   tile_req, tile_q0, n_tiles, out, nq, nkv, d, false,
+                                   tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, d, false,
                                    static_cast<cudaStream_t>(stream));
 }

@@ -23,7 +23,7 @@ const char* last_error() { return g_err; }
 // row i of the output <- row r = row_idx ? row_idx[i] : i of the residual stream.
 //   embed_tokens != null : resid[r] = embed[token[r]]                       (layer-0 entry)
 //   else                 : resid[r] += sum_s partials[s][r]                 (n_splits may be 0)
-//   xn[i] = bf16( resid[r] * rsqrt(mean(resid[r]^2) + eps) * w )
+//   y = resid[r] * rsqrt(mean(resid[r]^2) + eps) * w;  xn[i] = bf16(y);  xn_lo[i] = bf16(y - xn[i])
 constexpr int NORM_THREADS = 256;
 constexpr int NORM_MAXV = 8;      // float4 per thread -> h <= 8192
 
@@ -31,7 +31,8 @@ __global__ void __launch_bounds__(NORM_THREADS)
 add_rmsnorm_kernel(float* __restrict__ resid, const float* __restrict__ partials, int n_splits,
                    size_t split_stride, const int* __restrict__ embed_tokens,
                    const __nv_bfloat16* __restrict__ embed, const __nv_bfloat16* __restrict__ w,
-                   __nv_bfloat16* __restrict__ xn, const int* __restrict__ row_idx, int h, float eps) {
+                   __nv_bfloat16* __restrict__ xn, __nv_bfloat16* __restrict__ xn_lo,
+                   const int* __restrict__ row_idx, int h, float eps) {
     pdl_wait();
     pdl_launch_dependents();
     const int i = blockIdx.x;
@@ -50,8 +51,17 @@ add_rmsnorm_kernel(float* __restrict__ resid, const float* __restrict__ partials
                 x = make_float4(bf16_lo(e.x), bf16_hi(e.x), bf16_lo(e.y), bf16_hi(e.y));
             } else {
                 x = reinterpret_cast<const float4*>(rrow)[c];
-                for (int s = 0; s < n_splits; ++s) {
-                    const float4 p = reinterpret_cast<const float4*>(partials + s * split_stride + (size_t)r * h)[c];
+                const float4* pp = reinterpret_cast<const float4*>(partials + (size_t)r * h) + c;
+                const size_t ps = split_stride >> 2;
+                int s = 0;
+                for (; s + 4 <= n_splits; s += 4) {        // four independent loads in flight
+                    const float4 p0 = __ldcg(pp + (s + 0) * ps), p1 = __ldcg(pp + (s + 1) * ps);
+                    const float4 p2 = __ldcg(pp + (s + 2) * ps), p3 = __ldcg(pp + (s + 3) * ps);
+                    x.x += (p0.x + p1.x) + (p2.x + p3.x); x.y += (p0.y + p1.y) + (p2.y + p3.y);
+                    x.z += (p0.z + p1.z) + (p2.z + p3.z); x.w += (p0.w + p1.w) + (p2.w + p3.w);
+                }
+                for (; s < n_splits; ++s) {
+                    const float4 p = __ldcg(pp + s * ps);
                     x.x += p.x; x.y += p.y; x.z += p.z; x.w += p.w;
                 }
             }
@@ -73,10 +83,18 @@ add_rmsnorm_kernel(float* __restrict__ resid, const float* __restrict__ partials
         const int c = threadIdx.x + v * NORM_THREADS;
         if (c < nv) {
             const uint2 wv = *reinterpret_cast<const uint2*>(w + c * 4);
+            const float y0 = a[v].x * rstd * bf16_lo(wv.x), y1 = a[v].y * rstd * bf16_hi(wv.x);
+            const float y2 = a[v].z * rstd * bf16_lo(wv.y), y3 = a[v].w * rstd * bf16_hi(wv.y);
             uint2 o;
-            o.x = pack_bf16(a[v].x * rstd * bf16_lo(wv.x), a[v].y * rstd * bf16_hi(wv.x));
-            o.y = pack_bf16(a[v].z * rstd * bf16_lo(wv.y), a[v].w * rstd * bf16_hi(wv.y));
+            o.x = pack_bf16(y0, y1);
+            o.y = pack_bf16(y2, y3);
             *reinterpret_cast<uint2*>(xn + (size_t)i * h + c * 4) = o;
+            if (xn_lo) {
+                uint2 l;
+                l.x = pack_bf16(y0 - bf16_lo(o.x), y1 - bf16_hi(o.x));
+                l.y = pack_bf16(y2 - bf16_lo(o.y), y3 - bf16_hi(o.y));
+                *reinterpret_cast<uint2*>(xn_lo + (size_t)i * h + c * 4) = l;
+            }
         }
     }
 }
@@ -113,9 +131,10 @@ rope_kv_append_kernel(const float* __restrict__ qkv, int n_splits, size_t split_
     for (int p = 0; p < PAIRS; ++p) {
         const int i = lane + p * 32;
         float a = 0.f, b = 0.f;
+#pragma unroll 4
         for (int s = 0; s < n_splits; ++s) {
-            a += qkv[s * split_stride + row_off + i];
-            b += qkv[s * split_stride + row_off + i + HALF];
+            a += __ldcg(qkv + s * split_stride + row_off + i);
+            b += __ldcg(qkv + s * split_stride + row_off + i + HALF);
         }
         lo[p] = a;
         hi[p] = b;
@@ -160,7 +179,7 @@ rope_kv_append_kernel(const float* __restrict__ qkv, int n_splits, size_t split_
 // act[t][j] = bf16( silu(sum_s gu[s][t][j]) * sum_s gu[s][t][f + j] )
 __global__ void __launch_bounds__(256)
 silu_mul_kernel(const float* __restrict__ gu, int n_splits, size_t split_stride,
-                __nv_bfloat16* __restrict__ act, int T, int f) {
+                __nv_bfloat16* __restrict__ act, __nv_bfloat16* __restrict__ act_lo, int T, int f) {
     pdl_wait();
     pdl_launch_dependents();
     const int fv = f >> 2;
@@ -176,10 +195,17 @@ silu_mul_kernel(const float* __restrict__ gu, int n_splits, size_t split_stride,
         u.x += b.x; u.y += b.y; u.z += b.z; u.w += b.w;
     }
     auto silu = [](float x) { return x / (1.f + __expf(-x)); };
+    const float y0 = silu(g.x) * u.x, y1 = silu(g.y) * u.y, y2 = silu(g.z) * u.z, y3 = silu(g.w) * u.w;
     uint2 o;
-    o.x = pack_bf16(silu(g.x) * u.x, silu(g.y) * u.y);
-    o.y = pack_bf16(silu(g.z) * u.z, silu(g.w) * u.w);
+    o.x = pack_bf16(y0, y1);
+    o.y = pack_bf16(y2, y3);
     *reinterpret_cast<uint2*>(act + (size_t)t * f + c * 4) = o;
+    if (act_lo) {
+        uint2 l;
+        l.x = pack_bf16(y0 - bf16_lo(o.x), y1 - bf16_hi(o.x));
+        l.y = pack_bf16(y2 - bf16_lo(o.y), y3 - bf16_hi(o.y));
+        *reinterpret_cast<uint2*>(act_lo + (size_t)t * f + c * 4) = l;
+    }
 }
 
 // ------------------------------------------------------------------ launchers
@@ -198,7 +224,7 @@ static void fill_cfg(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr, dim3 gr
 
 int launch_add_rmsnorm(float* resid, const float* partials, int n_splits, size_t split_stride,
                        const int* embed_tokens, const void* embed_table, const void* norm_w,
-                       void* xn_out, const int* row_idx, int T, int h, float eps, bool pdl,
+                       void* xn_out, void* xn_lo, const int* row_idx, int T, int h, float eps, bool pdl,
                        cudaStream_t stream) {
     FT_REQUIRE(h % 4 == 0 && h <= 4 * NORM_THREADS * NORM_MAXV, "add_rmsnorm: unsupported h=%d", h);
     FT_REQUIRE(T >= 1, "add_rmsnorm: T=%d", T);
@@ -207,8 +233,8 @@ int launch_add_rmsnorm(float* resid, const float* partials, int n_splits, size_t
     fill_cfg(cfg, attr, dim3(T), dim3(NORM_THREADS), 0, pdl, stream);
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, add_rmsnorm_kernel, resid, partials, n_splits, split_stride,
                                      embed_tokens, (const __nv_bfloat16*)embed_table,
-                                     (const __nv_bfloat16*)norm_w, (__nv_bfloat16*)xn_out, row_idx, h,
-                                     eps));
+                                     (const __nv_bfloat16*)norm_w, (__nv_bfloat16*)xn_out,
+                                     (__nv_bfloat16*)xn_lo, row_idx, h, eps));
     return 0;
 }
 
@@ -233,15 +259,15 @@ int launch_rope_kv_append(const float* qkv, int n_splits, size_t split_stride, c
     return 0;
 }
 
-int launch_silu_mul(const float* gu, int n_splits, size_t split_stride, void* act, int T, int f,
-                    bool pdl, cudaStream_t stream) {
+int launch_silu_mul(const float* gu, int n_splits, size_t split_stride, void* act, void* act_lo, int T,
+                    int f, bool pdl, cudaStream_t stream) {
     FT_REQUIRE(f % 4 == 0, "silu_mul: f=%d must be a multiple of 4", f);
     const size_t n = (size_t)T * (f / 4);
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
     fill_cfg(cfg, attr, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, pdl, stream);
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, silu_mul_kernel, gu, n_splits, split_stride,
-                                     (__nv_bfloat16*)act, T, f));
+                                     (__nv_bfloat16*)act, (__nv_bfloat16*)act_lo, T, f));
     return 0;
 }
 
@@ -252,9 +278,10 @@ extern "C" const char* ft_last_error(void) { return ft::last_error(); }
 
 extern "C" int ft_add_rmsnorm(float* resid, const float* partials, int n_splits, long long split_stride,
                               const int* embed_tokens, const void* embed_table, const void* norm_w,
-                              void* xn_out, const int* row_idx, int T, int h, float eps, void* stream) {
+                              void* xn_out, void* xn_lo, const int* row_idx, int T, int h, float eps,
+                              void* stream) {
     return ft::launch_add_rmsnorm(resid, partials, n_splits, (size_t)split_stride, embed_tokens,
-                                  embed_table, norm_w, xn_out, row_idx, T, h, eps, false,
+                                  embed_table, norm_w, xn_out, xn_lo, row_idx, T, h, eps, false,
                                   static_cast<cudaStream_t>(stream));
 }
 
@@ -267,8 +294,8 @@ extern "C" int ft_rope_kv_append(const float* qkv, int n_splits, long long split
                                      false, static_cast<cudaStream_t>(stream));
 }
 
-extern "C" int ft_silu_mul(const float* gu, int n_splits, long long split_stride, void* act, int T,
-                           int f, void* stream) {
-    return ft::launch_silu_mul(gu, n_splits, (size_t)split_stride, act, T, f, false,
+extern "C" int ft_silu_mul(const float* gu, int n_splits, long long split_stride, void* act, void* act_lo,
+                           int T, int f, void* stream) {
+    return ft::launch_silu_mul(gu, n_splits, (size_t)split_stride, act, act_lo, T, f, false,
                                static_cast<cudaStream_t>(stream));
 }

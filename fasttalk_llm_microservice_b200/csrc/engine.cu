@@ -81,7 +81,9 @@ struct Engine {
     float* resid = nullptr;
     float* part = nullptr;
     size_t part_floats = 0;
+    // bf16 activations feeding the GEMMs are kept as hi + lo planes (see gemm.cu)
     void *xn = nullptr, *q = nullptr, *attn_out = nullptr, *act = nullptr, *xn_last = nullptr;
+    void *xn_lo = nullptr, *attn_out_lo = nullptr, *act_lo = nullptr, *xn_last_lo = nullptr;
     float* logits = nullptr;
     float* attn_scratch = nullptr;
     StepMeta meta;
@@ -89,7 +91,8 @@ struct Engine {
     // tensor maps: weights per layer, activations per BN
     std::vector<CUtensorMap> m_wqkv, m_wo, m_wgu, m_wd;
     CUtensorMap m_lm;
-    CUtensorMap m_xn[5], m_attn[5], m_act[5], m_last[5];
+    CUtensorMap m_xn[4], m_attn[4], m_act[4], m_last[4];              // token tiles 16/32/64/128
+    CUtensorMap m_xn_lo[4], m_attn_lo[4], m_act_lo[4], m_last_lo[4];
 
     // scheduler state
     std::vector<int> free_pages;
@@ -109,8 +112,8 @@ struct Engine {
     cudaEvent_t t0 = nullptr, t1 = nullptr;
 };
 
-static int bn_index(int bn) { return bn == 16 ? 0 : bn == 32 ? 1 : bn == 64 ? 2 : bn == 128 ? 3 : 4; }
-static const int kBns[5] = {16, 32, 64, 128, 256};
+static int bn_index(int bn) { return bn == 16 ? 0 : bn == 32 ? 1 : bn == 64 ? 2 : 3; }
+static const int kBns[4] = {16, 32, 64, 128};
 
 // ------------------------------------------------------------------ pages / sessions
 static void release_pages_beyond(Engine* e, Session* s, int keep_tokens) {
@@ -178,13 +181,14 @@ struct Batch {
         if (_r) return _r;                          \
     } while (0)
 
-static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, int T, int n_out, int K,
-                    void* out, int* splits_out) {
-    const int bn = gemm_pick_bn(T);
-    const int splits = gemm_pick_splits(n_out, T, K, e->sms);
+static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, const CUtensorMap* xmaps_lo,
+                    int T, int n_out, int K, void* out, int* splits_out) {
+    const int bn = gemm_pick_bn(T, true);
+    const int splits = gemm_pick_splits(n_out, T, K, e->sms, true);
     *splits_out = splits;
     e->st.kernel_launches++;
-    return launch_gemm(mw, xmaps[bn_index(bn)], bn, out, n_out, T, K, splits, 0, e->pdl, e->stream);
+    return launch_gemm(mw, xmaps[bn_index(bn)], &xmaps_lo[bn_index(bn)], bn, out, nullptr, n_out, T, K, splits,
+                       0, e->pdl, e->stream);
 }
 
 static int forward(Engine* e, const Batch& b) {
@@ -197,16 +201,17 @@ static int forward(Engine* e, const Batch& b) {
         return (const void*)((const uint8_t*)p + elems * 2);
     };
     FT_TRY(launch_add_rmsnorm(e->resid, nullptr, 0, 0, d + m.o_tokens, e->w.embed, e->w.attn_norm, e->xn,
-                              nullptr, T, c.hidden, c.rms_eps, e->pdl, e->stream));
+                              e->xn_lo, nullptr, T, c.hidden, c.rms_eps, e->pdl, e->stream));
     e->st.kernel_launches++;
     if (b.n_decode > 0) {
-        FT_TRY(launch_attn_decode_plan(d + m.o_ctx, d + m.o_tprefix, b.n_decode, e->pdl, e->stream));
+        FT_TRY(launch_attn_decode_plan(d + m.o_ctx, d + m.o_tprefix, b.n_decode, c.n_kv_heads, e->attn_scratch,
+                                       e->pdl, e->stream));
         e->st.kernel_launches++;
     }
     int s = 0;
     for (int l = 0; l < c.layers; ++l) {
         uint8_t* kv_l = e->kv + (size_t)l * e->kv_layer_bytes;
-        FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, T, e->qkv_dim, c.hidden, e->part, &s));
+        FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, e->m_xn_lo, T, e->qkv_dim, c.hidden, e->part, &s));
         FT_TRY(launch_rope_kv_append(e->part, s, (size_t)T * e->qkv_dim, e->w.rope_cos, e->w.rope_sin,
                                      d + m.o_pos, d + m.o_rows, d + m.o_pt, e->max_pages, e->q, kv_l, T,
                                      c.n_q_heads, c.n_kv_heads, c.head_dim, e->pdl, e->stream));
@@ -219,43 +224,45 @@ static int forward(Engine* e, const Batch& b) {
                 e->prof_used = l + 1;
             }
             FT_TRY(launch_attn_decode(e->q, kv_l, d + m.o_pt, e->max_pages, d + m.o_ctx, d + m.o_tprefix,
-                                      e->attn_out, e->attn_scratch, b.n_decode, c.n_q_heads, c.n_kv_heads,
-                                      c.head_dim, e->attn_ctas, e->pdl, e->stream, ev0, ev1));
-            e->st.kernel_launches += 2;
+                                      e->attn_out, e->attn_out_lo, e->attn_scratch, b.n_decode, c.n_q_heads,
+                                      c.n_kv_heads, c.head_dim, e->attn_ctas, e->pdl, e->stream, ev0, ev1));
+            e->st.kernel_launches++;
         }
         if (b.n_tiles > 0) {
             FT_TRY(launch_attn_prefill(e->q, kv_l, d + m.o_pt, e->max_pages, d + m.o_qstart, d + m.o_rslot,
                                        d + m.o_rpos0, d + m.o_treq, d + m.o_tq0, b.n_tiles, e->attn_out,
-                                       c.n_q_heads, c.n_kv_heads, c.head_dim, e->pdl, e->stream));
+                                       e->attn_out_lo, c.n_q_heads, c.n_kv_heads, c.head_dim, e->pdl,
+                                       e->stream));
             e->st.kernel_launches++;
         }
-        FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, T, c.hidden, e->q_dim, e->part, &s));
+        FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, e->m_attn_lo, T, c.hidden, e->q_dim, e->part, &s));
         FT_TRY(launch_add_rmsnorm(e->resid, e->part, s, (size_t)T * H, nullptr, nullptr,
-                                  bf16_off(e->w.mlp_norm, (size_t)l * H), e->xn, nullptr, T, c.hidden,
+                                  bf16_off(e->w.mlp_norm, (size_t)l * H), e->xn, e->xn_lo, nullptr, T, c.hidden,
                                   c.rms_eps, e->pdl, e->stream));
         e->st.kernel_launches++;
-        FT_TRY(run_gemm(e, e->m_wgu[l], e->m_xn, T, 2 * c.ffn, c.hidden, e->part, &s));
-        FT_TRY(launch_silu_mul(e->part, s, (size_t)T * 2 * c.ffn, e->act, T, c.ffn, e->pdl, e->stream));
-        e->st.kernel_launches++;
-        FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, T, c.hidden, c.ffn, e->part, &s));
+        {   // gate/up projection with the SwiGLU fused into the epilogue: act = silu(g) * u
+            const int bn = gemm_pick_bn(T, true);
+            FT_TRY(launch_gemm(e->m_wgu[l], e->m_xn[bn_index(bn)], &e->m_xn_lo[bn_index(bn)], bn, e->act,
+                               e->act_lo, 2 * c.ffn, T, c.hidden, 1, 2, e->pdl, e->stream));
+            e->st.kernel_launches++;
+        }
+        FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, e->m_act_lo, T, c.hidden, c.ffn, e->part, &s));
         if (l + 1 < c.layers) {
             FT_TRY(launch_add_rmsnorm(e->resid, e->part, s, (size_t)T * H, nullptr, nullptr,
-                                      bf16_off(e->w.attn_norm, (size_t)(l + 1) * H), e->xn, nullptr, T,
+                                      bf16_off(e->w.attn_norm, (size_t)(l + 1) * H), e->xn, e->xn_lo, nullptr, T,
                                       c.hidden, c.rms_eps, e->pdl, e->stream));
             e->st.kernel_launches++;
         }
     }
     if (b.n_logit_rows > 0) {
         FT_TRY(launch_add_rmsnorm(e->resid, e->part, s, (size_t)T * H, nullptr, nullptr, e->w.final_norm,
-                                  e->xn_last, d + m.o_lrow, b.n_logit_rows, c.hidden, c.rms_eps, e->pdl,
-                                  e->stream));
+                                  e->xn_last, e->xn_last_lo, d + m.o_lrow, b.n_logit_rows, c.hidden, c.rms_eps,
+                                  e->pdl, e->stream));
         e->st.kernel_launches++;
-        int s2 = 0;
-        const int bn = gemm_pick_bn(b.n_logit_rows);
+        const int bn = gemm_pick_bn(b.n_logit_rows, true);
         e->st.kernel_launches++;
-        FT_TRY(launch_gemm(e->m_lm, e->m_last[bn_index(bn)], bn, e->logits, c.vocab, b.n_logit_rows,
-                           c.hidden, 1, 0, e->pdl, e->stream));
-        (void)s2;
+        FT_TRY(launch_gemm(e->m_lm, e->m_last[bn_index(bn)], &e->m_last_lo[bn_index(bn)], bn, e->logits, nullptr,
+                           c.vocab, b.n_logit_rows, c.hidden, 1, 0, e->pdl, e->stream));
     }
     return 0;
 }
@@ -469,8 +476,8 @@ static int engine_init(Engine* e) {
     FT_REQUIRE(c.head_dim == 64 || c.head_dim == 128, "engine: head_dim %d not supported", c.head_dim);
     FT_REQUIRE(c.n_q_heads % c.n_kv_heads == 0 && c.n_q_heads / c.n_kv_heads <= 8,
                "engine: GQA group must divide and be <= 8");
-    FT_REQUIRE(c.hidden % 128 == 0 && c.ffn % 128 == 0 && c.vocab % 128 == 0,
-               "engine: hidden/ffn/vocab must be multiples of 128");
+    FT_REQUIRE(c.hidden % 128 == 0 && c.ffn % 64 == 0 && c.vocab % 128 == 0,
+               "engine: hidden/vocab must be multiples of 128 and ffn of 64");
     FT_REQUIRE(c.max_batch >= 1 && c.max_batched_tokens >= c.max_batch, "engine: bad batch limits");
     FT_REQUIRE(c.max_context >= 64 && c.num_pages >= 1, "engine: bad context/page limits");
     FT_CHECK_CUDA(cudaGetDevice(&e->dev));
@@ -497,23 +504,28 @@ static int engine_init(Engine* e) {
     FT_CHECK_CUDA(cudaMemsetAsync(e->kv, 0, e->kv_layer_bytes * c.layers, e->stream));
     FT_CHECK_CUDA(cudaMalloc(&e->resid, T * c.hidden * 4));
     const size_t rows_last = std::max<size_t>(e->logit_rows, 256);
-    FT_CHECK_CUDA(cudaMalloc(&e->xn, T * c.hidden * 2));
     FT_CHECK_CUDA(cudaMalloc(&e->q, T * e->q_dim * 2));
-    FT_CHECK_CUDA(cudaMalloc(&e->attn_out, T * e->q_dim * 2));
-    FT_CHECK_CUDA(cudaMalloc(&e->act, T * c.ffn * 2));
-    FT_CHECK_CUDA(cudaMalloc(&e->xn_last, rows_last * c.hidden * 2));
     FT_CHECK_CUDA(cudaMalloc(&e->logits, (size_t)e->logit_rows * c.vocab * 4));
-    FT_CHECK_CUDA(cudaMemsetAsync(e->xn, 0, T * c.hidden * 2, e->stream));
-    FT_CHECK_CUDA(cudaMemsetAsync(e->attn_out, 0, T * e->q_dim * 2, e->stream));
-    FT_CHECK_CUDA(cudaMemsetAsync(e->act, 0, T * c.ffn * 2, e->stream));
-    FT_CHECK_CUDA(cudaMemsetAsync(e->xn_last, 0, rows_last * c.hidden * 2, e->stream));
+    auto alloc_zero = [&](void** p, size_t bytes) -> int {
+        FT_CHECK_CUDA(cudaMalloc(p, bytes));
+        FT_CHECK_CUDA(cudaMemsetAsync(*p, 0, bytes, e->stream));
+        return 0;
+    };
+    FT_TRY(alloc_zero(&e->xn, T * c.hidden * 2));
+    FT_TRY(alloc_zero(&e->xn_lo, T * c.hidden * 2));
+    FT_TRY(alloc_zero(&e->attn_out, T * e->q_dim * 2));
+    FT_TRY(alloc_zero(&e->attn_out_lo, T * e->q_dim * 2));
+    FT_TRY(alloc_zero(&e->act, T * c.ffn * 2));
+    FT_TRY(alloc_zero(&e->act_lo, T * c.ffn * 2));
+    FT_TRY(alloc_zero(&e->xn_last, rows_last * c.hidden * 2));
+    FT_TRY(alloc_zero(&e->xn_last_lo, rows_last * c.hidden * 2));
     // split-K partial sums: worst case over the four projections and every token count
     size_t pf = 0;
-    const int widths[4] = {e->qkv_dim, c.hidden, 2 * c.ffn, c.hidden};
-    const int ks[4] = {c.hidden, e->q_dim, c.hidden, c.ffn};
+    const int widths[3] = {e->qkv_dim, c.hidden, c.hidden};      // QKV, O, down (gate/up never splits)
+    const int ks[3] = {c.hidden, e->q_dim, c.ffn};
     for (int t = 1; t <= e->t_max; ++t)
-        for (int i = 0; i < 4; ++i)
-            pf = std::max(pf, (size_t)gemm_pick_splits(widths[i], t, ks[i], e->sms) * t * widths[i]);
+        for (int i = 0; i < 3; ++i)
+            pf = std::max(pf, (size_t)gemm_pick_splits(widths[i], t, ks[i], e->sms, true) * t * widths[i]);
     e->part_floats = pf;
     FT_CHECK_CUDA(cudaMalloc(&e->part, pf * 4));
 
@@ -559,13 +571,17 @@ static int engine_init(Engine* e) {
         FT_TRY(make_tmap_bf16_k64(&e->m_wd[l], at(e->w.wd, l * (size_t)c.hidden * c.ffn), c.hidden, c.ffn, 128));
     }
     FT_TRY(make_tmap_bf16_k64(&e->m_lm, e->w.lm_head, c.vocab, c.hidden, 128));
-    for (int i = 0; i < 5; ++i) {
+    for (int i = 0; i < 4; ++i) {
         // activation maps span the whole buffer; rows past the step's T hold stale (finite) data
         // whose output columns the GEMM epilogue masks
         FT_TRY(make_tmap_bf16_k64(&e->m_xn[i], e->xn, (int)T, c.hidden, kBns[i]));
+        FT_TRY(make_tmap_bf16_k64(&e->m_xn_lo[i], e->xn_lo, (int)T, c.hidden, kBns[i]));
         FT_TRY(make_tmap_bf16_k64(&e->m_attn[i], e->attn_out, (int)T, e->q_dim, kBns[i]));
+        FT_TRY(make_tmap_bf16_k64(&e->m_attn_lo[i], e->attn_out_lo, (int)T, e->q_dim, kBns[i]));
         FT_TRY(make_tmap_bf16_k64(&e->m_act[i], e->act, (int)T, c.ffn, kBns[i]));
+        FT_TRY(make_tmap_bf16_k64(&e->m_act_lo[i], e->act_lo, (int)T, c.ffn, kBns[i]));
         FT_TRY(make_tmap_bf16_k64(&e->m_last[i], e->xn_last, (int)rows_last, c.hidden, kBns[i]));
+        FT_TRY(make_tmap_bf16_k64(&e->m_last_lo[i], e->xn_last_lo, (int)rows_last, c.hidden, kBns[i]));
     }
     e->prof_ev.resize(2 * L);
     for (auto& ev : e->prof_ev) FT_CHECK_CUDA(cudaEventCreate(&ev));
@@ -584,6 +600,7 @@ static void engine_free(Engine* e) {
     for (auto& kv : e->requests) delete kv.second;
     cudaFree(e->kv); cudaFree(e->resid); cudaFree(e->part); cudaFree(e->xn); cudaFree(e->q);
     cudaFree(e->attn_out); cudaFree(e->act); cudaFree(e->xn_last); cudaFree(e->logits);
+    cudaFree(e->xn_lo); cudaFree(e->attn_out_lo); cudaFree(e->act_lo); cudaFree(e->xn_last_lo);
     cudaFree(e->attn_scratch); cudaFree(e->meta.d);
     if (e->meta.h) cudaFreeHost(e->meta.h);
     for (auto ev : e->prof_ev) if (ev) cudaEventDestroy(ev);

@@ -11,36 +11,39 @@ constexpr int GEMM_MAX_SPLITS = 16;
 
 // ---- gemm.cu
 int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int box_rows);
-int gemm_pick_bn(int T);
-int gemm_pick_splits(int n_out, int T, int K, int num_sms);
-int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, int bn, void* out, int n_out, int T,
-                int K, int splits, int out_mode, bool pdl, cudaStream_t stream);
+int gemm_pick_bn(int T, bool hilo);
+int gemm_pick_splits(int n_out, int T, int K, int num_sms, bool hilo);
+// out_mode 0: fp32 partials [split][T][n_out]; 1: bf16 [T][n_out] (+ lo plane); 2: fused SwiGLU
+// (weight rows interleaved gate/up in blocks of 64) -> bf16 [T][n_out/2] (+ lo plane)
+int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap* mx_lo, int bn, void* out,
+                void* out_lo, int n_out, int T, int K, int splits, int out_mode, bool pdl,
+                cudaStream_t stream);
 
 // ---- elementwise.cu
 int launch_add_rmsnorm(float* resid, const float* partials, int n_splits, size_t split_stride,
                        const int* embed_tokens, const void* embed_table, const void* norm_w,
-                       void* xn_out, const int* row_idx, int T, int h, float eps, bool pdl,
+                       void* xn_out, void* xn_lo, const int* row_idx, int T, int h, float eps, bool pdl,
                        cudaStream_t stream);
 int launch_rope_kv_append(const float* qkv, int n_splits, size_t split_stride, const float* cos_t,
                           const float* sin_t, const int* positions, const int* seq_slots,
                           const int* page_table, int max_pages, void* q_out, void* kv_layer, int T,
                           int nq, int nkv, int d, bool pdl, cudaStream_t stream);
-int launch_silu_mul(const float* gu, int n_splits, size_t split_stride, void* act, int T, int f,
-                    bool pdl, cudaStream_t stream);
+int launch_silu_mul(const float* gu, int n_splits, size_t split_stride, void* act, void* act_lo, int T,
+                    int f, bool pdl, cudaStream_t stream);
 
 // ---- attention.cu
 size_t attn_decode_scratch_floats(int B, int nkv, int group, int d, int n_ctas);
 int attn_decode_ctas_per_sm(int d);      // resident CTAs of the decode kernel per SM (<= 0: error)
 const char* last_error();
-int launch_attn_decode_plan(const int* ctx_lens, int* tile_prefix, int B, bool pdl,
+int launch_attn_decode_plan(const int* ctx_lens, int* tile_prefix, int B, int nkv, float* scratch, bool pdl,
                             cudaStream_t stream);
 int launch_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
-                       const int* ctx_lens, const int* tile_prefix, void* out, float* scratch, int B,
-                       int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream,
+                       const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo, float* scratch,
+                       int B, int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream,
                        cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr);
 int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                         const int* req_q_start, const int* req_slot, const int* req_pos0,
-                        const int* tile_req, const int* tile_q0, int n_tiles, void* out, int nq,
+                        const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq,
                         int nkv, int d, bool pdl, cudaStream_t stream);
 
 // ---- sampling.cu

@@ -16,7 +16,7 @@ import torch
 
 from . import native as N
 from .model_spec import ModelSpec
-from .weights import rope_tables
+from .weights import interleave_gate_up, rope_tables
 
 FINISH_REASONS = {0: None, 1: "stop", 2: "length", 3: "cancelled", 4: "error"}
 LLAMA3_EOS = (128009, 128001)
@@ -55,6 +55,12 @@ class Engine:
         w["lm_head"] = w["embed"] if weights["lm_head"] is weights["embed"] else weights["lm_head"].to(self.device).contiguous()
         for k, v in w.items():
             assert v.dtype == torch.bfloat16, f"weight {k} must be bf16"
+        # engine-side layout of the gate/up projection (fused SwiGLU epilogue); one layer at a time
+        # so the temporary stays small
+        wgu = torch.empty_like(w["wgu"])
+        for l in range(spec.layers):
+            wgu[l] = interleave_gate_up(w["wgu"][l])
+        w["wgu"] = wgu
         cos, sin = rope_tables(spec, lim.max_context, device=self.device)
         self._keep = (w, cos, sin)      # the engine only borrows these pointers
         pages_per_ctx = -(-lim.max_context // 64)

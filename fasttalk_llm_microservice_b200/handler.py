@@ -332,15 +332,23 @@ class NativeHandler:
 
     @staticmethod
     def _apply_stop(sink: _Sink, piece: str):
-        """Returns (text to yield, hit_stop)."""
+        """Returns (text to yield now, hit_stop).  Text that could still turn out to be the start
+        of a stop string is held back in sink.text until it is disambiguated."""
         if not sink.stop:
             return piece, False
-        before = len(sink.text)
-        sink.text += piece
-        cut = min((i for i in (sink.text.find(s) for s in sink.stop if s) if i >= 0), default=-1)
-        if cut < 0:
-            return piece, False
-        return sink.text[before:cut] if cut > before else "", True
+        buf = sink.text + piece
+        cut = min((i for i in (buf.find(s) for s in sink.stop if s) if i >= 0), default=-1)
+        if cut >= 0:
+            sink.text = ""
+            return buf[:cut], True
+        hold = 0
+        for s_ in sink.stop:
+            for k in range(min(len(s_) - 1, len(buf)), 0, -1):
+                if buf.endswith(s_[:k]):
+                    hold = max(hold, k)
+                    break
+        sink.text = buf[len(buf) - hold:] if hold else ""
+        return buf[:len(buf) - hold], False
 
     def generate_stream(self, messages: List[Dict[str, str]], temperature: Optional[float] = None,
                         max_tokens: Optional[int] = None, top_p: Optional[float] = None,
@@ -366,6 +374,8 @@ class NativeHandler:
                 if item is _DONE:
                     if sink.error:
                         raise sink.error
+                    if sink.text:               # held-back text that never became a stop string
+                        yield sink.text
                     break
                 text, hit = self._apply_stop(sink, item)
                 if text:
@@ -397,6 +407,8 @@ class NativeHandler:
                 if item is _DONE:
                     if sink.error:
                         raise sink.error
+                    if sink.text:
+                        yield sink.text
                     break
                 text, hit = self._apply_stop(sink, item)
                 if text:

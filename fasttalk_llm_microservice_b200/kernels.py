@@ -15,40 +15,58 @@ def _chk_bf16(t, name):
     assert t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous(), f"{name}: need contiguous CUDA bf16"
 
 
-def gemm_bf16(w: torch.Tensor, x: torch.Tensor, n_splits: int = 0, out_bf16: bool = False) -> torch.Tensor:
-    """Y[t, n] = sum_k X[t, k] W[n, k].  Returns fp32 partials [S, T, n_out] or bf16 [T, n_out]."""
+def split_hi_lo(x: torch.Tensor):
+    """fp32 -> (bf16 hi, bf16 lo) planes with hi + lo ~= x to ~16 mantissa bits."""
+    hi = x.to(torch.bfloat16)
+    lo = (x.float() - hi.float()).to(torch.bfloat16)
+    return hi.contiguous(), lo.contiguous()
+
+
+def gemm_bf16(w: torch.Tensor, x: torch.Tensor, x_lo: Optional[torch.Tensor] = None, n_splits: int = 0,
+              mode: str = "partials"):
+    """Y[t, n] = sum_k (X + Xlo)[t, k] W[n, k].
+    mode "partials": fp32 [S, T, n_out]; "bf16": (hi, lo) bf16 [T, n_out];
+    "swiglu": w rows interleaved gate|up per 64 -> (hi, lo) bf16 [T, n_out/2]."""
     _chk_bf16(w, "w"); _chk_bf16(x, "x")
+    if x_lo is not None:
+        _chk_bf16(x_lo, "x_lo")
     n_out, K = w.shape
     T = x.shape[0]
     assert x.shape[1] == K
     lib = N.load()
-    if out_bf16:
-        out = torch.empty(T, n_out, device=x.device, dtype=torch.bfloat16)
-        N.check(lib.ft_gemm_bf16(N.ptr(w), N.ptr(x), N.ptr(out), n_out, T, K, 1, 1, N.cur_stream()), "ft_gemm_bf16")
+    st = N.cur_stream()
+    if mode == "partials":
+        if n_splits <= 0:
+            n_splits = lib.ft_gemm_pick_splits(n_out, T, K, int(x_lo is not None))
+        out = torch.empty(n_splits, T, n_out, device=x.device, dtype=torch.float32)
+        N.check(lib.ft_gemm_bf16(N.ptr(w), N.ptr(x), N.ptr(x_lo), N.ptr(out), 0, n_out, T, K, n_splits, 0, st),
+                "ft_gemm_bf16")
         return out
-    if n_splits <= 0:
-        n_splits = lib.ft_gemm_pick_splits(n_out, T, K)
-    out = torch.empty(n_splits, T, n_out, device=x.device, dtype=torch.float32)
-    N.check(lib.ft_gemm_bf16(N.ptr(w), N.ptr(x), N.ptr(out), n_out, T, K, n_splits, 0, N.cur_stream()), "ft_gemm_bf16")
-    return out
+    width = n_out if mode == "bf16" else n_out // 2
+    out = torch.empty(T, width, device=x.device, dtype=torch.bfloat16)
+    out_lo = torch.empty_like(out)
+    N.check(lib.ft_gemm_bf16(N.ptr(w), N.ptr(x), N.ptr(x_lo), N.ptr(out), N.ptr(out_lo), n_out, T, K, 1,
+                             1 if mode == "bf16" else 2, st), "ft_gemm_bf16")
+    return out, out_lo
 
 
 def add_rmsnorm(resid: torch.Tensor, norm_w: torch.Tensor, eps: float, partials: Optional[torch.Tensor] = None,
                 embed_tokens: Optional[torch.Tensor] = None, embed_table: Optional[torch.Tensor] = None,
-                row_idx: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """In-place residual update + RMSNorm; returns bf16 xn [n_rows, h]."""
+                row_idx: Optional[torch.Tensor] = None):
+    """In-place residual update + RMSNorm; returns the bf16 (hi, lo) planes [n_rows, h]."""
     assert resid.dtype == torch.float32 and resid.is_contiguous()
     h = resid.shape[1]
     T = row_idx.numel() if row_idx is not None else resid.shape[0]
     xn = torch.empty(T, h, device=resid.device, dtype=torch.bfloat16)
+    xn_lo = torch.empty_like(xn)
     ns, stride = 0, 0
     if partials is not None:
         assert partials.dtype == torch.float32 and partials.is_contiguous()
         ns, stride = partials.shape[0], partials.stride(0)
     N.check(N.load().ft_add_rmsnorm(N.ptr(resid), N.ptr(partials), ns, stride, N.ptr(embed_tokens),
-                                    N.ptr(embed_table), N.ptr(norm_w), N.ptr(xn), N.ptr(row_idx), T, h,
-                                    eps, N.cur_stream()), "ft_add_rmsnorm")
-    return xn
+                                    N.ptr(embed_table), N.ptr(norm_w), N.ptr(xn), N.ptr(xn_lo), N.ptr(row_idx),
+                                    T, h, eps, N.cur_stream()), "ft_add_rmsnorm")
+    return xn, xn_lo
 
 
 def kv_cache_alloc(num_pages: int, nkv: int, d: int, device) -> torch.Tensor:
@@ -68,17 +86,18 @@ def rope_kv_append(qkv_partials: torch.Tensor, cos: torch.Tensor, sin: torch.Ten
     return q
 
 
-def silu_mul(gu_partials: torch.Tensor) -> torch.Tensor:
+def silu_mul(gu_partials: torch.Tensor):
     S, T, f2 = gu_partials.shape
     act = torch.empty(T, f2 // 2, device=gu_partials.device, dtype=torch.bfloat16)
-    N.check(N.load().ft_silu_mul(N.ptr(gu_partials), S, gu_partials.stride(0), N.ptr(act), T, f2 // 2,
-                                 N.cur_stream()), "ft_silu_mul")
-    return act
+    act_lo = torch.empty_like(act)
+    N.check(N.load().ft_silu_mul(N.ptr(gu_partials), S, gu_partials.stride(0), N.ptr(act), N.ptr(act_lo), T,
+                                 f2 // 2, N.cur_stream()), "ft_silu_mul")
+    return act, act_lo
 
 
 def attn_decode(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tensor, ctx_lens: torch.Tensor,
-                n_ctas: int = 0) -> torch.Tensor:
-    """q bf16 [B, nq, d] -> bf16 [B, nq*d]."""
+                n_ctas: int = 0):
+    """q bf16 [B, nq, d] -> bf16 (hi, lo) planes [B, nq*d]."""
     B, nq, d = q.shape
     nkv = kv_layer.shape[1]
     lib = N.load()
@@ -88,15 +107,16 @@ def attn_decode(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tenso
                           device=q.device, dtype=torch.float32)
     tile_prefix = torch.empty(B + 1, device=q.device, dtype=torch.int32)
     out = torch.empty(B, nq * d, device=q.device, dtype=torch.bfloat16)
+    out_lo = torch.empty_like(out)
     N.check(lib.ft_attn_decode(N.ptr(q), N.ptr(kv_layer), N.ptr(page_table), page_table.shape[1],
-                               N.ptr(ctx_lens), N.ptr(tile_prefix), N.ptr(out), N.ptr(scratch), B, nq, nkv, d,
-                               n_ctas, N.cur_stream()), "ft_attn_decode")
-    return out
+                               N.ptr(ctx_lens), N.ptr(tile_prefix), N.ptr(out), N.ptr(out_lo), N.ptr(scratch), B,
+                               nq, nkv, d, n_ctas, N.cur_stream()), "ft_attn_decode")
+    return out, out_lo
 
 
 def attn_prefill(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tensor, req_q_start, req_slot,
-                 req_pos0) -> torch.Tensor:
-    """q bf16 [T, nq, d]; request r owns rows req_q_start[r]:req_q_start[r+1]."""
+                 req_pos0):
+    """q bf16 [T, nq, d]; request r owns rows req_q_start[r]:req_q_start[r+1].  Returns (hi, lo)."""
     T, nq, d = q.shape
     nkv = kv_layer.shape[1]
     dev = q.device
@@ -107,10 +127,12 @@ def attn_prefill(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tens
     i32 = lambda v: torch.tensor(v, device=dev, dtype=torch.int32)
     t_qs, t_slot, t_pos0, t_treq, t_tq0 = i32(req_q_start), i32(req_slot), i32(req_pos0), i32(tile_req), i32(tile_q0)
     out = torch.zeros(T, nq * d, device=dev, dtype=torch.bfloat16)
+    out_lo = torch.zeros_like(out)
     N.check(N.load().ft_attn_prefill(N.ptr(q), N.ptr(kv_layer), N.ptr(page_table), page_table.shape[1],
                                      N.ptr(t_qs), N.ptr(t_slot), N.ptr(t_pos0), N.ptr(t_treq), N.ptr(t_tq0),
-                                     len(tile_req), N.ptr(out), nq, nkv, d, N.cur_stream()), "ft_attn_prefill")
-    return out
+                                     len(tile_req), N.ptr(out), N.ptr(out_lo), nq, nkv, d, N.cur_stream()),
+            "ft_attn_prefill")
+    return out, out_lo
 
 
 def sample(logits: torch.Tensor, temperature=None, top_k=None, top_p=None, seeds=None) -> torch.Tensor:

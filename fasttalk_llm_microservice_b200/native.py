@@ -65,15 +65,15 @@ SIGNATURES = {
     "ft_engine_timer": (_I, [_VP, _I, _VP]),
     "ft_engine_set_profile": (_I, [_VP, _I]),
     "ft_debug_prefill_logits": (_I, [_VP, _VP, _I, _I, _VP]),
-    "ft_gemm_bf16": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
-    "ft_gemm_pick_splits": (_I, [_I, _I, _I]),
-    "ft_add_rmsnorm": (_I, [_VP, _VP, _I, _LL, _VP, _VP, _VP, _VP, _VP, _I, _I, _F, _VP]),
+    "ft_gemm_bf16": (_I, [_VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
+    "ft_gemm_pick_splits": (_I, [_I, _I, _I, _I]),
+    "ft_add_rmsnorm": (_I, [_VP, _VP, _I, _LL, _VP, _VP, _VP, _VP, _VP, _VP, _I, _I, _F, _VP]),
     "ft_rope_kv_append": (_I, [_VP, _I, _LL, _VP, _VP, _VP, _VP, _VP, _I, _VP, _VP, _I, _I, _I, _I, _VP]),
-    "ft_silu_mul": (_I, [_VP, _I, _LL, _VP, _I, _I, _VP]),
+    "ft_silu_mul": (_I, [_VP, _I, _LL, _VP, _VP, _I, _I, _VP]),
     "ft_attn_decode_scratch_bytes": (_LL, [_I, _I, _I, _I, _I]),
     "ft_attn_decode_default_ctas": (_I, [_I]),
-    "ft_attn_decode": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
-    "ft_attn_prefill": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP, _I, _VP, _I, _I, _I, _VP]),
+    "ft_attn_decode": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
+    "ft_attn_prefill": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP, _I, _VP, _VP, _I, _I, _I, _VP]),
     "ft_sample": (_I, [_VP, _I, _I, _VP, _VP, _VP, _VP, _VP, _VP]),
 }
 

@@ -87,3 +87,15 @@ def rope_inv_freq(spec: ModelSpec) -> torch.Tensor:
     mid = (1 - smooth) * scaled / spec.rope_factor + smooth * scaled
     is_mid = (wl >= high_wl) & (wl <= low_wl)
     return torch.where(is_mid, mid, scaled)
+
+
+def interleave_gate_up(wgu: torch.Tensor) -> torch.Tensor:
+    """[..., 2f, h] rows (gate | up) -> rows interleaved in blocks of 64 (gate 64i.., up 64i..), the
+    layout the GEMM's fused SwiGLU epilogue reads (include/fasttalk_b200.h: ft_weights.wgu)."""
+    f2, h = wgu.shape[-2], wgu.shape[-1]
+    f = f2 // 2
+    assert f % 64 == 0, "ffn must be a multiple of 64"
+    lead = wgu.shape[:-2]
+    g = wgu[..., :f, :].reshape(*lead, f // 64, 1, 64, h)
+    u = wgu[..., f:, :].reshape(*lead, f // 64, 1, 64, h)
+    return torch.cat([g, u], dim=-3).reshape(*lead, f2, h).contiguous()

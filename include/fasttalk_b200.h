@@ -55,7 +55,8 @@ typedef struct {
     const void* wqkv;        /* [L, (nq + 2 nkv) * d, hidden]   rows: q | k | v */
     const void* wo;          /* [L, hidden, nq * d] */
     const void* mlp_norm;    /* [L, hidden] */
-    const void* wgu;         /* [L, 2 * ffn, hidden]            rows: gate | up */
+    const void* wgu;         /* [L, 2 * ffn, hidden]  rows interleaved in blocks of 64: gate rows
+                                64i..64i+63, then up rows 64i..64i+63 (for the fused SwiGLU epilogue) */
     const void* wd;          /* [L, hidden, ffn] */
     const float* rope_cos;   /* fp32 [max_context, d/2] */
     const float* rope_sin;   /* fp32 [max_context, d/2] */
@@ -119,18 +120,24 @@ int ft_debug_prefill_logits(ft_engine* e, const int* tokens, int n_tokens, int c
  * Kernel level — one entry point per kernel so each can be checked against the oracle.
  * ---------------------------------------------------------------------------------------- */
 
-/* K3: Y[t, n] = sum_k X[t, k] W[n, k]  (tcgen05/TMEM, TMA-fed).  out_mode 0: fp32 partial sums
- * out[split][T][n_out] (n_splits <= 0 picks a split count; ft_gemm_pick_splits tells which);
- * out_mode 1: bf16 out[T][n_out].  n_out % 128 == 0, K % 64 == 0. */
-int ft_gemm_bf16(const void* w, const void* x, void* out, int n_out, int T, int K, int n_splits,
-                 int out_mode, void* stream);
-int ft_gemm_pick_splits(int n_out, int T, int K);
+/* K3: Y[t, n] = sum_k (X[t, k] + Xlo[t, k]) W[n, k]  (tcgen05/TMEM, TMA-fed).  x_lo (may be NULL) is the
+ * bf16 residual plane of the activations: x = bf16(a), x_lo = bf16(a - x).
+ * out_mode 0: fp32 partial sums out[split][T][n_out] (n_splits <= 0 picks a split count;
+ *             ft_gemm_pick_splits tells which);
+ * out_mode 1: bf16 out[T][n_out] (+ residual plane out_lo if not NULL);
+ * out_mode 2: fused SwiGLU, w rows interleaved gate|up in blocks of 64 (see ft_weights.wgu):
+ *             out[T][n_out/2] = bf16(silu(g) * u) (+ out_lo).
+ * n_out % 128 == 0, K % 64 == 0. */
+int ft_gemm_bf16(const void* w, const void* x, const void* x_lo, void* out, void* out_lo, int n_out, int T,
+                 int K, int n_splits, int out_mode, void* stream);
+int ft_gemm_pick_splits(int n_out, int T, int K, int hilo);
 
 /* K1+K2: resid[r] (fp32) = embed[token[r]]  or  resid[r] += sum_s partials[s][r];
- * xn[i] = bf16(rmsnorm(resid[r]) * w), r = row_idx ? row_idx[i] : i. */
+ * y = rmsnorm(resid[r]) * w, r = row_idx ? row_idx[i] : i;  xn[i] = bf16(y), xn_lo[i] = bf16(y - xn[i])
+ * (xn_lo may be NULL). */
 int ft_add_rmsnorm(float* resid, const float* partials, int n_splits, long long split_stride,
                    const int* embed_tokens, const void* embed_table, const void* norm_w, void* xn_out,
-                   const int* row_idx, int T, int h, float eps, void* stream);
+                   void* xn_lo, const int* row_idx, int T, int h, float eps, void* stream);
 
 /* K4: split-K reduce of the fused QKV projection, RoPE on q and k (cos/sin tables fp32
  * [pos][d/2]), q -> bf16 [T][nq][d], k/v -> paged cache layer
@@ -140,25 +147,28 @@ int ft_rope_kv_append(const float* qkv, int n_splits, long long split_stride, co
                       const int* page_table, int max_pages, void* q_out, void* kv_layer, int T, int nq,
                       int nkv, int d, void* stream);
 
-/* SwiGLU: act[t][j] = bf16(silu(sum_s gu[s][t][j]) * sum_s gu[s][t][f+j]). */
-int ft_silu_mul(const float* gu, int n_splits, long long split_stride, void* act, int T, int f, void* stream);
+/* SwiGLU on un-interleaved partials: a = silu(sum_s gu[s][t][j]) * sum_s gu[s][t][f+j];
+ * act = bf16(a), act_lo = bf16(a - act) (may be NULL).  The engine uses the GEMM's fused epilogue. */
+int ft_silu_mul(const float* gu, int n_splits, long long split_stride, void* act, void* act_lo, int T, int f,
+                void* stream);
 
 /* K5: paged GQA decode attention, one query token per sequence.  q bf16 [B][nq][d],
- * out bf16 [B][nq*d].  `tile_prefix` (int32 [B+1]) and `scratch`
- * (ft_attn_decode_scratch_bytes) are device work buffers the call fills. */
+ * out bf16 [B][nq*d] (+ residual plane out_lo, may be NULL).  `tile_prefix` (int32 [B+1]) and
+ * `scratch` (ft_attn_decode_scratch_bytes) are device work buffers the call fills. */
 long long ft_attn_decode_scratch_bytes(int B, int nkv, int group, int d, int n_ctas);
 /* persistent grid size the engine uses: SM count x resident CTAs of the decode kernel */
 int ft_attn_decode_default_ctas(int d);
 int ft_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
-                   const int* ctx_lens, int* tile_prefix, void* out, float* scratch, int B, int nq, int nkv,
-                   int d, int n_ctas, void* stream);
+                   const int* ctx_lens, int* tile_prefix, void* out, void* out_lo, float* scratch, int B, int nq,
+                   int nkv, int d, int n_ctas, void* stream);
 
 /* K6: causal chunked-prefill attention over the paged cache.  Request r owns query rows
  * [req_q_start[r], req_q_start[r+1]) of q/out, page-table row req_slot[r], and its first query
  * sits at absolute position req_pos0[r].  Tiles (tile_req, tile_q0) enumerate 64-query blocks. */
 int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                     const int* req_q_start, const int* req_slot, const int* req_pos0, const int* tile_req,
-                    const int* tile_q0, int n_tiles, void* out, int nq, int nkv, int d, void* stream);
+                    const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq, int nkv, int d,
+                    void* stream);
 
 /* K7: per-row temperature / top-k / top-p sampling (argmax when temperature <= 0). */
 int ft_sample(const float* logits, int B, int V, const float* temperature, const int* top_k,

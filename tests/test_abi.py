@@ -40,9 +40,9 @@ def test_last_error_is_a_string(lib):
 
 def test_pick_splits_is_host_only(lib):
     # pure host arithmetic; falls back to 148 SMs when no device is present
-    s = lib.ft_gemm_pick_splits(3072, 64, 2048)
-    assert 1 <= s <= 16
-    assert lib.ft_gemm_pick_splits(128256, 64, 2048) == 1
+    s = lib.ft_gemm_pick_splits(3072, 64, 2048, 1)
+    assert 1 <= s <= 16 and 24 * s <= 148          # one wave of CTAs (gemm.cu: gemm_pick_splits)
+    assert lib.ft_gemm_pick_splits(128256, 64, 2048, 1) == 1
 
 
 def test_engine_refuses_without_gpu():

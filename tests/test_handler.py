@@ -11,7 +11,7 @@ import pytest
 from fasttalk_llm_microservice_b200.errors import LLMServiceError
 from fasttalk_llm_microservice_b200.handler import EngineRunner, NativeHandler
 from fasttalk_llm_microservice_b200.tokenizer import ByteTokenizer
-from tests.fake_engine import FakeEngine
+from fake_engine import FakeEngine
 
 REF = os.environ.get("FASTTALK_REFERENCE_PATH", "/root/reference")
 HAVE_REF = os.path.exists(os.path.join(REF, "app", "core", "vllm_handler.py"))
