@@ -17,6 +17,8 @@
 #include "common.cuh"
 #include "ft_internal.h"
 
+#include <mutex>
+
 namespace ft {
 
 constexpr int ATTN_COMPUTE_WARPS = 4;
@@ -665,4 +667,85 @@ extern "C" int ft_attn_prefill(const void* q, const void* kv_layer, const int* p
     return ft::launch_attn_prefill(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
                                    tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, d, false,
                                    static_cast<cudaStream_t>(stream));
+}
+
+// ------------------------------------------------------------------ decode attention without allocations
+// Some hosts hand this library device buffers but must not let it (or themselves) allocate while
+// they are serving: a voice pipeline whose GPU memory is carved up once at start-up (the
+// reference's deployment gives the engine a fixed share of the card, docker-compose.vllm.yml:44
+// `--gpu-memory-utilization`), or a latency-critical audio thread for which cudaMalloc's implicit
+// device-wide synchronisation is a dropout.  ft_attn_decode makes such callers bring their own
+// work buffers; ft_attn_decode_noalloc needs none: its tile-prefix table, per-segment arrival
+// counters and partial-result records live in the fixed array below, which every GPU that loads
+// this library carries from module load until the process exits (about 6.1 MiB).
+//
+// The array is one per device and is shared by every call: it still holds whatever the previous
+// call left in it.  Nothing is assumed about those contents — the planning kernel rewrites the
+// prefix table and zeroes the arrival counters at the start of every call, and partial records
+// are always written before they are read — but two calls that overlap on the same GPU
+// (different streams, or different host threads) would trample each other's counters and
+// records.  Issue them so that one finishes before the next starts.
+namespace ft {
+
+constexpr int NOALLOC_MAX_SEQS = 1024;        // B
+constexpr int NOALLOC_MAX_SEGMENTS = 1024;    // B * nkv
+constexpr int NOALLOC_MAX_CTAS = 512;
+constexpr size_t NOALLOC_SCRATCH_FLOATS =
+    NOALLOC_MAX_SEGMENTS + (size_t)(NOALLOC_MAX_CTAS + NOALLOC_MAX_SEGMENTS) * ATTN_GMAX * (128 + 2);
+constexpr size_t NOALLOC_PREFIX_INTS = NOALLOC_MAX_SEQS + 64;
+
+static __device__ __align__(256) float g_noalloc_scratch[NOALLOC_SCRATCH_FLOATS + NOALLOC_PREFIX_INTS];
+
+// In host code `g_noalloc_scratch` is only a handle for the device symbol, not an address a
+// kernel can use; the device address is looked up once per GPU, with that GPU current.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static float* g_noalloc_dev_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch_for_current_device(float** out) {
+    int dev = -1;
+    FT_CHECK_CUDA(cudaGetDevice(&dev));
+    FT_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "ft_attn_decode_noalloc: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_dev_ptr[dev]) {
+        float* p = nullptr;
+        FT_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch));
+        FT_REQUIRE(p != nullptr, "ft_attn_decode_noalloc: cudaGetSymbolAddress returned a null address");
+        g_noalloc_dev_ptr[dev] = p;
+    }
+    *out = g_noalloc_dev_ptr[dev];
+    return 0;
+}
+
+}  // namespace ft
+
+extern "C" int ft_attn_decode_noalloc(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                                      const int* ctx_lens, void* out, void* out_lo, int B, int nq, int nkv, int d,
+                                      int n_ctas, void* stream) {
+    using namespace ft;
+    FT_REQUIRE(q && kv_layer && page_table && ctx_lens && out, "ft_attn_decode_noalloc: null argument");
+    FT_REQUIRE(d == 64 || d == 128, "ft_attn_decode_noalloc: head_dim %d not supported (64 or 128)", d);
+    FT_REQUIRE(B >= 1 && nkv >= 1 && nq >= nkv, "ft_attn_decode_noalloc: bad shape B=%d nq=%d nkv=%d", B, nq, nkv);
+    if (n_ctas <= 0) {
+        n_ctas = ft_attn_decode_default_ctas(d);
+        if (n_ctas <= 0) return n_ctas;
+    }
+    FT_REQUIRE(B <= NOALLOC_MAX_SEQS && (long long)B * nkv <= NOALLOC_MAX_SEGMENTS && n_ctas <= NOALLOC_MAX_CTAS,
+               "ft_attn_decode_noalloc: B=%d, B*nkv=%lld, n_ctas=%d exceed the built-in work area "
+               "(at most %d sequences, %d (sequence, kv-head) pairs, %d CTAs); use ft_attn_decode with "
+               "caller-provided scratch for larger batches",
+               B, (long long)B * nkv, n_ctas, NOALLOC_MAX_SEQS, NOALLOC_MAX_SEGMENTS, NOALLOC_MAX_CTAS);
+    const size_t need = attn_decode_scratch_floats(B, nkv, nq / nkv, d, n_ctas);
+    FT_REQUIRE(need <= NOALLOC_SCRATCH_FLOATS,
+               "ft_attn_decode_noalloc: needs %zu floats of work area, the built-in one holds %zu", need,
+               (size_t)NOALLOC_SCRATCH_FLOATS);
+    float* scratch = nullptr;
+    if (int r = noalloc_scratch_for_current_device(&scratch)) return r;
+    int* tile_prefix = reinterpret_cast<int*>(scratch + NOALLOC_SCRATCH_FLOATS);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // the planning kernel rewrites the prefix table and zeroes the arrival counters: nothing a
+    // previous call left behind is relied upon
+    if (int r = launch_attn_decode_plan(ctx_lens, tile_prefix, B, nkv, scratch, false, st)) return r;
+    return launch_attn_decode(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo, scratch, B,
+                              nq, nkv, d, n_ctas, false, st, nullptr, nullptr);
 }

@@ -114,6 +114,20 @@ def attn_decode(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tenso
     return out, out_lo
 
 
+def attn_decode_noalloc(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tensor, ctx_lens: torch.Tensor,
+                        out: torch.Tensor, out_lo: torch.Tensor, n_ctas: int = 0) -> None:
+    """Decode attention for callers that may not allocate device memory while serving (fixed
+    start-up memory budget, real-time audio thread): the library's built-in work area replaces
+    the scratch buffers attn_decode() allocates, and the caller supplies `out` / `out_lo`
+    (bf16 [B, nq*d]) itself, so this call allocates nothing anywhere.  Calls on one GPU share
+    that work area: do not overlap them.  Raises NativeError beyond B*nkv = 1024 / n_ctas = 512."""
+    B, nq, d = q.shape
+    nkv = kv_layer.shape[1]
+    N.check(N.load().ft_attn_decode_noalloc(N.ptr(q), N.ptr(kv_layer), N.ptr(page_table), page_table.shape[1],
+                                            N.ptr(ctx_lens), N.ptr(out), N.ptr(out_lo), B, nq, nkv, d, n_ctas,
+                                            N.cur_stream()), "ft_attn_decode_noalloc")
+
+
 def attn_prefill(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tensor, req_q_start, req_slot,
                  req_pos0):
     """q bf16 [T, nq, d]; request r owns rows req_q_start[r]:req_q_start[r+1].  Returns (hi, lo)."""

@@ -162,6 +162,23 @@ int ft_attn_decode(const void* q, const void* kv_layer, const int* page_table, i
                    const int* ctx_lens, int* tile_prefix, void* out, void* out_lo, float* scratch, int B, int nq,
                    int nkv, int d, int n_ctas, void* stream);
 
+/* K5 without allocations — no counterpart in the reference (its engines sit behind HTTP and own
+ * their memory).  Same computation as ft_attn_decode for hosts that must not allocate device
+ * memory while serving (GPU memory carved up once at start-up; real-time audio threads where
+ * cudaMalloc's device-wide synchronisation is a dropout): the tile-prefix table, arrival counters
+ * and partial-result records live in a fixed ~6.1 MiB array inside the library, present on every
+ * GPU that loads it until the process exits.  The caller passes only inputs and outputs.
+ * Limits: B <= 1024 sequences, B * nkv <= 1024, n_ctas <= 512 (n_ctas <= 0 picks the default);
+ * anything larger is refused with an error — use ft_attn_decode with your own scratch instead.
+ * The first call on each GPU looks up the array's device address (cudaGetSymbolAddress, with
+ * that GPU current); make that first call before starting any stream capture.  No cudaMalloc /
+ * cudaFree / allocating library routine is called.  All calls on a GPU share the one array and
+ * it keeps the previous call's contents: every call re-initialises what it needs (prefix table,
+ * zeroed counters), but calls that overlap in time on the same GPU race on it — serialise them. */
+int ft_attn_decode_noalloc(const void* q, const void* kv_layer, const int* page_table, int max_pages,
+                           const int* ctx_lens, void* out, void* out_lo, int B, int nq, int nkv, int d,
+                           int n_ctas, void* stream);
+
 /* K6: causal chunked-prefill attention over the paged cache.  Request r owns query rows
  * [req_q_start[r], req_q_start[r+1]) of q/out, page-table row req_slot[r], and its first query
  * sits at absolute position req_pos0[r].  Tiles (tile_req, tile_q0) enumerate 64-query blocks. */
