@@ -99,6 +99,65 @@ add_rmsnorm_kernel(float* __restrict__ resid, const float* __restrict__ partials
     }
 }
 
+// ------------------------------------------------------------------ norm-deferred pipeline entry / row gather
+// resid[t] = embed[token[t]];  planes = hi/lo(resid * gamma);  ssq[0][t] = sum resid^2, ssq[p>0][t] = 0
+__global__ void __launch_bounds__(NORM_THREADS)
+embed_planes_kernel(const int* __restrict__ tokens, const __nv_bfloat16* __restrict__ embed,
+                    const __nv_bfloat16* __restrict__ gamma, float* __restrict__ resid,
+                    __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo,
+                    float* __restrict__ ssq, int ssq_parts, int ssq_stride, int h) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int t = blockIdx.x;
+    const int nv = h >> 2;
+    const __nv_bfloat16* erow = embed + (size_t)tokens[t] * h;
+    float ss = 0.f;
+    for (int c = threadIdx.x; c < nv; c += NORM_THREADS) {
+        const uint2 e = *reinterpret_cast<const uint2*>(erow + c * 4);
+        const uint2 g = *reinterpret_cast<const uint2*>(gamma + c * 4);
+        const float4 x = make_float4(bf16_lo(e.x), bf16_hi(e.x), bf16_lo(e.y), bf16_hi(e.y));
+        reinterpret_cast<float4*>(resid + (size_t)t * h)[c] = x;
+        ss += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+        const float y0 = x.x * bf16_lo(g.x), y1 = x.y * bf16_hi(g.x), y2 = x.z * bf16_lo(g.y), y3 = x.w * bf16_hi(g.y);
+        uint2 o, l;
+        o.x = pack_bf16(y0, y1);
+        o.y = pack_bf16(y2, y3);
+        l.x = pack_bf16(y0 - bf16_lo(o.x), y1 - bf16_hi(o.x));
+        l.y = pack_bf16(y2 - bf16_lo(o.y), y3 - bf16_hi(o.y));
+        *reinterpret_cast<uint2*>(out + (size_t)t * h + c * 4) = o;
+        *reinterpret_cast<uint2*>(out_lo + (size_t)t * h + c * 4) = l;
+    }
+    __shared__ float red[NORM_THREADS / 32];
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x < ssq_parts) {
+        float tot = 0.f;
+        if (threadIdx.x == 0)
+            for (int k = 0; k < NORM_THREADS / 32; ++k) tot += red[k];
+        ssq[(size_t)threadIdx.x * ssq_stride + t] = tot;
+    }
+}
+
+// out[i] = x[row_idx[i]] for both planes, and the rows' sums of squares.
+__global__ void __launch_bounds__(NORM_THREADS)
+gather_planes_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x_lo,
+                     const float* __restrict__ ssq, int ssq_parts, int ssq_stride,
+                     const int* __restrict__ row_idx, int h, __nv_bfloat16* __restrict__ out,
+                     __nv_bfloat16* __restrict__ out_lo, float* __restrict__ ssq_out, int ssq_out_stride) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int i = blockIdx.x;
+    const int r = row_idx[i];
+    const int nv = h >> 3;              // 16-byte chunks
+    for (int c = threadIdx.x; c < nv; c += NORM_THREADS) {
+        reinterpret_cast<uint4*>(out + (size_t)i * h)[c] = reinterpret_cast<const uint4*>(x + (size_t)r * h)[c];
+        reinterpret_cast<uint4*>(out_lo + (size_t)i * h)[c] = reinterpret_cast<const uint4*>(x_lo + (size_t)r * h)[c];
+    }
+    if (threadIdx.x < ssq_parts)
+        ssq_out[(size_t)threadIdx.x * ssq_out_stride + i] = __ldcg(ssq + (size_t)threadIdx.x * ssq_stride + r);
+}
+
 // ------------------------------------------------------------------ K4
 // One warp per (token, head) of the fused QKV projection output:
 //   q heads : reduce partials, RoPE (rotate_half pairs i, i+d/2), write bf16 q[t][head][d]
@@ -259,6 +318,34 @@ int launch_rope_kv_append(const float* qkv, int n_splits, size_t split_stride, c
     return 0;
 }
 
+int launch_embed_planes(const int* tokens, const void* embed, const void* gamma, float* resid, void* out,
+                        void* out_lo, float* ssq, int ssq_parts, int ssq_stride, int T, int h, bool pdl,
+                        cudaStream_t stream) {
+    FT_REQUIRE(h % 4 == 0 && ssq_parts >= 1 && ssq_parts <= NORM_THREADS && T >= 1,
+               "embed_planes: bad shape h=%d parts=%d T=%d", h, ssq_parts, T);
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    fill_cfg(cfg, attr, dim3(T), dim3(NORM_THREADS), 0, pdl, stream);
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, embed_planes_kernel, tokens, (const __nv_bfloat16*)embed,
+                                     (const __nv_bfloat16*)gamma, resid, (__nv_bfloat16*)out,
+                                     (__nv_bfloat16*)out_lo, ssq, ssq_parts, ssq_stride, h));
+    return 0;
+}
+
+int launch_gather_planes(const void* x, const void* x_lo, const float* ssq, int ssq_parts, int ssq_stride,
+                         const int* row_idx, int n_rows, int h, void* out, void* out_lo, float* ssq_out,
+                         int ssq_out_stride, bool pdl, cudaStream_t stream) {
+    FT_REQUIRE(h % 8 == 0 && ssq_parts >= 1 && ssq_parts <= NORM_THREADS && n_rows >= 1,
+               "gather_planes: bad shape h=%d parts=%d rows=%d", h, ssq_parts, n_rows);
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    fill_cfg(cfg, attr, dim3(n_rows), dim3(NORM_THREADS), 0, pdl, stream);
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gather_planes_kernel, (const __nv_bfloat16*)x,
+                                     (const __nv_bfloat16*)x_lo, ssq, ssq_parts, ssq_stride, row_idx, h,
+                                     (__nv_bfloat16*)out, (__nv_bfloat16*)out_lo, ssq_out, ssq_out_stride));
+    return 0;
+}
+
 int launch_silu_mul(const float* gu, int n_splits, size_t split_stride, void* act, void* act_lo, int T,
                     int f, bool pdl, cudaStream_t stream) {
     FT_REQUIRE(f % 4 == 0, "silu_mul: f=%d must be a multiple of 4", f);
@@ -292,6 +379,20 @@ extern "C" int ft_rope_kv_append(const float* qkv, int n_splits, long long split
     return ft::launch_rope_kv_append(qkv, n_splits, (size_t)split_stride, cos_t, sin_t, positions,
                                      seq_slots, page_table, max_pages, q_out, kv_layer, T, nq, nkv, d,
                                      false, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ft_embed_planes(const int* tokens, const void* embed_table, const void* gamma, float* resid,
+                               void* out, void* out_lo, float* ssq, int ssq_parts, int ssq_stride, int T, int h,
+                               void* stream) {
+    return ft::launch_embed_planes(tokens, embed_table, gamma, resid, out, out_lo, ssq, ssq_parts, ssq_stride, T,
+                                   h, false, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ft_gather_planes(const void* x, const void* x_lo, const float* ssq, int ssq_parts, int ssq_stride,
+                                const int* row_idx, int n_rows, int h, void* out, void* out_lo, float* ssq_out,
+                                int ssq_out_stride, void* stream) {
+    return ft::launch_gather_planes(x, x_lo, ssq, ssq_parts, ssq_stride, row_idx, n_rows, h, out, out_lo, ssq_out,
+                                    ssq_out_stride, false, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int ft_silu_mul(const float* gu, int n_splits, long long split_stride, void* act, void* act_lo,

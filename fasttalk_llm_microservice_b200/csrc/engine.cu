@@ -79,8 +79,9 @@ struct Engine {
     // device buffers
     uint8_t* kv = nullptr;
     float* resid = nullptr;
-    float* part = nullptr;
-    size_t part_floats = 0;
+    float* ssq = nullptr;          // [ssq_parts][t_max] partial sums of squares of the residual rows
+    float* ssq_last = nullptr;     // [ssq_parts][rows_last] gathered for the LM-head rows
+    int ssq_parts = 0, rows_last = 0;
     // bf16 activations feeding the GEMMs are kept as hi + lo planes (see gemm.cu)
     void *xn = nullptr, *q = nullptr, *attn_out = nullptr, *act = nullptr, *xn_last = nullptr;
     void *xn_lo = nullptr, *attn_out_lo = nullptr, *act_lo = nullptr, *xn_last_lo = nullptr;
@@ -173,6 +174,7 @@ struct Batch {
     int n_prefill_req = 0;
     int n_tiles = 0;                  // prefill attention q tiles
     int n_logit_rows = 0;
+    bool logit_rows_identity = false; // logits wanted for rows 0..n_logit_rows-1 exactly (no gather)
 };
 
 #define FT_TRY(x)                                   \
@@ -181,16 +183,22 @@ struct Batch {
         if (_r) return _r;                          \
     } while (0)
 
+// One projection with a fused epilogue.  `staged` epilogues (RESID / QKV_ROPE) split K across
+// a thread-block cluster; the others run unsplit.
 static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, const CUtensorMap* xmaps_lo,
-                    int T, int n_out, int K, void* out, int* splits_out) {
+                    int T, int n_out, int K, const ft_gemm_epilogue& epi) {
     const int bn = gemm_pick_bn(T, true);
-    const int splits = gemm_pick_splits(n_out, T, K, e->sms, true);
-    *splits_out = splits;
+    const bool staged = epi.mode == FT_EPI_RESID || epi.mode == FT_EPI_QKV_ROPE;
+    const int splits = staged ? gemm_pick_cluster_splits(n_out, T, K, e->sms) : 1;
     e->st.kernel_launches++;
-    return launch_gemm(mw, xmaps[bn_index(bn)], &xmaps_lo[bn_index(bn)], bn, out, nullptr, n_out, T, K, splits,
-                       0, e->pdl, e->stream);
+    return launch_gemm(mw, xmaps[bn_index(bn)], &xmaps_lo[bn_index(bn)], bn, n_out, T, K, splits, epi, e->pdl,
+                       e->stream);
 }
 
+// The norm-deferred layer chain (5 kernels per layer):
+//   QKV GEMM [x 1/rms, RoPE, KV append] -> attention -> O GEMM [resid +=, planes = resid*gamma_mlp, ssq]
+//   -> gate/up GEMM [x 1/rms, SwiGLU] -> down GEMM [resid +=, planes = resid*gamma_next, ssq]
+// `xn` planes always hold resid * gamma of the NEXT norm; `ssq` its per-row-tile sums of squares.
 static int forward(Engine* e, const Batch& b) {
     const ft_engine_config& c = e->cfg;
     StepMeta& m = e->meta;
@@ -200,22 +208,38 @@ static int forward(Engine* e, const Batch& b) {
     auto bf16_off = [](const void* p, size_t elems) {
         return (const void*)((const uint8_t*)p + elems * 2);
     };
-    FT_TRY(launch_add_rmsnorm(e->resid, nullptr, 0, 0, d + m.o_tokens, e->w.embed, e->w.attn_norm, e->xn,
-                              e->xn_lo, nullptr, T, c.hidden, c.rms_eps, e->pdl, e->stream));
+    FT_TRY(launch_embed_planes(d + m.o_tokens, e->w.embed, e->w.attn_norm, e->resid, e->xn, e->xn_lo, e->ssq,
+                               e->ssq_parts, e->t_max, T, c.hidden, e->pdl, e->stream));
     e->st.kernel_launches++;
     if (b.n_decode > 0) {
         FT_TRY(launch_attn_decode_plan(d + m.o_ctx, d + m.o_tprefix, b.n_decode, c.n_kv_heads, e->attn_scratch,
                                        e->pdl, e->stream));
         e->st.kernel_launches++;
     }
-    int s = 0;
+    ft_gemm_epilogue rstd = {};            // fields shared by every epilogue that applies 1/rms
+    rstd.ssq_in = e->ssq;
+    rstd.ssq_parts = e->ssq_parts;
+    rstd.ssq_stride = e->t_max;
+    rstd.inv_h = 1.f / (float)c.hidden;
+    rstd.eps = c.rms_eps;
     for (int l = 0; l < c.layers; ++l) {
         uint8_t* kv_l = e->kv + (size_t)l * e->kv_layer_bytes;
-        FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, e->m_xn_lo, T, e->qkv_dim, c.hidden, e->part, &s));
-        FT_TRY(launch_rope_kv_append(e->part, s, (size_t)T * e->qkv_dim, e->w.rope_cos, e->w.rope_sin,
-                                     d + m.o_pos, d + m.o_rows, d + m.o_pt, e->max_pages, e->q, kv_l, T,
-                                     c.n_q_heads, c.n_kv_heads, c.head_dim, e->pdl, e->stream));
-        e->st.kernel_launches++;
+        {
+            ft_gemm_epilogue ep = rstd;
+            ep.mode = FT_EPI_QKV_ROPE;
+            ep.rope_cos = e->w.rope_cos;
+            ep.rope_sin = e->w.rope_sin;
+            ep.positions = d + m.o_pos;
+            ep.seq_rows = d + m.o_rows;
+            ep.page_table = d + m.o_pt;
+            ep.max_pages = e->max_pages;
+            ep.q_out = e->q;
+            ep.kv_layer = kv_l;
+            ep.nq = c.n_q_heads;
+            ep.nkv = c.n_kv_heads;
+            ep.head_dim = c.head_dim;
+            FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, e->m_xn_lo, T, e->qkv_dim, c.hidden, ep));
+        }
         if (b.n_decode > 0) {
             cudaEvent_t ev0 = nullptr, ev1 = nullptr;
             if (e->profile) {
@@ -235,34 +259,54 @@ static int forward(Engine* e, const Batch& b) {
                                        e->stream));
             e->st.kernel_launches++;
         }
-        FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, e->m_attn_lo, T, c.hidden, e->q_dim, e->part, &s));
-        FT_TRY(launch_add_rmsnorm(e->resid, e->part, s, (size_t)T * H, nullptr, nullptr,
-                                  bf16_off(e->w.mlp_norm, (size_t)l * H), e->xn, e->xn_lo, nullptr, T, c.hidden,
-                                  c.rms_eps, e->pdl, e->stream));
-        e->st.kernel_launches++;
-        {   // gate/up projection with the SwiGLU fused into the epilogue: act = silu(g) * u
-            const int bn = gemm_pick_bn(T, true);
-            FT_TRY(launch_gemm(e->m_wgu[l], e->m_xn[bn_index(bn)], &e->m_xn_lo[bn_index(bn)], bn, e->act,
-                               e->act_lo, 2 * c.ffn, T, c.hidden, 1, 2, e->pdl, e->stream));
-            e->st.kernel_launches++;
+        {
+            ft_gemm_epilogue ep = {};
+            ep.mode = FT_EPI_RESID;
+            ep.resid = e->resid;
+            ep.gamma = bf16_off(e->w.mlp_norm, (size_t)l * H);
+            ep.out = e->xn;
+            ep.out_lo = e->xn_lo;
+            ep.ssq_out = e->ssq;
+            ep.ssq_stride = e->t_max;
+            FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, e->m_attn_lo, T, c.hidden, e->q_dim, ep));
         }
-        FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, e->m_act_lo, T, c.hidden, c.ffn, e->part, &s));
-        if (l + 1 < c.layers) {
-            FT_TRY(launch_add_rmsnorm(e->resid, e->part, s, (size_t)T * H, nullptr, nullptr,
-                                      bf16_off(e->w.attn_norm, (size_t)(l + 1) * H), e->xn, e->xn_lo, nullptr, T,
-                                      c.hidden, c.rms_eps, e->pdl, e->stream));
-            e->st.kernel_launches++;
+        {   // gate/up projection: 1/rms and SwiGLU in the epilogue, act = silu(g) * u
+            ft_gemm_epilogue ep = rstd;
+            ep.mode = FT_EPI_SWIGLU;
+            ep.out = e->act;
+            ep.out_lo = e->act_lo;
+            FT_TRY(run_gemm(e, e->m_wgu[l], e->m_xn, e->m_xn_lo, T, 2 * c.ffn, c.hidden, ep));
+        }
+        {
+            ft_gemm_epilogue ep = {};
+            ep.mode = FT_EPI_RESID;
+            ep.resid = e->resid;
+            ep.gamma = l + 1 < c.layers ? bf16_off(e->w.attn_norm, (size_t)(l + 1) * H) : e->w.final_norm;
+            ep.out = e->xn;
+            ep.out_lo = e->xn_lo;
+            ep.ssq_out = e->ssq;
+            ep.ssq_stride = e->t_max;
+            FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, e->m_act_lo, T, c.hidden, c.ffn, ep));
         }
     }
     if (b.n_logit_rows > 0) {
-        FT_TRY(launch_add_rmsnorm(e->resid, e->part, s, (size_t)T * H, nullptr, nullptr, e->w.final_norm,
-                                  e->xn_last, e->xn_last_lo, d + m.o_lrow, b.n_logit_rows, c.hidden, c.rms_eps,
-                                  e->pdl, e->stream));
-        e->st.kernel_launches++;
-        const int bn = gemm_pick_bn(b.n_logit_rows, true);
-        e->st.kernel_launches++;
-        FT_TRY(launch_gemm(e->m_lm, e->m_last[bn_index(bn)], &e->m_last_lo[bn_index(bn)], bn, e->logits, nullptr,
-                           c.vocab, b.n_logit_rows, c.hidden, 1, 0, e->pdl, e->stream));
+        // LM head on the rows that need logits (all of them in a pure decode step)
+        const CUtensorMap* xm = e->m_xn;
+        const CUtensorMap* xl = e->m_xn_lo;
+        ft_gemm_epilogue ep = rstd;
+        ep.mode = FT_EPI_LOGITS;
+        ep.out = e->logits;
+        if (!b.logit_rows_identity) {
+            FT_TRY(launch_gather_planes(e->xn, e->xn_lo, e->ssq, e->ssq_parts, e->t_max, d + m.o_lrow,
+                                        b.n_logit_rows, c.hidden, e->xn_last, e->xn_last_lo, e->ssq_last,
+                                        e->rows_last, e->pdl, e->stream));
+            e->st.kernel_launches++;
+            xm = e->m_last;
+            xl = e->m_last_lo;
+            ep.ssq_in = e->ssq_last;
+            ep.ssq_stride = e->rows_last;
+        }
+        FT_TRY(run_gemm(e, e->m_lm, xm, xl, b.n_logit_rows, c.vocab, c.hidden, ep));
     }
     return 0;
 }
@@ -392,6 +436,7 @@ static int engine_step(Engine* e) {
     b.T = row;
     b.n_tiles = tiles;
     b.n_logit_rows = lrow;
+    b.logit_rows_identity = lrow == b.T && b.n_prefill_req == 0;      // pure decode: row i wants logits row i
     // sampling parameters per logit row
     float* hf = reinterpret_cast<float*>(h);
     unsigned long long* hseed = reinterpret_cast<unsigned long long*>(h + m.o_seed);
@@ -519,15 +564,16 @@ static int engine_init(Engine* e) {
     FT_TRY(alloc_zero(&e->act_lo, T * c.ffn * 2));
     FT_TRY(alloc_zero(&e->xn_last, rows_last * c.hidden * 2));
     FT_TRY(alloc_zero(&e->xn_last_lo, rows_last * c.hidden * 2));
-    // split-K partial sums: worst case over the four projections and every token count
-    size_t pf = 0;
-    const int widths[3] = {e->qkv_dim, c.hidden, c.hidden};      // QKV, O, down (gate/up never splits)
-    const int ks[3] = {c.hidden, e->q_dim, c.ffn};
-    for (int t = 1; t <= e->t_max; ++t)
-        for (int i = 0; i < 3; ++i)
-            pf = std::max(pf, (size_t)gemm_pick_splits(widths[i], t, ks[i], e->sms, true) * t * widths[i]);
-    e->part_floats = pf;
-    FT_CHECK_CUDA(cudaMalloc(&e->part, pf * 4));
+    // per-row-tile sums of squares of the residual rows (RMSNorm statistics, see forward())
+    e->ssq_parts = c.hidden / 128;
+    e->rows_last = (int)rows_last;
+    {
+        void* p = nullptr;
+        FT_TRY(alloc_zero(&p, (size_t)e->ssq_parts * T * 4));
+        e->ssq = static_cast<float*>(p);
+        FT_TRY(alloc_zero(&p, (size_t)e->ssq_parts * rows_last * 4));
+        e->ssq_last = static_cast<float*>(p);
+    }
 
     // decode attention: persistent grid = SMs x resident CTAs
     {
@@ -598,7 +644,7 @@ static void engine_free(Engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     for (auto& kv : e->sessions) delete kv.second;
     for (auto& kv : e->requests) delete kv.second;
-    cudaFree(e->kv); cudaFree(e->resid); cudaFree(e->part); cudaFree(e->xn); cudaFree(e->q);
+    cudaFree(e->kv); cudaFree(e->resid); cudaFree(e->ssq); cudaFree(e->ssq_last); cudaFree(e->xn); cudaFree(e->q);
     cudaFree(e->attn_out); cudaFree(e->act); cudaFree(e->xn_last); cudaFree(e->logits);
     cudaFree(e->xn_lo); cudaFree(e->attn_out_lo); cudaFree(e->act_lo); cudaFree(e->xn_last_lo);
     cudaFree(e->attn_scratch); cudaFree(e->meta.d);
@@ -806,6 +852,7 @@ extern "C" int ft_debug_prefill_logits(ft_engine* h, const int* tokens, int n, i
         const int len = std::min(chunk, n - p0);
         Batch b;
         b.n_decode = 0; b.T = len; b.n_req = 1; b.n_prefill_req = 1; b.n_logit_rows = len;
+        b.logit_rows_identity = true;
         layout_step(m, 1, e->max_pages, len);
         for (int k = 0; k < len; ++k) {
             hh[m.o_tokens + k] = tokens[p0 + k];

@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/fasttalk_b200.h"
+
 namespace ft {
 
 constexpr int GEMM_MAX_SPLITS = 16;
@@ -13,11 +15,12 @@ constexpr int GEMM_MAX_SPLITS = 16;
 int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int box_rows);
 int gemm_pick_bn(int T, bool hilo);
 int gemm_pick_splits(int n_out, int T, int K, int num_sms, bool hilo);
-// out_mode 0: fp32 partials [split][T][n_out]; 1: bf16 [T][n_out] (+ lo plane); 2: fused SwiGLU
-// (weight rows interleaved gate/up in blocks of 64) -> bf16 [T][n_out/2] (+ lo plane)
-int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap* mx_lo, int bn, void* out,
-                void* out_lo, int n_out, int T, int K, int splits, int out_mode, bool pdl,
-                cudaStream_t stream);
+// split count for the cluster-reduced epilogues (FT_EPI_RESID / FT_EPI_QKV_ROPE): <= 8, all
+// clusters of the grid resident at once
+int gemm_pick_cluster_splits(int n_out, int T, int K, int num_sms);
+// Modes and fields: ft_gemm_epilogue in include/fasttalk_b200.h.
+int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap* mx_lo, int bn, int n_out,
+                int T, int K, int splits, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream);
 
 // ---- elementwise.cu
 int launch_add_rmsnorm(float* resid, const float* partials, int n_splits, size_t split_stride,
@@ -28,6 +31,12 @@ int launch_rope_kv_append(const float* qkv, int n_splits, size_t split_stride, c
                           const float* sin_t, const int* positions, const int* seq_slots,
                           const int* page_table, int max_pages, void* q_out, void* kv_layer, int T,
                           int nq, int nkv, int d, bool pdl, cudaStream_t stream);
+int launch_embed_planes(const int* tokens, const void* embed, const void* gamma, float* resid, void* out,
+                        void* out_lo, float* ssq, int ssq_parts, int ssq_stride, int T, int h, bool pdl,
+                        cudaStream_t stream);
+int launch_gather_planes(const void* x, const void* x_lo, const float* ssq, int ssq_parts, int ssq_stride,
+                         const int* row_idx, int n_rows, int h, void* out, void* out_lo, float* ssq_out,
+                         int ssq_out_stride, bool pdl, cudaStream_t stream);
 int launch_silu_mul(const float* gu, int n_splits, size_t split_stride, void* act, void* act_lo, int T,
                     int f, bool pdl, cudaStream_t stream);
 

@@ -50,6 +50,46 @@ def gemm_bf16(w: torch.Tensor, x: torch.Tensor, x_lo: Optional[torch.Tensor] = N
     return out, out_lo
 
 
+def gemm_fused(w: torch.Tensor, x: torch.Tensor, x_lo: torch.Tensor, mode: int, n_splits: int = 0, **f) -> None:
+    """ft_gemm_fused with an ft_gemm_epilogue built from keyword tensors / scalars (see
+    include/fasttalk_b200.h).  Outputs are whatever tensors the caller put in the epilogue."""
+    import ctypes as C
+    _chk_bf16(w, "w"); _chk_bf16(x, "x"); _chk_bf16(x_lo, "x_lo")
+    n_out, K = w.shape
+    T = x.shape[0]
+    ep = N.GemmEpilogue()
+    ep.mode = mode
+    for name, _ in N.GemmEpilogue._fields_:
+        if name == "mode" or name not in f:
+            continue
+        v = f[name]
+        setattr(ep, name, v.data_ptr() if isinstance(v, torch.Tensor) else v)
+    N.check(N.load().ft_gemm_fused(N.ptr(w), N.ptr(x), N.ptr(x_lo), n_out, T, K, n_splits, C.byref(ep),
+                                   N.cur_stream()), "ft_gemm_fused")
+
+
+def embed_planes(tokens: torch.Tensor, table: torch.Tensor, gamma: torch.Tensor, ssq_parts: int):
+    """resid = table[tokens] (fp32); planes = hi/lo(resid * gamma); ssq [parts, T]."""
+    T, h = tokens.numel(), table.shape[1]
+    resid = torch.empty(T, h, device=table.device, dtype=torch.float32)
+    hi = torch.empty(T, h, device=table.device, dtype=torch.bfloat16)
+    lo = torch.empty_like(hi)
+    ssq = torch.empty(ssq_parts, T, device=table.device, dtype=torch.float32)
+    N.check(N.load().ft_embed_planes(N.ptr(tokens), N.ptr(table), N.ptr(gamma), N.ptr(resid), N.ptr(hi), N.ptr(lo),
+                                     N.ptr(ssq), ssq_parts, T, T, h, N.cur_stream()), "ft_embed_planes")
+    return resid, hi, lo, ssq
+
+
+def gather_planes(x: torch.Tensor, x_lo: torch.Tensor, ssq: torch.Tensor, row_idx: torch.Tensor):
+    n, h = row_idx.numel(), x.shape[1]
+    hi = torch.empty(n, h, device=x.device, dtype=torch.bfloat16)
+    lo = torch.empty_like(hi)
+    so = torch.empty(ssq.shape[0], n, device=x.device, dtype=torch.float32)
+    N.check(N.load().ft_gather_planes(N.ptr(x), N.ptr(x_lo), N.ptr(ssq), ssq.shape[0], ssq.stride(0), N.ptr(row_idx),
+                                      n, h, N.ptr(hi), N.ptr(lo), N.ptr(so), n, N.cur_stream()), "ft_gather_planes")
+    return hi, lo, so
+
+
 def add_rmsnorm(resid: torch.Tensor, norm_w: torch.Tensor, eps: float, partials: Optional[torch.Tensor] = None,
                 embed_tokens: Optional[torch.Tensor] = None, embed_table: Optional[torch.Tensor] = None,
                 row_idx: Optional[torch.Tensor] = None):

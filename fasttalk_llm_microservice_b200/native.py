@@ -49,6 +49,21 @@ class EngineStats(C.Structure):
     ]
 
 
+class GemmEpilogue(C.Structure):
+    """ft_gemm_epilogue (include/fasttalk_b200.h)."""
+    _fields_ = [
+        ("mode", C.c_int), ("out", C.c_void_p), ("out_lo", C.c_void_p), ("resid", C.c_void_p),
+        ("gamma", C.c_void_p), ("ssq_out", C.c_void_p), ("ssq_in", C.c_void_p),
+        ("ssq_parts", C.c_int), ("ssq_stride", C.c_int), ("inv_h", C.c_float), ("eps", C.c_float),
+        ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p), ("positions", C.c_void_p),
+        ("seq_rows", C.c_void_p), ("page_table", C.c_void_p), ("max_pages", C.c_int),
+        ("q_out", C.c_void_p), ("kv_layer", C.c_void_p),
+        ("nq", C.c_int), ("nkv", C.c_int), ("head_dim", C.c_int),
+    ]
+
+
+EPI_PARTIAL, EPI_BF16, EPI_SWIGLU, EPI_RESID, EPI_QKV_ROPE, EPI_LOGITS = range(6)
+
 # name -> (restype, argtypes); every symbol include/fasttalk_b200.h declares
 _VP, _I, _LL, _F, _ULL = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong
 SIGNATURES = {
@@ -67,6 +82,9 @@ SIGNATURES = {
     "ft_debug_prefill_logits": (_I, [_VP, _VP, _I, _I, _VP]),
     "ft_gemm_bf16": (_I, [_VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
     "ft_gemm_pick_splits": (_I, [_I, _I, _I, _I]),
+    "ft_gemm_fused": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, _VP, _VP]),
+    "ft_embed_planes": (_I, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _VP]),
+    "ft_gather_planes": (_I, [_VP, _VP, _VP, _I, _I, _VP, _I, _I, _VP, _VP, _VP, _I, _VP]),
     "ft_add_rmsnorm": (_I, [_VP, _VP, _I, _LL, _VP, _VP, _VP, _VP, _VP, _VP, _I, _I, _F, _VP]),
     "ft_rope_kv_append": (_I, [_VP, _I, _LL, _VP, _VP, _VP, _VP, _VP, _I, _VP, _VP, _I, _I, _I, _I, _VP]),
     "ft_silu_mul": (_I, [_VP, _I, _LL, _VP, _VP, _I, _I, _VP]),

@@ -132,6 +132,53 @@ int ft_gemm_bf16(const void* w, const void* x, const void* x_lo, void* out, void
                  int K, int n_splits, int out_mode, void* stream);
 int ft_gemm_pick_splits(int n_out, int T, int K, int hilo);
 
+/* K3 with the fused epilogues the engine uses.  RMSNorm is applied AFTER the projection: the
+ * activation planes hold resid * gamma (un-normalised), the per-token 1/rms is a scalar that
+ * commutes with the GEMM, so it is applied in the consumer's epilogue from per-row-tile partial
+ * sums of squares.  This removes every stand-alone norm / RoPE kernel from the decode chain.
+ *   FT_EPI_SWIGLU  (2): as out_mode 2, gate and up scaled by rstd[t] first (ssq_in may be NULL)
+ *   FT_EPI_RESID   (3): split-K partial tiles are reduced across the CTAs of a thread-block
+ *                       cluster through distributed shared memory, then
+ *                       resid[t][n] += y;  out/out_lo[t][n] = hi/lo(resid * gamma[n]);
+ *                       ssq_out[row_tile][t] = sum over the tile's 128 rows of resid^2
+ *   FT_EPI_QKV_ROPE(4): cluster reduce, y *= rstd[t], RoPE on q and k rows, q -> q_out bf16
+ *                       [T][nq*d], k/v -> paged KV cache layer (layout of ft_rope_kv_append)
+ *   FT_EPI_LOGITS  (5): out fp32 [T][n_out] = y * rstd[t]
+ * rstd[t] = rsqrt(sum_p ssq_in[p * ssq_stride + t] * inv_h + eps).  x_lo is required. */
+enum { FT_EPI_PARTIAL = 0, FT_EPI_BF16 = 1, FT_EPI_SWIGLU = 2, FT_EPI_RESID = 3, FT_EPI_QKV_ROPE = 4,
+       FT_EPI_LOGITS = 5 };
+typedef struct {
+    int mode;
+    void* out;                 /* see the mode */
+    void* out_lo;
+    float* resid;              /* RESID: fp32 [T][n_out], updated in place */
+    const void* gamma;         /* RESID: bf16 [n_out], weight of the NEXT RMSNorm */
+    float* ssq_out;            /* RESID: fp32 [n_out/128][ssq_stride] */
+    const float* ssq_in;       /* SWIGLU / QKV_ROPE / LOGITS: fp32 [ssq_parts][ssq_stride] or NULL */
+    int ssq_parts, ssq_stride;
+    float inv_h, eps;
+    const float* rope_cos;     /* QKV_ROPE: fp32 [pos][d/2] */
+    const float* rope_sin;
+    const int* positions;      /* QKV_ROPE: int32 [T] */
+    const int* seq_rows;       /* QKV_ROPE: int32 [T], page-table row of each token */
+    const int* page_table;     /* QKV_ROPE: int32 [rows][max_pages] */
+    int max_pages;
+    void* q_out;               /* QKV_ROPE: bf16 [T][nq*d] */
+    void* kv_layer;            /* QKV_ROPE: paged KV cache layer */
+    int nq, nkv, head_dim;
+} ft_gemm_epilogue;
+int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int n_out, int T, int K, int n_splits,
+                  const ft_gemm_epilogue* epi, void* stream);
+
+/* Layer-0 entry of the norm-deferred pipeline: resid[t] = embed[token[t]] (fp32);
+ * out/out_lo[t] = hi/lo(resid * gamma); ssq[0][t] = sum resid^2, ssq[p>0][t] = 0. */
+int ft_embed_planes(const int* tokens, const void* embed_table, const void* gamma, float* resid, void* out,
+                    void* out_lo, float* ssq, int ssq_parts, int ssq_stride, int T, int h, void* stream);
+/* Row gather of activation planes + their sums of squares (last-token rows for the LM head). */
+int ft_gather_planes(const void* x, const void* x_lo, const float* ssq, int ssq_parts, int ssq_stride,
+                     const int* row_idx, int n_rows, int h, void* out, void* out_lo, float* ssq_out,
+                     int ssq_out_stride, void* stream);
+
 /* K1+K2: resid[r] (fp32) = embed[token[r]]  or  resid[r] += sum_s partials[s][r];
  * y = rmsnorm(resid[r]) * w, r = row_idx ? row_idx[i] : i;  xn[i] = bf16(y), xn_lo[i] = bf16(y - xn[i])
  * (xn_lo may be NULL). */

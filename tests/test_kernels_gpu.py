@@ -94,6 +94,119 @@ def test_gemm_linearity(K):
     assert torch.equal(K.gemm_bf16(w, x1, x2).sum(0), y(x1) + y(x2))      # second plane == second product
 
 
+# ------------------------------------------------------------------ K3 fused epilogues (norm-deferred chain)
+@pytest.mark.parametrize("h,T,Kd,splits", [(2048, 64, 2048, 0), (2048, 64, 8192, 0), (256, 5, 512, 1),
+                                           (384, 37, 256, 2), (2048, 200, 2048, 0), (4096, 16, 1024, 8)])
+def test_gemm_resid_epilogue(K, h, T, Kd, splits):
+    """O / down projection: cluster split-K reduce through DSMEM, resid += y, planes of
+    resid * gamma_next, per-row-tile sums of squares."""
+    from fasttalk_llm_microservice_b200 import native as N
+    g = torch.Generator(device=DEV).manual_seed(h + T + Kd)
+    w = (torch.randn(h, Kd, device=DEV, generator=g) * 0.05).bfloat16()
+    x, x_lo = K.split_hi_lo(torch.randn(T, Kd, device=DEV, generator=g))
+    resid = torch.randn(T, h, device=DEV, generator=g)
+    gamma = (1 + 0.1 * torch.randn(h, device=DEV, generator=g)).bfloat16()
+    ref_resid = resid + hilo(x, x_lo) @ w.float().T
+    out, out_lo = torch.zeros(T, h, device=DEV, dtype=torch.bfloat16), torch.zeros(T, h, device=DEV, dtype=torch.bfloat16)
+    parts = h // 128
+    ssq = torch.full((parts, T + 3), -1.0, device=DEV)
+    r2 = resid.clone()
+    K.gemm_fused(w, x, x_lo, N.EPI_RESID, n_splits=splits, resid=r2, gamma=gamma, out=out, out_lo=out_lo,
+                 ssq_out=ssq, ssq_stride=T + 3)
+    torch.cuda.synchronize()
+    assert rel_err(r2, ref_resid) < 1e-3
+    assert rel_err(hilo(out, out_lo), ref_resid * gamma.float()) < 1e-3
+    ref_ssq = (ref_resid ** 2).reshape(T, parts, 128).sum(-1).T
+    assert rel_err(ssq[:, :T], ref_ssq) < 2e-3
+    assert (ssq[:, T:] == -1).all()
+
+
+@pytest.mark.parametrize("nq,nkv,d,T,Kd,splits", [(32, 8, 64, 64, 2048, 0), (24, 8, 128, 9, 3072, 0),
+                                                  (8, 2, 64, 5, 256, 1), (3, 1, 128, 70, 384, 2),
+                                                  (32, 8, 128, 130, 512, 0)])
+def test_gemm_qkv_rope_epilogue(K, nq, nkv, d, T, Kd, splits):
+    """QKV projection: cluster reduce, 1/rms, RoPE, q out and swizzled paged K/V append."""
+    from fasttalk_llm_microservice_b200 import native as N
+    from fasttalk_llm_microservice_b200.model_spec import ModelSpec
+    from fasttalk_llm_microservice_b200.weights import rope_tables
+    spec = ModelSpec("t", hidden=Kd, ffn=128, layers=1, n_q_heads=nq, n_kv_heads=nkv, head_dim=d)
+    g = torch.Generator(device=DEV).manual_seed(nq + d + T)
+    n_out = (nq + 2 * nkv) * d
+    w = (torch.randn(n_out, Kd, device=DEV, generator=g) * 0.05).bfloat16()
+    x, x_lo = K.split_hi_lo(torch.randn(T, Kd, device=DEV, generator=g))
+    parts = 3
+    ssq = torch.rand(parts, T, device=DEV, generator=g) * Kd
+    rstd = torch.rsqrt(ssq.sum(0) / Kd + 1e-5)
+    n_seq, max_pages, num_pages = 3, 8, 32
+    rows = torch.randint(0, n_seq, (T,), device=DEV, generator=g, dtype=torch.int32)
+    # distinct (sequence, position) per token
+    pos = torch.zeros(T, dtype=torch.int32, device=DEV)
+    seen = {}
+    for t in range(T):
+        r = int(rows[t])
+        seen[r] = seen.get(r, int(torch.randint(0, 60, (1,), generator=torch.Generator().manual_seed(r)))) + 1
+        pos[t] = seen[r]
+    pt = torch.randperm(num_pages, device=DEV, generator=g)[:n_seq * max_pages].reshape(n_seq, max_pages).int().contiguous()
+    cos, sin = rope_tables(spec, 512, device=DEV)
+    kv = K.kv_cache_alloc(num_pages, nkv, d, DEV)
+    q = torch.zeros(T, nq, d, device=DEV, dtype=torch.bfloat16)
+    K.gemm_fused(w, x, x_lo, N.EPI_QKV_ROPE, n_splits=splits, ssq_in=ssq, ssq_parts=parts, ssq_stride=T,
+                 inv_h=1.0 / Kd, eps=1e-5, rope_cos=cos, rope_sin=sin, positions=pos, seq_rows=rows, page_table=pt,
+                 max_pages=max_pages, q_out=q, kv_layer=kv, nq=nq, nkv=nkv, head_dim=d)
+    torch.cuda.synchronize()
+    full = (hilo(x, x_lo) @ w.float().T) * rstd[:, None]
+    qr = full[:, :nq * d].reshape(T, nq, d)
+    kr = full[:, nq * d:(nq + nkv) * d].reshape(T, nkv, d)
+    vr = full[:, (nq + nkv) * d:].reshape(T, nkv, d)
+    c, s = O.rope_cos_sin(spec, pos.cpu().long())
+    c, s = c.to(DEV), s.to(DEV)
+    assert rel_err(q, O.apply_rope(qr, c, s)) < 6e-3
+    kref = O.apply_rope(kr, c, s)
+    for t in range(T):
+        page = pt[rows[t], pos[t] // 64].item()
+        r = pos[t].item() % 64
+        for hk in range(nkv):
+            assert rel_err(K.kv_slab_logical(kv[page, hk, 0])[r], kref[t, hk]) < 6e-3
+            assert rel_err(K.kv_slab_logical(kv[page, hk, 1])[r], vr[t, hk]) < 6e-3
+
+
+def test_gemm_logits_and_swiglu_with_rstd(K):
+    from fasttalk_llm_microservice_b200 import native as N
+    from fasttalk_llm_microservice_b200.weights import interleave_gate_up
+    g = torch.Generator(device=DEV).manual_seed(3)
+    T, h, V, f = 33, 256, 1024, 512
+    x, x_lo = K.split_hi_lo(torch.randn(T, h, device=DEV, generator=g))
+    ssq = torch.rand(2, T, device=DEV, generator=g) * h
+    rstd = torch.rsqrt(ssq.sum(0) / h + 1e-5)
+    w = (torch.randn(V, h, device=DEV, generator=g) * 0.05).bfloat16()
+    logits = torch.zeros(T, V, device=DEV)
+    K.gemm_fused(w, x, x_lo, N.EPI_LOGITS, out=logits, ssq_in=ssq, ssq_parts=2, ssq_stride=T, inv_h=1.0 / h, eps=1e-5)
+    assert rel_err(logits, (hilo(x, x_lo) @ w.float().T) * rstd[:, None]) < 1e-3
+    wgu = (torch.randn(2 * f, h, device=DEV, generator=g) * 0.05).bfloat16()
+    act, act_lo = torch.zeros(T, f, device=DEV, dtype=torch.bfloat16), torch.zeros(T, f, device=DEV, dtype=torch.bfloat16)
+    K.gemm_fused(interleave_gate_up(wgu), x, x_lo, N.EPI_SWIGLU, out=act, out_lo=act_lo, ssq_in=ssq, ssq_parts=2,
+                 ssq_stride=T, inv_h=1.0 / h, eps=1e-5)
+    ref = O.swiglu((hilo(x, x_lo) @ wgu.float().T) * rstd[:, None])
+    assert rel_err(hilo(act, act_lo), ref) < 2e-4
+
+
+def test_embed_and_gather_planes(K):
+    g = torch.Generator(device=DEV).manual_seed(6)
+    V, h, T, parts = 1000, 2048, 19, 16
+    table = torch.randn(V, h, device=DEV, generator=g).bfloat16()
+    gamma = (1 + 0.1 * torch.randn(h, device=DEV, generator=g)).bfloat16()
+    toks = torch.randint(0, V, (T,), device=DEV, generator=g, dtype=torch.int32)
+    resid, hi, lo, ssq = K.embed_planes(toks, table, gamma, parts)
+    ref = table[toks.long()].float()
+    assert torch.equal(resid, ref)
+    assert rel_err(hilo(hi, lo), ref * gamma.float()) < 5e-5
+    assert rel_err(ssq.sum(0), (ref ** 2).sum(-1)) < 1e-5 and (ssq[1:] == 0).all()
+    rows = torch.tensor([18, 0, 7], device=DEV, dtype=torch.int32)
+    ghi, glo, gss = K.gather_planes(hi, lo, ssq, rows)
+    assert torch.equal(ghi, hi[rows.long()]) and torch.equal(glo, lo[rows.long()])
+    assert torch.equal(gss, ssq[:, rows.long()])
+
+
 # ------------------------------------------------------------------ K1 / K2
 def test_add_rmsnorm_partials(K):
     g = torch.Generator(device=DEV).manual_seed(1)
