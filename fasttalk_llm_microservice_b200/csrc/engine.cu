@@ -82,6 +82,8 @@ struct Engine {
     float* ssq = nullptr;          // [ssq_parts][t_max] partial sums of squares of the residual rows
     float* ssq_last = nullptr;     // [ssq_parts][rows_last] gathered for the LM-head rows
     int ssq_parts = 0, rows_last = 0;
+    float* gemm_scratch = nullptr; // split-K slabs of the fused-epilogue GEMMs (one wave of CTAs)
+    int* gemm_sync = nullptr;      // their arrival counters
     // bf16 activations feeding the GEMMs are kept as hi + lo planes (see gemm.cu)
     void *xn = nullptr, *q = nullptr, *attn_out = nullptr, *act = nullptr, *xn_last = nullptr;
     void *xn_lo = nullptr, *attn_out_lo = nullptr, *act_lo = nullptr, *xn_last_lo = nullptr;
@@ -184,12 +186,14 @@ struct Batch {
     } while (0)
 
 // One projection with a fused epilogue.  `staged` epilogues (RESID / QKV_ROPE) split K across
-// a thread-block cluster; the others run unsplit.
+// one wave of CTAs that rendezvous in the epilogue; the others run unsplit.
 static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, const CUtensorMap* xmaps_lo,
-                    int T, int n_out, int K, const ft_gemm_epilogue& epi) {
+                    int T, int n_out, int K, ft_gemm_epilogue epi) {
     const int bn = gemm_pick_bn(T, true);
     const bool staged = epi.mode == FT_EPI_RESID || epi.mode == FT_EPI_QKV_ROPE;
-    const int splits = staged ? gemm_pick_cluster_splits(n_out, T, K, e->sms) : 1;
+    const int splits = staged ? gemm_pick_splits(n_out, T, K, e->sms, true) : 1;
+    epi.scratch = e->gemm_scratch;
+    epi.sync = e->gemm_sync;
     e->st.kernel_launches++;
     return launch_gemm(mw, xmaps[bn_index(bn)], &xmaps_lo[bn_index(bn)], bn, n_out, T, K, splits, epi, e->pdl,
                        e->stream);
@@ -573,6 +577,11 @@ static int engine_init(Engine* e) {
         e->ssq = static_cast<float*>(p);
         FT_TRY(alloc_zero(&p, (size_t)e->ssq_parts * rows_last * 4));
         e->ssq_last = static_cast<float*>(p);
+        // a split-K grid never exceeds one CTA per SM, each parking at most a 128 x 128 fp32 tile
+        FT_TRY(alloc_zero(&p, (size_t)e->sms * 128 * 128 * 4));
+        e->gemm_scratch = static_cast<float*>(p);
+        FT_TRY(alloc_zero(&p, (size_t)2 * e->sms * 4));
+        e->gemm_sync = static_cast<int*>(p);
     }
 
     // decode attention: persistent grid = SMs x resident CTAs
@@ -644,7 +653,7 @@ static void engine_free(Engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     for (auto& kv : e->sessions) delete kv.second;
     for (auto& kv : e->requests) delete kv.second;
-    cudaFree(e->kv); cudaFree(e->resid); cudaFree(e->ssq); cudaFree(e->ssq_last); cudaFree(e->xn); cudaFree(e->q);
+    cudaFree(e->kv); cudaFree(e->resid); cudaFree(e->ssq); cudaFree(e->ssq_last); cudaFree(e->gemm_scratch); cudaFree(e->gemm_sync); cudaFree(e->xn); cudaFree(e->q);
     cudaFree(e->attn_out); cudaFree(e->act); cudaFree(e->xn_last); cudaFree(e->logits);
     cudaFree(e->xn_lo); cudaFree(e->attn_out_lo); cudaFree(e->act_lo); cudaFree(e->xn_last_lo);
     cudaFree(e->attn_scratch); cudaFree(e->meta.d);

@@ -15,9 +15,7 @@ constexpr int GEMM_MAX_SPLITS = 16;
 int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int box_rows);
 int gemm_pick_bn(int T, bool hilo);
 int gemm_pick_splits(int n_out, int T, int K, int num_sms, bool hilo);
-// split count for the cluster-reduced epilogues (FT_EPI_RESID / FT_EPI_QKV_ROPE): <= 8, all
-// clusters of the grid resident at once
-int gemm_pick_cluster_splits(int n_out, int T, int K, int num_sms);
+size_t gemm_scratch_floats(int n_out, int T, int splits, bool hilo);   // split-K slabs of one launch
 // Modes and fields: ft_gemm_epilogue in include/fasttalk_b200.h.
 int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap* mx_lo, int bn, int n_out,
                 int T, int K, int splits, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream);

@@ -3,8 +3,8 @@
 // The weight matrix is the UMMA "A" operand (128 output features fill the 128 TMEM lanes),
 // the activations are the "B" operand (tokens = UMMA N, 16..256), so the decode case
 // (T <= 64 tokens) is pure weight streaming: every CTA pulls its 128 x K_range slab of W
-// through a ring of TMA stages exactly once.  Split-K over gridDim.z gives enough CTAs to
-// keep HBM busy when n_out/128 is small.
+// through a ring of TMA stages exactly once (measured ~6 TB/s in steady state).  Split-K over
+// gridDim.z gives one full wave of CTAs when n_out/128 is small.
 //
 // Activations come as TWO bf16 planes, hi = bf16(x) and lo = bf16(x - hi): both are multiplied
 // by the same weight tile into the same TMEM accumulator (D += W*hi; D += W*lo).  That keeps
@@ -12,51 +12,73 @@
 // the weight tile is already in shared memory, so in the HBM-bound decode regime the second
 // product is free (DESIGN.md "precision").  lo may be absent (HILO = false).
 //
-// Epilogues (ft_gemm_epilogue.mode, include/fasttalk_b200.h):
-//   PARTIAL / BF16 / SWIGLU / LOGITS  straight from TMEM to global memory;
-//   RESID / QKV_ROPE                  the split-K CTAs of one row tile form a thread-block
-//     CLUSTER: each parks its fp32 partial tile in its own shared memory, and after a cluster
-//     barrier every CTA reduces a slice of the tokens across all peers through distributed
-//     shared memory (ld.shared::cluster) and finishes the layer step there — residual add +
-//     next-norm statistics, or RoPE + paged KV append — so no stand-alone reduce / norm / RoPE
-//     kernel sits between the projections (RMSNorm's 1/rms is applied after the next GEMM).
+// Epilogue (8 warps): phase 1 moves the fp32 accumulator tile TMEM -> [token][row] staging
+// (shared memory, or — when K is split — this CTA's slab of an L2-resident scratch buffer);
+// phase 2, for split K, is a rendezvous of the row tile's CTAs on a global arrival counter (all
+// CTAs of the one-wave grid are co-resident); phase 3 walks tokens one per warp with float4
+// rows, sums the split-K slabs for this CTA's share of the tokens and finishes the layer step
+// right there (ft_gemm_epilogue.mode): residual add + next-norm statistics, 1/rms + RoPE + paged
+// KV append, 1/rms + SwiGLU, or logits.  RMSNorm's 1/rms is applied AFTER the projection, so no
+// stand-alone reduce / norm / RoPE kernel sits between the GEMMs of a layer.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
-// warps 2..5 = epilogue (tcgen05.ld -> global).
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2..9 = epilogue.
 #include "common.cuh"
 #include "ft_internal.h"
+
+#include <stdlib.h>
 
 namespace ft {
 
 constexpr int GEMM_BM = 128;      // W rows per CTA  (UMMA M)
 constexpr int GEMM_BK = 64;       // bf16 per 128-byte swizzle row
 constexpr int GEMM_A_BYTES = GEMM_BM * GEMM_BK * 2;
-constexpr int GEMM_THREADS = 192;
-constexpr int GEMM_MAX_CLUSTER = 8;
+constexpr int GEMM_EPI_WARPS = 8;
+constexpr int GEMM_EPI_THREADS = 32 * GEMM_EPI_WARPS;
+constexpr int GEMM_THREADS = 64 + GEMM_EPI_THREADS;
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
-
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
+__device__ __forceinline__ void epi_bar_sync() {
+    asm volatile("bar.sync 2, %0;" ::"n"(GEMM_EPI_THREADS) : "memory");
 }
-__device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank) {
-    uint32_t remote;
-    float v;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
-    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 
-struct HiLo {
-    __nv_bfloat16 hi, lo;
-};
-__device__ __forceinline__ HiLo split_hi_lo(float x) {
-    HiLo r;
-    r.hi = __float2bfloat16(x);
-    r.lo = __float2bfloat16(x - __bfloat162float(r.hi));
-    return r;
+// Always-on, nearly free timeline of CTA (0,0,0) of the most recent GEMM launch (globaltimer ns):
+// read back with ft_debug_gemm_trace (tuning aid, scripts/trace_gemm.py).
+__device__ unsigned long long g_gemm_trace[16];
+__device__ __forceinline__ void trace(int slot) {
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_gemm_trace[slot] = t;
+    }
 }
+
+__device__ __forceinline__ float4 f4_mul(float4 a, float s) { return make_float4(a.x * s, a.y * s, a.z * s, a.w * s); }
+__device__ __forceinline__ float4 f4_add(float4 a, float4 b) {
+    return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+}
+__device__ __forceinline__ float4 f4_shfl_xor(float4 a, int m) {
+    return make_float4(__shfl_xor_sync(0xffffffffu, a.x, m), __shfl_xor_sync(0xffffffffu, a.y, m),
+                       __shfl_xor_sync(0xffffffffu, a.z, m), __shfl_xor_sync(0xffffffffu, a.w, m));
+}
+// four fp32 -> bf16 hi plane (8 bytes) and bf16 lo plane = rounding residual (8 bytes)
+__device__ __forceinline__ void store_hi_lo4(__nv_bfloat16* hi, __nv_bfloat16* lo, size_t idx, float4 y) {
+    uint2 h;
+    h.x = pack_bf16(y.x, y.y);
+    h.y = pack_bf16(y.z, y.w);
+    *reinterpret_cast<uint2*>(hi + idx) = h;
+    if (lo) {
+        uint2 l;
+        l.x = pack_bf16(y.x - bf16_lo(h.x), y.y - bf16_hi(h.x));
+        l.y = pack_bf16(y.z - bf16_lo(h.y), y.w - bf16_hi(h.y));
+        *reinterpret_cast<uint2*>(lo + idx) = l;
+    }
+}
+__device__ __forceinline__ float silu(float g) { return g / (1.f + __expf(-g)); }
 
 template <int BN, bool HILO>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -78,7 +100,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
     uint64_t* tmem_full_bar = empty_bar + stages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
     float* rstd_s = reinterpret_cast<float*>(tmem_slot + 2);     // [BN] per-token 1/rms
-    float* red_s = rstd_s + BN;                                  // [4][BN] cross-warp sums
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -90,7 +111,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
     const int kc_end = (int)(((long long)k_chunks * (split + 1)) / n_split);
     const int n_iter = kc_end - kc_begin;
     const int mode = ep.mode;
-    const bool staged = mode == FT_EPI_RESID || mode == FT_EPI_QKV_ROPE;
+    if (threadIdx.x == 0) trace(0);
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
@@ -111,6 +132,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) trace(1);
 
     pdl_launch_dependents();
 
@@ -126,7 +148,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                 tma_tile_2d(smem + (size_t)i * STAGE_BYTES, &map_w, (kc_begin + i) * GEMM_BK, row0,
                             &full_bar[i], pol_w);
             }
+            trace(2);
             pdl_wait();
+            trace(3);
             for (int i = 0; i < pre; ++i) {
                 uint8_t* bs = smem + (size_t)i * STAGE_BYTES + GEMM_A_BYTES;
                 tma_tile_2d(bs, &map_x, (kc_begin + i) * GEMM_BK, t0, &full_bar[i], pol_x);
@@ -153,6 +177,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
             uint32_t ph = 0;
             for (int i = 0; i < n_iter; ++i) {
                 mbar_wait(&full_bar[s], ph);
+                if (i == 0) trace(4);
                 tc_fence_after();
                 const uint32_t a_addr = smem_u32(smem + (size_t)s * STAGE_BYTES);
                 const uint64_t a_desc = umma_desc_k128(a_addr);
@@ -169,16 +194,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                 umma_commit(&empty_bar[s]);               // frees the smem stage when MMAs retire
                 if (++s == stages) { s = 0; ph ^= 1; }
             }
+            trace(5);
             umma_commit(tmem_full_bar);
         }
     } else {
-        // ---------------- epilogue warps.  A warp may only touch the TMEM lane quarter (warp_id % 4).
-        const int q = warp & 3;
-        const int tid = q * 32 + lane;          // tile row owned by this thread
-        const int row = row0 + tid;
+        // ================================================================ epilogue warps (2..9)
+        const int ew = warp - 2;                // 0..7
+        const int q = warp & 3;                 // TMEM lane quarter this warp may read (warp_id % 4)
+        const int et = threadIdx.x - 64;        // 0..255
+        const bool reduce = (mode == FT_EPI_RESID || mode == FT_EPI_QKV_ROPE) && n_split > 1;
         pdl_wait();                             // ssq_in / resid / positions come from earlier kernels
         // per-token 1/rms of the activation's source (RMSNorm deferred past the projection)
-        for (int j = tid; j < BN; j += 128) {
+        for (int j = et; j < BN; j += GEMM_EPI_THREADS) {
             float r = 1.f;
             const int t = t0 + j;
             if (ep.ssq_in && t < T) {
@@ -188,155 +215,115 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
             }
             rstd_s[j] = r;
         }
-        epi_bar_sync();
         if (n_iter > 0) {
             mbar_wait(tmem_full_bar, 0);
             tc_fence_after();
         }
-        const size_t split_off = (size_t)split * T;
+        if (et == 0) trace(6);
+
+        // ---- phase 1: accumulator tile TMEM -> [token][row] staging
+        const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
         float* stage_f = reinterpret_cast<float*>(smem);   // pipeline stages are idle once the MMAs retired
+        float* slabs = reduce ? ep.scratch + (size_t)tile_id * n_split * (BN * GEMM_BM) : nullptr;
+        float* dst;
+        size_t tok_stride = GEMM_BM;
+        if (mode == FT_EPI_PARTIAL) {
+            dst = reinterpret_cast<float*>(ep.out) + ((size_t)split * T + t0) * n_out + row0;
+            tok_stride = n_out;
+        } else {
+            dst = reduce ? slabs + (size_t)split * (BN * GEMM_BM) : stage_f;
+        }
+        {
+            constexpr int CPW = BN >= 32 ? BN / 2 : 16;     // columns per warp: two warps share a lane quarter
+            const int cbeg = (ew >> 2) * CPW;
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 16) {
-            if (t0 + c0 >= T) break;
-            float v[16];
-            if (n_iter > 0) {
-                tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + c0, v);
-            } else {
+            for (int c0 = cbeg; c0 < cbeg + CPW && c0 < BN; c0 += 16) {
+                if (t0 + c0 >= T) break;
+                float v[16];
+                if (n_iter > 0) {
+                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + c0, v);
+                } else {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) v[j] = 0.f;
-            }
-            if (staged) {
-                // park the fp32 partial tile as [token][row] for the cluster-wide reduction
-#pragma unroll
-                for (int j = 0; j < 16; ++j) stage_f[(c0 + j) * GEMM_BM + tid] = v[j];
-            } else if (mode == FT_EPI_PARTIAL || mode == FT_EPI_LOGITS) {
-                float* o = reinterpret_cast<float*>(ep.out);
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const int t = t0 + c0 + j;
-                    if (t < T) o[(split_off + t) * n_out + row] = v[j] * rstd_s[c0 + j];
+                    for (int j = 0; j < 16; ++j) v[j] = 0.f;
                 }
-            } else if (mode == FT_EPI_BF16) {
-                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out);
-                __nv_bfloat16* ol = reinterpret_cast<__nv_bfloat16*>(ep.out_lo);
+                float* p = dst + (size_t)c0 * tok_stride + q * 32 + lane;
+                const int valid = mode == FT_EPI_PARTIAL ? T - (t0 + c0) : 16;
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const int t = t0 + c0 + j;
-                    if (t < T) {
-                        const HiLo hl = split_hi_lo(v[j] * rstd_s[c0 + j]);
-                        o[(size_t)t * n_out + row] = hl.hi;
-                        if (ol) ol[(size_t)t * n_out + row] = hl.lo;
-                    }
-                }
-            } else {
-                // fused SwiGLU: lanes 0..63 hold gate features, lanes 64..127 the matching up
-                // features; up warps hand their values to the gate warps through smem
-                const int f_half = n_out >> 1;
-                if (q >= 2) {
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) stage_f[((q - 2) * 32 + lane) * 17 + j] = v[j];
-                }
-                epi_bar_sync();
-                if (q < 2) {
-                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out);
-                    __nv_bfloat16* ol = reinterpret_cast<__nv_bfloat16*>(ep.out_lo);
-                    const int feat = blockIdx.x * 64 + q * 32 + lane;
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int t = t0 + c0 + j;
-                        if (t < T) {
-                            const float rs = rstd_s[c0 + j];
-                            const float g = v[j] * rs, u = stage_f[(q * 32 + lane) * 17 + j] * rs;
-                            const HiLo hl = split_hi_lo(g / (1.f + __expf(-g)) * u);
-                            o[(size_t)t * f_half + feat] = hl.hi;
-                            if (ol) ol[(size_t)t * f_half + feat] = hl.lo;
-                        }
-                    }
-                }
-                epi_bar_sync();
+                for (int j = 0; j < 16; ++j)
+                    if (j < valid) p[(size_t)j * tok_stride] = v[j];
             }
         }
-    }
+        if (et == 0) trace(7);
 
-    if (staged) {
-        // ---------------- cluster-wide split-K reduction through distributed shared memory
-        __syncwarp();
-        if (n_split > 1) cluster_sync_all(); else __syncthreads();
-        if (warp >= 2) {
-            const int q = warp & 3;
-            const int tid = q * 32 + lane;
-            const int row = row0 + tid;
-            float* stage_f = reinterpret_cast<float*>(smem);
-            const uint32_t stage_addr = smem_u32(stage_f);
-            // this CTA finishes tokens [j0, j1) of the tile
-            const int j0 = BN * split / n_split, j1 = BN * (split + 1) / n_split;
-            if (mode == FT_EPI_RESID) {
-                float* resid = ep.resid;
-                const float gam = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(ep.gamma)[row]);
-                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out);
-                __nv_bfloat16* ol = reinterpret_cast<__nv_bfloat16*>(ep.out_lo);
-                for (int j = j0; j < j1; ++j) {
-                    const int t = t0 + j;
-                    float ss = 0.f;
-                    if (t < T) {
-                        float y = 0.f;
-                        if (n_split == 1) {
-                            y = stage_f[j * GEMM_BM + tid];
-                        } else {
-                            for (int p = 0; p < n_split; ++p)
-                                y += ld_dsmem_f32(stage_addr + (uint32_t)(j * GEMM_BM + tid) * 4, (uint32_t)p);
-                        }
-                        const size_t idx = (size_t)t * n_out + row;
-                        const float r = resid[idx] + y;
-                        resid[idx] = r;
-                        const HiLo hl = split_hi_lo(r * gam);
-                        o[idx] = hl.hi;
-                        ol[idx] = hl.lo;
-                        ss = r * r;
+        if (mode != FT_EPI_PARTIAL) {
+            // ---- phase 2: make the tile visible (CTA barrier, or split-K rendezvous in global memory)
+            unsigned* cnt = reinterpret_cast<unsigned*>(ep.sync) + 2 * tile_id;
+            if (reduce) {
+                __threadfence();
+                epi_bar_sync();
+                if (et == 0) {
+                    atomicAdd(cnt, 1u);
+                    unsigned spins = 0;
+                    while (ld_acquire_u32(cnt) < (unsigned)n_split) {
+                        __nanosleep(32);
+                        if (++spins > (1u << 25)) __trap();      // a peer never arrived: fail loudly, do not hang
                     }
-                    ss = warp_sum(ss);
-                    if (lane == 0) red_s[q * BN + j] = ss;
                 }
                 epi_bar_sync();
-                for (int j = j0 + tid; j < j1; j += 128) {
-                    const int t = t0 + j;
-                    if (t < T)
-                        ep.ssq_out[(size_t)blockIdx.x * ep.ssq_stride + t] =
-                            (red_s[j] + red_s[BN + j]) + (red_s[2 * BN + j] + red_s[3 * BN + j]);
-                }
+                __threadfence();
             } else {
-                // QKV_ROPE.  pass A: reduce, apply 1/rms, leave the value in my own staging slot
-                // (slots of my token slice are read by nobody else)
-                for (int j = j0; j < j1; ++j) {
-                    if (t0 + j >= T) break;
-                    float y = 0.f;
-                    if (n_split == 1) {
-                        y = stage_f[j * GEMM_BM + tid];
-                    } else {
-                        for (int p = 0; p < n_split; ++p)
-                            y += ld_dsmem_f32(stage_addr + (uint32_t)(j * GEMM_BM + tid) * 4, (uint32_t)p);
-                    }
-                    stage_f[j * GEMM_BM + tid] = y * rstd_s[j];
-                }
                 epi_bar_sync();
-                // pass B: rotate with the partner row (i +- d/2 lives in the same 128-row tile)
-                const int d = ep.head_dim, half = d >> 1;
-                const int q_dim = ep.nq * d, kv_dim = ep.nkv * d;
-                const int i = row % d, fi = i % half;
-                const int region = row < q_dim ? 0 : row < q_dim + kv_dim ? 1 : 2;
-                for (int j = j0; j < j1; ++j) {
-                    const int t = t0 + j;
-                    if (t >= T) break;
-                    const float a = stage_f[j * GEMM_BM + tid];
-                    float val = a;
+            }
+
+            // ---- phase 3: one token per warp, four consecutive rows per lane
+            const int jbeg = reduce ? BN * split / n_split : 0;
+            const int jend = reduce ? BN * (split + 1) / n_split : BN;
+            const int r4 = 4 * lane;
+            const int row = row0 + r4;
+            float4 gam = make_float4(1.f, 1.f, 1.f, 1.f);
+            if (mode == FT_EPI_RESID) {
+                const uint2 gv = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(ep.gamma) + row);
+                gam = make_float4(bf16_lo(gv.x), bf16_hi(gv.x), bf16_lo(gv.y), bf16_hi(gv.y));
+            }
+            for (int j = jbeg + ew; j < jend; j += GEMM_EPI_WARPS) {
+                const int t = t0 + j;
+                if (t >= T) break;
+                float4 y;
+                if (reduce) {
+                    const float4* src = reinterpret_cast<const float4*>(slabs + (size_t)j * GEMM_BM + r4);
+                    y = __ldcg(src);
+                    for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
+                } else {
+                    y = *reinterpret_cast<const float4*>(stage_f + j * GEMM_BM + r4);
+                }
+                const float rs = rstd_s[j];
+                if (mode == FT_EPI_RESID) {
+                    const size_t idx = (size_t)t * n_out + row;
+                    float4 r = *reinterpret_cast<const float4*>(ep.resid + idx);
+                    r = f4_add(r, y);
+                    *reinterpret_cast<float4*>(ep.resid + idx) = r;
+                    store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
+                                 idx, make_float4(r.x * gam.x, r.y * gam.y, r.z * gam.z, r.w * gam.w));
+                    const float ss = warp_sum(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
+                    if (lane == 0) ep.ssq_out[(size_t)blockIdx.x * ep.ssq_stride + t] = ss;
+                } else if (mode == FT_EPI_QKV_ROPE) {
+                    const int d = ep.head_dim, half = d >> 1;
+                    const int q_dim = ep.nq * d, kv_dim = ep.nkv * d;
+                    const int region = row0 < q_dim ? 0 : row0 < q_dim + kv_dim ? 1 : 2;   // tile-uniform
+                    const int i = row % d;
                     const int pos = ep.positions[t];
+                    float4 val = f4_mul(y, rs);
                     if (region < 2) {
-                        const float b = stage_f[j * GEMM_BM + (tid ^ half)];
-                        const float c = ep.rope_cos[(size_t)pos * half + fi], s = ep.rope_sin[(size_t)pos * half + fi];
-                        val = i < half ? a * c - b * s : a * c + b * s;
+                        // rotate_half partner (i +- d/2) sits half/4 lanes away in the same warp
+                        const float4 b = f4_shfl_xor(val, half >> 2);
+                        const float4 c = *reinterpret_cast<const float4*>(ep.rope_cos + (size_t)pos * half + (i % half));
+                        const float4 s = *reinterpret_cast<const float4*>(ep.rope_sin + (size_t)pos * half + (i % half));
+                        const float sg = i < half ? -1.f : 1.f;
+                        val = make_float4(val.x * c.x + sg * b.x * s.x, val.y * c.y + sg * b.y * s.y,
+                                          val.z * c.z + sg * b.z * s.z, val.w * c.w + sg * b.w * s.w);
                     }
                     if (region == 0) {
-                        reinterpret_cast<__nv_bfloat16*>(ep.q_out)[(size_t)t * q_dim + row] = __float2bfloat16(val);
+                        store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.q_out), nullptr, (size_t)t * q_dim + row, val);
                     } else {
                         const int kvh = (row - q_dim - (region == 2 ? kv_dim : 0)) / d;
                         const int page = ep.page_table[(size_t)ep.seq_rows[t] * ep.max_pages + pos / kKvTile];
@@ -345,13 +332,34 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                                         (((size_t)page * ep.nkv + kvh) * 2 + (region == 2 ? 1 : 0)) *
                                             (size_t)(kKvTile * d * 2);
                         const int off = r * (d * 2) + ((((i >> 3) ^ (r & 7))) << 4) + (i & 7) * 2;
-                        *reinterpret_cast<__nv_bfloat16*>(slab + off) = __float2bfloat16(val);
+                        store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(slab + off), nullptr, 0, val);
                     }
+                } else if (mode == FT_EPI_SWIGLU) {
+                    // lanes 0..15 hold gate features 0..63 of the tile, lanes 16..31 the matching up features
+                    const float4 u = f4_shfl_xor(y, 16);
+                    if (lane < 16) {
+                        const float4 a = make_float4(silu(y.x * rs) * (u.x * rs), silu(y.y * rs) * (u.y * rs),
+                                                     silu(y.z * rs) * (u.z * rs), silu(y.w * rs) * (u.w * rs));
+                        store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
+                                     (size_t)t * (n_out >> 1) + blockIdx.x * 64 + r4, a);
+                    }
+                } else if (mode == FT_EPI_LOGITS) {
+                    *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + (size_t)t * n_out + row) = f4_mul(y, rs);
+                } else {   // FT_EPI_BF16
+                    store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
+                                 (size_t)t * n_out + row, f4_mul(y, rs));
+                }
+            }
+            if (reduce) {
+                // the last CTA of the row tile to finish re-arms the counters for the next launch
+                epi_bar_sync();
+                if (et == 0 && atomicAdd(cnt + 1, 1u) == (unsigned)n_split - 1) {
+                    cnt[0] = 0;
+                    cnt[1] = 0;
                 }
             }
         }
-        __syncwarp();
-        if (n_split > 1) cluster_sync_all();     // peers may still be reading my staging tile
+        if (et == 0) trace(8);
     }
 
     tc_fence_before();
@@ -360,6 +368,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
         tc_fence_after();
         tmem_dealloc(tmem_base, TMEM_COLS);
     }
+    if (threadIdx.x == 0) trace(9);
 }
 
 // ------------------------------------------------------------------ host side
@@ -442,12 +451,16 @@ static int stage_plan(int n_out, int T, int K, int splits, int* stages_out, size
     const int budget = tiles > device_sms() ? 108 * 1024 : 208 * 1024;
     int stages = budget / STAGE_BYTES;
     if (stages > 12) stages = 12;
+    if (const char* ov = getenv("FT_GEMM_STAGES")) {      // tuning experiments (scripts/bench_gemm.py)
+        const int v = atoi(ov);
+        if (v >= 2 && v <= stages) stages = v;
+    }
     if (stages > per_cta) stages = per_cta;
     if (stages < 2) stages = 2;
-    // the staged epilogues park a [BN][128] fp32 tile in the (idle) pipeline memory
+    // the epilogue parks a [BN][128] fp32 tile in the (idle) pipeline memory
     while ((size_t)stages * STAGE_BYTES < (size_t)BN * GEMM_BM * 4) ++stages;
     *stages_out = stages;
-    *smem_out = (size_t)stages * STAGE_BYTES + 1024 + (2 * stages + 1) * 8 + 16 + 5 * BN * 4 + 16;
+    *smem_out = (size_t)stages * STAGE_BYTES + 1024 + (2 * stages + 1) * 8 + 16 + BN * 4 + 16;
     FT_REQUIRE(*smem_out <= 227 * 1024, "gemm: %zu bytes of shared memory needed", *smem_out);
     return 0;
 }
@@ -464,7 +477,6 @@ static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CU
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set = true;
     }
-    const bool staged = epi.mode == FT_EPI_RESID || epi.mode == FT_EPI_QKV_ROPE;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(n_out / GEMM_BM, (T + BN - 1) / BN, splits);
     cfg.blockDim = dim3(GEMM_THREADS);
@@ -477,13 +489,6 @@ static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CU
         attr[na].val.programmaticStreamSerializationAllowed = 1;
         ++na;
     }
-    if (staged && splits > 1) {
-        attr[na].id = cudaLaunchAttributeClusterDimension;
-        attr[na].val.clusterDim.x = 1;
-        attr[na].val.clusterDim.y = 1;
-        attr[na].val.clusterDim.z = splits;
-        ++na;
-    }
     cfg.attrs = attr;
     cfg.numAttrs = na;
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<BN, HILO>, mw, mx, mxl, epi, n_out, T,
@@ -491,56 +496,9 @@ static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CU
     return 0;
 }
 
-// How many clusters of `splits` CTAs of the hi/lo kernel can be resident at once.
-template <int BN>
-static int max_active_clusters(int splits, size_t smem) {
-    cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         227 * 1024);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(1, 1, splits);
-    cfg.blockDim = dim3(GEMM_THREADS);
-    cfg.dynamicSmemBytes = smem;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 1;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = splits;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, gemm_bf16_tcgen05_kernel<BN, true>, &cfg) != cudaSuccess) {
-        cudaGetLastError();
-        return 0;
-    }
-    return n;
-}
-
-int gemm_pick_cluster_splits(int n_out, int T, int K, int num_sms) {
-    const int bn = gemm_pick_bn(T, true);
-    const int tiles = (n_out / GEMM_BM) * ((T + bn - 1) / bn);
-    const int kc = K / GEMM_BK;
-    if (tiles >= num_sms) return 1;
-    int s = num_sms / tiles;
-    if (s > GEMM_MAX_CLUSTER) s = GEMM_MAX_CLUSTER;
-    if (s > kc / 2) s = kc / 2 > 0 ? kc / 2 : 1;
-    static int cache[4][GEMM_MAX_CLUSTER + 1];      // [bn index][splits] -> resident clusters (0 = unknown)
-    const int bi = bn == 16 ? 0 : bn == 32 ? 1 : bn == 64 ? 2 : 3;
-    for (; s > 1; --s) {
-        if (!cache[bi][s]) {
-            int stages = 0;
-            size_t smem = 0;
-            int n = 0;
-            switch (bn) {
-                case 16: if (!stage_plan<16, true>(n_out, T, K, s, &stages, &smem)) n = max_active_clusters<16>(s, smem); break;
-                case 32: if (!stage_plan<32, true>(n_out, T, K, s, &stages, &smem)) n = max_active_clusters<32>(s, smem); break;
-                case 64: if (!stage_plan<64, true>(n_out, T, K, s, &stages, &smem)) n = max_active_clusters<64>(s, smem); break;
-                default: if (!stage_plan<128, true>(n_out, T, K, s, &stages, &smem)) n = max_active_clusters<128>(s, smem); break;
-            }
-            cache[bi][s] = n > 0 ? n : -1;
-        }
-        if (cache[bi][s] >= tiles) return s;       // every cluster of the grid is resident in one wave
-    }
-    return 1;
+size_t gemm_scratch_floats(int n_out, int T, int splits, bool hilo) {
+    const int bn = gemm_pick_bn(T, hilo);
+    return (size_t)(n_out / GEMM_BM) * ((T + bn - 1) / bn) * splits * bn * GEMM_BM;
 }
 
 int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap* mx_lo, int bn, int n_out,
@@ -554,10 +512,15 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
     FT_REQUIRE(mode >= FT_EPI_PARTIAL && mode <= FT_EPI_LOGITS, "gemm: bad epilogue mode %d", mode);
     const bool staged = mode == FT_EPI_RESID || mode == FT_EPI_QKV_ROPE;
     FT_REQUIRE(mode == FT_EPI_PARTIAL || staged || splits == 1, "gemm: this epilogue needs splits == 1");
-    FT_REQUIRE(!staged || splits <= GEMM_MAX_CLUSTER, "gemm: cluster-reduced epilogues split at most %d ways",
-               GEMM_MAX_CLUSTER);
     const bool hilo = mx_lo != nullptr;
-    FT_REQUIRE(!staged || hilo, "gemm: the fused RESID / QKV_ROPE epilogues need both activation planes");
+    FT_REQUIRE(mode <= FT_EPI_BF16 || hilo, "gemm: the fused epilogues need both activation planes");
+    if (staged && splits > 1) {
+        // the split-K rendezvous spins on peers of the same row tile: every CTA must be resident
+        const int ctas = (n_out / GEMM_BM) * ((T + bn - 1) / bn) * splits;
+        FT_REQUIRE(ctas <= device_sms(), "gemm: %d CTAs do not fit one wave of %d SMs (split-K rendezvous)", ctas,
+                   device_sms());
+        FT_REQUIRE(epi.scratch && epi.sync, "gemm: split-K fused epilogues need scratch and sync buffers");
+    }
     FT_REQUIRE(!(hilo && bn > 128), "gemm: hi/lo activations support token tiles up to 128");
     if (mode == FT_EPI_QKV_ROPE) {
         FT_REQUIRE(epi.head_dim == 64 || epi.head_dim == 128, "gemm: head_dim %d not supported", epi.head_dim);
@@ -595,9 +558,7 @@ extern "C" int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int
     const bool staged = epi->mode == FT_EPI_RESID || epi->mode == FT_EPI_QKV_ROPE;
     const int bn = gemm_pick_bn(T, hilo);
     if (n_splits <= 0)
-        n_splits = epi->mode == FT_EPI_PARTIAL ? gemm_pick_splits(n_out, T, K, sms, hilo)
-                   : staged                    ? gemm_pick_cluster_splits(n_out, T, K, sms)
-                                               : 1;
+        n_splits = epi->mode == FT_EPI_PARTIAL || staged ? gemm_pick_splits(n_out, T, K, sms, hilo) : 1;
     CUtensorMap mw, mx, mxl;
     if (int r = make_tmap_bf16_k64(&mw, w, n_out, K, GEMM_BM)) return r;
     if (int r = make_tmap_bf16_k64(&mx, x, T, K, bn)) return r;
@@ -616,6 +577,17 @@ extern "C" int ft_gemm_bf16(const void* w, const void* x, const void* x_lo, void
     epi.out = out;
     epi.out_lo = out_lo;
     return ft_gemm_fused(w, x, x_lo, n_out, T, K, n_splits, &epi, stream);
+}
+
+extern "C" int ft_debug_gemm_trace(unsigned long long* host_out16) {
+    FT_CHECK_CUDA(cudaDeviceSynchronize());
+    FT_CHECK_CUDA(cudaMemcpyFromSymbol(host_out16, ft::g_gemm_trace, sizeof(unsigned long long) * 16));
+    return 0;
+}
+
+extern "C" long long ft_gemm_scratch_bytes(int n_out, int T, int K, int n_splits) {
+    if (n_splits <= 0) n_splits = ft::gemm_pick_splits(n_out, T, K, ft::device_sms(), true);
+    return (long long)ft::gemm_scratch_floats(n_out, T, n_splits, true) * 4;
 }
 
 extern "C" int ft_gemm_pick_splits(int n_out, int T, int K, int hilo) {

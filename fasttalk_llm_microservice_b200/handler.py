@@ -75,9 +75,9 @@ class EngineRunner:
         return rid
 
     def cancel(self, sink: _Sink):
+        sink.cancelled = True
         with self._lock:
             if sink.rid in self._sinks and not sink.finished:
-                sink.cancelled = True
                 try:
                     self.engine.cancel(sink.rid)
                 except Exception:  # noqa: BLE001
@@ -377,6 +377,8 @@ class NativeHandler:
                     if sink.text:               # held-back text that never became a stop string
                         yield sink.text
                     break
+                if sink.cancelled:              # cancel_generation: stop at once, like the
+                    break                       # reference's per-chunk flag check (vllm_handler.py:181-187)
                 text, hit = self._apply_stop(sink, item)
                 if text:
                     yield text
@@ -409,6 +411,8 @@ class NativeHandler:
                         raise sink.error
                     if sink.text:
                         yield sink.text
+                    break
+                if sink.cancelled:
                     break
                 text, hit = self._apply_stop(sink, item)
                 if text:

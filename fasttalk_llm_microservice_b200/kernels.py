@@ -59,6 +59,13 @@ def gemm_fused(w: torch.Tensor, x: torch.Tensor, x_lo: torch.Tensor, mode: int, 
     T = x.shape[0]
     ep = N.GemmEpilogue()
     ep.mode = mode
+    lib = N.load()
+    if mode in (N.EPI_RESID, N.EPI_QKV_ROPE) and "scratch" not in f:
+        # split-K work buffers: slabs for the partial tiles + self re-arming arrival counters
+        f = dict(f)
+        f["scratch"] = torch.empty(max(1, lib.ft_gemm_scratch_bytes(n_out, T, K, n_splits) // 4), device=x.device,
+                                   dtype=torch.float32)
+        f["sync"] = torch.zeros(2 * (n_out // 128) * ((T + 15) // 16), device=x.device, dtype=torch.int32)
     for name, _ in N.GemmEpilogue._fields_:
         if name == "mode" or name not in f:
             continue

@@ -59,6 +59,7 @@ class GemmEpilogue(C.Structure):
         ("seq_rows", C.c_void_p), ("page_table", C.c_void_p), ("max_pages", C.c_int),
         ("q_out", C.c_void_p), ("kv_layer", C.c_void_p),
         ("nq", C.c_int), ("nkv", C.c_int), ("head_dim", C.c_int),
+        ("scratch", C.c_void_p), ("sync", C.c_void_p),
     ]
 
 
@@ -82,6 +83,8 @@ SIGNATURES = {
     "ft_debug_prefill_logits": (_I, [_VP, _VP, _I, _I, _VP]),
     "ft_gemm_bf16": (_I, [_VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
     "ft_gemm_pick_splits": (_I, [_I, _I, _I, _I]),
+    "ft_debug_gemm_trace": (_I, [_VP]),
+    "ft_gemm_scratch_bytes": (_LL, [_I, _I, _I, _I]),
     "ft_gemm_fused": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, _VP, _VP]),
     "ft_embed_planes": (_I, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _VP]),
     "ft_gather_planes": (_I, [_VP, _VP, _VP, _I, _I, _VP, _I, _I, _VP, _VP, _VP, _I, _VP]),

@@ -131,17 +131,23 @@ int ft_debug_prefill_logits(ft_engine* e, const int* tokens, int n_tokens, int c
 int ft_gemm_bf16(const void* w, const void* x, const void* x_lo, void* out, void* out_lo, int n_out, int T,
                  int K, int n_splits, int out_mode, void* stream);
 int ft_gemm_pick_splits(int n_out, int T, int K, int hilo);
+/* Tuning aid: globaltimer (ns) timeline of CTA (0,0,0) of the most recent GEMM launch -> HOST
+ * uint64[16]: 0 entry, 1 set-up done, 2 weights requested, 3 dependency wait passed, 4 first stage
+ * landed, 5 last MMA issued, 6 accumulator ready, 7 epilogue stores issued, 8 reduce done, 9 exit. */
+int ft_debug_gemm_trace(unsigned long long* host_out16);
 
 /* K3 with the fused epilogues the engine uses.  RMSNorm is applied AFTER the projection: the
  * activation planes hold resid * gamma (un-normalised), the per-token 1/rms is a scalar that
  * commutes with the GEMM, so it is applied in the consumer's epilogue from per-row-tile partial
  * sums of squares.  This removes every stand-alone norm / RoPE kernel from the decode chain.
  *   FT_EPI_SWIGLU  (2): as out_mode 2, gate and up scaled by rstd[t] first (ssq_in may be NULL)
- *   FT_EPI_RESID   (3): split-K partial tiles are reduced across the CTAs of a thread-block
- *                       cluster through distributed shared memory, then
+ *   FT_EPI_RESID   (3): the split-K CTAs of a row tile park their fp32 partial tiles in an
+ *                       L2-resident scratch buffer, rendezvous on a global arrival counter (the
+ *                       grid is one wave, so all of them are resident) and each finishes a share
+ *                       of the tokens:
  *                       resid[t][n] += y;  out/out_lo[t][n] = hi/lo(resid * gamma[n]);
  *                       ssq_out[row_tile][t] = sum over the tile's 128 rows of resid^2
- *   FT_EPI_QKV_ROPE(4): cluster reduce, y *= rstd[t], RoPE on q and k rows, q -> q_out bf16
+ *   FT_EPI_QKV_ROPE(4): same reduction, y *= rstd[t], RoPE on q and k rows, q -> q_out bf16
  *                       [T][nq*d], k/v -> paged KV cache layer (layout of ft_rope_kv_append)
  *   FT_EPI_LOGITS  (5): out fp32 [T][n_out] = y * rstd[t]
  * rstd[t] = rsqrt(sum_p ssq_in[p * ssq_stride + t] * inv_h + eps).  x_lo is required. */
@@ -166,7 +172,10 @@ typedef struct {
     void* q_out;               /* QKV_ROPE: bf16 [T][nq*d] */
     void* kv_layer;            /* QKV_ROPE: paged KV cache layer */
     int nq, nkv, head_dim;
+    float* scratch;            /* RESID / QKV_ROPE with n_splits > 1: ft_gemm_scratch_bytes() of device memory */
+    int* sync;                 /* 〃: int32 [2 * row tiles * token tiles], zero before first use (self re-arming) */
 } ft_gemm_epilogue;
+long long ft_gemm_scratch_bytes(int n_out, int T, int K, int n_splits);
 int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int n_out, int T, int K, int n_splits,
                   const ft_gemm_epilogue* epi, void* stream);
 
