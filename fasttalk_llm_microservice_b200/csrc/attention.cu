@@ -96,7 +96,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                    const int* __restrict__ page_table, int max_pages, const int* __restrict__ ctx_lens,
                    const int* __restrict__ tile_prefix, __nv_bfloat16* __restrict__ out,
                    __nv_bfloat16* __restrict__ out_lo, int* __restrict__ seg_counters,
-                   float* __restrict__ scratch, int B, int nq, int nkv, float scale_log2) {
+                   float* __restrict__ scratch, int B, int nq, int nkv, float scale_log2, int early) {
     using C = AttnCfg<D>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -104,6 +104,13 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
     uint64_t* empty_bar = full_bar + C::STAGES;
     float* merge_buf = reinterpret_cast<float*>(empty_bar + C::STAGES);
     __shared__ int s_last;
+    // `early` (engine, layers >= 1): the producer may start streaming KV tiles BEFORE the
+    // programmatic-dependency wait, because everything it reads then — the tile plan, the page
+    // table and every tile except the one that receives this step's token — was written by
+    // kernels that completed before the previous layer's attention released its dependents
+    // (this kernel triggers its dependents only AFTER its own wait, which is what makes that
+    // chain of completions hold).  The QKV projection's latency then hides behind the first
+    // 96 KB of KV per CTA.
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -117,20 +124,28 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
         fence_mbar_init();
     }
     __syncthreads();
-    pdl_wait();
-    pdl_launch_dependents();
+    const bool is_producer = warp == ATTN_COMPUTE_WARPS;
+    bool waited = false;
+    if (!(is_producer && early)) {
+        pdl_wait();
+        pdl_launch_dependents();
+        waited = true;
+    }
 
     const long long total = (long long)tile_prefix[B] * nkv;
     const long long per = (total + gridDim.x - 1) / gridDim.x;
     long long f = per * blockIdx.x;
     long long f_end = f + per < total ? f + per : total;
-    if (f >= total) return;
+    if (f >= total) {
+        if (!waited) pdl_wait();
+        return;
+    }
     int b_cur = find_seq(tile_prefix, B, nkv, f);
     DecodeSeg seg;
     int stage = 0;
     uint32_t phase = 0;
 
-    if (warp == ATTN_COMPUTE_WARPS) {
+    if (is_producer) {
         // ---------------- producer warp: one bulk-TMA copy per tile
         const uint64_t pol = policy_evict_first();       // every KV byte is read once per step
         while (next_decode_seg(f, f_end, tile_prefix, B, nkv, b_cur, seg)) {
@@ -141,6 +156,10 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                 const int n = seg.tile_end - t0 < 32 ? seg.tile_end - t0 : 32;
                 for (int i = 0; i < n; ++i) {
                     const int page = __shfl_sync(0xffffffffu, my_page, i);
+                    if (!waited && t0 + i == seg.tiles_b - 1) {
+                        pdl_wait();          // the sequence's last tile holds the token appended this step
+                        waited = true;
+                    }
                     if (lane == 0) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         mbar_expect_tx(&full_bar[stage], C::TILE_BYTES);
@@ -152,6 +171,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                 }
             }
         }
+        if (!waited) pdl_wait();
         return;
     }
 
@@ -561,7 +581,7 @@ template <int D>
 static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                                 const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo,
                                 float* scratch, int B, int nq, int nkv, int n_ctas, bool pdl,
-                                cudaStream_t stream, cudaEvent_t ev0, cudaEvent_t ev1) {
+                                cudaStream_t stream, cudaEvent_t ev0, cudaEvent_t ev1, bool early) {
     using C = AttnCfg<D>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -577,7 +597,8 @@ static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* 
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_kernel<D>, (const __nv_bfloat16*)q,
                                      (const uint8_t*)kv_layer, page_table, max_pages, ctx_lens, tile_prefix,
                                      (__nv_bfloat16*)out, (__nv_bfloat16*)out_lo, reinterpret_cast<int*>(scratch),
-                                     scratch + counter_floats(B, nkv), B, nq, nkv, scale_log2));
+                                     scratch + counter_floats(B, nkv), B, nq, nkv, scale_log2,
+                                     (int)(early && pdl && !ev0)));
     if (ev1) FT_CHECK_CUDA(cudaEventRecord(ev1, stream));
     return 0;
 }
@@ -585,15 +606,15 @@ static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* 
 int launch_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                        const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo, float* scratch,
                        int B, int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream,
-                       cudaEvent_t ev0, cudaEvent_t ev1) {
+                       cudaEvent_t ev0, cudaEvent_t ev1, bool early) {
     FT_REQUIRE(d == 64 || d == 128, "attn_decode: head_dim %d not supported (64 or 128)", d);
     FT_REQUIRE(nq % nkv == 0 && nq / nkv <= ATTN_GMAX, "attn_decode: GQA group %d/%d not supported", nq, nkv);
     FT_REQUIRE(B >= 1 && n_ctas >= 1, "attn_decode: B=%d n_ctas=%d", B, n_ctas);
     if (d == 64)
         return launch_attn_decode_d<64>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo,
-                                        scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1);
+                                        scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1, early);
     return launch_attn_decode_d<128>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo,
-                                     scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1);
+                                     scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1, early);
 }
 
 template <int D>
@@ -657,7 +678,7 @@ extern "C" int ft_attn_decode(const void* q, const void* kv_layer, const int* pa
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (int r = ft::launch_attn_decode_plan(ctx_lens, tile_prefix, B, nkv, scratch, false, st)) return r;
     return ft::launch_attn_decode(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo,
-                                  scratch, B, nq, nkv, d, n_ctas, false, st, nullptr, nullptr);
+                                  scratch, B, nq, nkv, d, n_ctas, false, st, nullptr, nullptr, false);
 }
 
 extern "C" int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
@@ -747,5 +768,5 @@ extern "C" int ft_attn_decode_noalloc(const void* q, const void* kv_layer, const
     // previous call left behind is relied upon
     if (int r = launch_attn_decode_plan(ctx_lens, tile_prefix, B, nkv, scratch, false, st)) return r;
     return launch_attn_decode(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo, scratch, B,
-                              nq, nkv, d, n_ctas, false, st, nullptr, nullptr);
+                              nq, nkv, d, n_ctas, false, st, nullptr, nullptr, false);
 }

@@ -220,6 +220,8 @@ static int forward(Engine* e, const Batch& b) {
                                        e->pdl, e->stream));
         e->st.kernel_launches++;
     }
+    // L2 prefetch of the next projection's weights only pays when the GEMMs are latency-bound
+    const bool decode_only = b.n_tiles == 0 && T <= 128;
     ft_gemm_epilogue rstd = {};            // fields shared by every epilogue that applies 1/rms
     rstd.ssq_in = e->ssq;
     rstd.ssq_parts = e->ssq_parts;
@@ -253,7 +255,8 @@ static int forward(Engine* e, const Batch& b) {
             }
             FT_TRY(launch_attn_decode(e->q, kv_l, d + m.o_pt, e->max_pages, d + m.o_ctx, d + m.o_tprefix,
                                       e->attn_out, e->attn_out_lo, e->attn_scratch, b.n_decode, c.n_q_heads,
-                                      c.n_kv_heads, c.head_dim, e->attn_ctas, e->pdl, e->stream, ev0, ev1));
+                                      c.n_kv_heads, c.head_dim, e->attn_ctas, e->pdl, e->stream, ev0, ev1,
+                                      /*early=*/l > 0 && b.n_tiles == 0));
             e->st.kernel_launches++;
         }
         if (b.n_tiles > 0) {
@@ -272,6 +275,10 @@ static int forward(Engine* e, const Batch& b) {
             ep.out_lo = e->xn_lo;
             ep.ssq_out = e->ssq;
             ep.ssq_stride = e->t_max;
+            if (decode_only) {      // stream the gate/up weights into L2 behind this latency-bound kernel
+                ep.prefetch = bf16_off(e->w.wgu, (size_t)l * 2 * c.ffn * H);
+                ep.prefetch_bytes = (long long)2 * c.ffn * H * 2;
+            }
             FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, e->m_attn_lo, T, c.hidden, e->q_dim, ep));
         }
         {   // gate/up projection: 1/rms and SwiGLU in the epilogue, act = silu(g) * u
@@ -279,6 +286,10 @@ static int forward(Engine* e, const Batch& b) {
             ep.mode = FT_EPI_SWIGLU;
             ep.out = e->act;
             ep.out_lo = e->act_lo;
+            if (decode_only) {
+                ep.prefetch = bf16_off(e->w.wd, (size_t)l * c.ffn * H);
+                ep.prefetch_bytes = (long long)c.ffn * H * 2;
+            }
             FT_TRY(run_gemm(e, e->m_wgu[l], e->m_xn, e->m_xn_lo, T, 2 * c.ffn, c.hidden, ep));
         }
         {
@@ -290,6 +301,10 @@ static int forward(Engine* e, const Batch& b) {
             ep.out_lo = e->xn_lo;
             ep.ssq_out = e->ssq;
             ep.ssq_stride = e->t_max;
+            if (decode_only && l + 1 < c.layers) {
+                ep.prefetch = bf16_off(e->w.wqkv, (size_t)(l + 1) * e->qkv_dim * H);
+                ep.prefetch_bytes = (long long)e->qkv_dim * H * 2;
+            }
             FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, e->m_act_lo, T, c.hidden, c.ffn, ep));
         }
     }

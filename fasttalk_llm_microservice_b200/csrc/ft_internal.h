@@ -47,7 +47,7 @@ int launch_attn_decode_plan(const int* ctx_lens, int* tile_prefix, int B, int nk
 int launch_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                        const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo, float* scratch,
                        int B, int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream,
-                       cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr);
+                       cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr, bool early = false);
 int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                         const int* req_q_start, const int* req_slot, const int* req_pos0,
                         const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq,

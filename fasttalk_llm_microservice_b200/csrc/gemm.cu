@@ -78,7 +78,7 @@ __device__ __forceinline__ void store_hi_lo4(__nv_bfloat16* hi, __nv_bfloat16* l
         *reinterpret_cast<uint2*>(lo + idx) = l;
     }
 }
-__device__ __forceinline__ float silu(float g) { return g / (1.f + __expf(-g)); }
+__device__ __forceinline__ float silu(float g) { return __fdividef(g, 1.f + __expf(-g)); }
 
 template <int BN, bool HILO>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -147,6 +147,21 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                 mbar_expect_tx(&full_bar[i], STAGE_BYTES);
                 tma_tile_2d(smem + (size_t)i * STAGE_BYTES, &map_w, (kc_begin + i) * GEMM_BK, row0,
                             &full_bar[i], pol_w);
+            }
+            // Keep HBM busy across the kernel boundary: pull this CTA's share of the NEXT
+            // projection's weights into L2 (126 MB) while this kernel waits on its producer.
+            if (ep.prefetch_bytes > 0) {
+                const unsigned long long n_cta = (unsigned long long)gridDim.x * gridDim.y * gridDim.z;
+                const unsigned long long cta = ((unsigned long long)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+                const unsigned long long total = (unsigned long long)ep.prefetch_bytes;
+                const unsigned long long per = ((total / n_cta) + 16383ull) & ~16383ull;
+                const unsigned long long beg = per * cta;
+                const unsigned long long end = beg + per < total ? beg + per : total;
+                const uint8_t* base = reinterpret_cast<const uint8_t*>(ep.prefetch);
+                for (unsigned long long off = beg; off < end; off += 16384ull) {
+                    const uint32_t sz = (uint32_t)(end - off < 16384ull ? end - off : 16384ull) & ~15u;
+                    if (sz) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(base + off), "r"(sz) : "memory");
+                }
             }
             trace(2);
             pdl_wait();
@@ -225,17 +240,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
         const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
         float* stage_f = reinterpret_cast<float*>(smem);   // pipeline stages are idle once the MMAs retired
         float* slabs = reduce ? ep.scratch + (size_t)tile_id * n_split * (BN * GEMM_BM) : nullptr;
-        float* dst;
-        size_t tok_stride = GEMM_BM;
-        if (mode == FT_EPI_PARTIAL) {
-            dst = reinterpret_cast<float*>(ep.out) + ((size_t)split * T + t0) * n_out + row0;
-            tok_stride = n_out;
-        } else {
-            dst = reduce ? slabs + (size_t)split * (BN * GEMM_BM) : stage_f;
-        }
         {
             constexpr int CPW = BN >= 32 ? BN / 2 : 16;     // columns per warp: two warps share a lane quarter
             const int cbeg = (ew >> 2) * CPW;
+            const int rl = q * 32 + lane;                   // tile row this thread reads out of TMEM
 #pragma unroll 1
             for (int c0 = cbeg; c0 < cbeg + CPW && c0 < BN; c0 += 16) {
                 if (t0 + c0 >= T) break;
@@ -246,11 +254,26 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
 #pragma unroll
                     for (int j = 0; j < 16; ++j) v[j] = 0.f;
                 }
-                float* p = dst + (size_t)c0 * tok_stride + q * 32 + lane;
-                const int valid = mode == FT_EPI_PARTIAL ? T - (t0 + c0) : 16;
+                // three store flavours, each with compile-time strides so that no address
+                // arithmetic is left in the unrolled body
+                if (mode == FT_EPI_PARTIAL) {
+                    float* p = reinterpret_cast<float*>(ep.out) + ((size_t)split * T + t0 + c0) * n_out + row0 + rl;
+                    const int valid = T - (t0 + c0);
 #pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    if (j < valid) p[(size_t)j * tok_stride] = v[j];
+                    for (int j = 0; j < 16; ++j) {
+                        if (j < valid) *p = v[j];
+                        p += n_out;
+                    }
+                } else if (reduce) {
+                    float* p = slabs + ((size_t)split * BN + c0) * GEMM_BM + rl;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) __stcg(p + j * GEMM_BM, v[j]);
+                } else {
+                    const uint32_t a = smem_u32(stage_f) + (uint32_t)(c0 * GEMM_BM + rl) * 4;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + j * GEMM_BM * 4), "f"(v[j]) : "memory");
+                }
             }
         }
         if (et == 0) trace(7);
@@ -335,14 +358,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                         store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(slab + off), nullptr, 0, val);
                     }
                 } else if (mode == FT_EPI_SWIGLU) {
-                    // lanes 0..15 hold gate features 0..63 of the tile, lanes 16..31 the matching up features
-                    const float4 u = f4_shfl_xor(y, 16);
-                    if (lane < 16) {
-                        const float4 a = make_float4(silu(y.x * rs) * (u.x * rs), silu(y.y * rs) * (u.y * rs),
-                                                     silu(y.z * rs) * (u.z * rs), silu(y.w * rs) * (u.w * rs));
-                        store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
-                                     (size_t)t * (n_out >> 1) + blockIdx.x * 64 + r4, a);
-                    }
+                    // rows 0..63 of the tile are gate features, rows 64..127 the matching up features:
+                    // every lane finishes two features (all 32 lanes busy, no shuffles)
+                    const float2 g2 = *reinterpret_cast<const float2*>(stage_f + j * GEMM_BM + 2 * lane);
+                    const float2 u2 = *reinterpret_cast<const float2*>(stage_f + j * GEMM_BM + 64 + 2 * lane);
+                    const float a0 = silu(g2.x * rs) * (u2.x * rs), a1 = silu(g2.y * rs) * (u2.y * rs);
+                    const uint32_t h = pack_bf16(a0, a1);
+                    const size_t idx = (size_t)t * (n_out >> 1) + blockIdx.x * 64 + 2 * lane;
+                    *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + idx) = h;
+                    if (ep.out_lo)
+                        *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out_lo) + idx) =
+                            pack_bf16(a0 - bf16_lo(h), a1 - bf16_hi(h));
                 } else if (mode == FT_EPI_LOGITS) {
                     *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + (size_t)t * n_out + row) = f4_mul(y, rs);
                 } else {   // FT_EPI_BF16

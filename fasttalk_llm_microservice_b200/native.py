@@ -60,6 +60,7 @@ class GemmEpilogue(C.Structure):
         ("q_out", C.c_void_p), ("kv_layer", C.c_void_p),
         ("nq", C.c_int), ("nkv", C.c_int), ("head_dim", C.c_int),
         ("scratch", C.c_void_p), ("sync", C.c_void_p),
+        ("prefetch", C.c_void_p), ("prefetch_bytes", C.c_longlong),
     ]
 
 

@@ -174,6 +174,8 @@ typedef struct {
     int nq, nkv, head_dim;
     float* scratch;            /* RESID / QKV_ROPE with n_splits > 1: ft_gemm_scratch_bytes() of device memory */
     int* sync;                 /* 〃: int32 [2 * row tiles * token tiles], zero before first use (self re-arming) */
+    const void* prefetch;      /* optional: a contiguous region (the NEXT projection's weights) the CTAs pull */
+    long long prefetch_bytes;  /*   into L2 while this kernel sits in its dependency / epilogue latency */
 } ft_gemm_epilogue;
 long long ft_gemm_scratch_bytes(int n_out, int T, int K, int n_splits);
 int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int n_out, int T, int K, int n_splits,
