@@ -109,4 +109,6 @@ def test_disconnect_frees_the_slot_and_sampling_runs(stack):
     assert eng.stats()["active_requests"] == 0 and h.get_active_requests() == {}
     out = list(h.generate_stream([{"role": "user", "content": "hello"}], temperature=0.8, top_p=0.9, top_k=40,
                                  max_tokens=12))
-    assert len(out) == 12
+    # 12 sampled tokens; a token that leaves a UTF-8 sequence open (or a special id) yields no
+    # chunk of its own, so there are at most 12 non-empty chunks
+    assert 1 <= len(out) <= 12 and all(out)
