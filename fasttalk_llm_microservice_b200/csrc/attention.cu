@@ -96,8 +96,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                    const int* __restrict__ page_table, int max_pages, const int* __restrict__ ctx_lens,
                    const int* __restrict__ tile_prefix, __nv_bfloat16* __restrict__ out,
                    __nv_bfloat16* __restrict__ out_lo, int* __restrict__ seg_counters,
-                   float* __restrict__ scratch, int B, int nq, int nkv, float scale_log2, int early,
-                   const unsigned* __restrict__ dep_in, unsigned dep_expected, unsigned* __restrict__ dep_out) {
+                   float* __restrict__ scratch, int B, int nq, int nkv, float scale_log2, int early) {
     using C = AttnCfg<D>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -126,19 +125,9 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
     }
     __syncthreads();
     const bool is_producer = warp == ATTN_COMPUTE_WARPS;
-    // wait for the QKV projection: a polled data flag inside the engine, else the plain
-    // programmatic dependency (one lane polls, the warp re-converges behind it)
-    auto wait_producer = [&]() {
-        if (dep_in) {
-            if (lane == 0) dep_wait(dep_in, dep_expected);
-            __syncwarp();
-        } else {
-            pdl_wait();
-        }
-    };
     bool waited = false;
     if (!(is_producer && early)) {
-        wait_producer();
+        pdl_wait();
         pdl_launch_dependents();
         waited = true;
     }
@@ -148,8 +137,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
     long long f = per * blockIdx.x;
     long long f_end = f + per < total ? f + per : total;
     if (f >= total) {
-        if (!waited) wait_producer();
-        if (dep_out && threadIdx.x == 0) dep_signal(dep_out);      // idle CTA: nothing to store
+        if (!waited) pdl_wait();
         return;
     }
     int b_cur = find_seq(tile_prefix, B, nkv, f);
@@ -169,7 +157,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                 for (int i = 0; i < n; ++i) {
                     const int page = __shfl_sync(0xffffffffu, my_page, i);
                     if (!waited && t0 + i == seg.tiles_b - 1) {
-                        wait_producer();     // the sequence's last tile holds the token appended this step
+                        pdl_wait();          // the sequence's last tile holds the token appended this step
                         waited = true;
                     }
                     if (lane == 0) {
@@ -183,7 +171,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                 }
             }
         }
-        if (!waited) wait_producer();
+        if (!waited) pdl_wait();
         return;
     }
 
@@ -355,11 +343,6 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
             }
         }
         compute_bar_sync();
-    }
-    if (dep_out) {                              // every output row of this CTA is stored
-        __threadfence();
-        compute_bar_sync();
-        if (threadIdx.x == 0) dep_signal(dep_out);
     }
 }
 
@@ -598,8 +581,7 @@ template <int D>
 static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                                 const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo,
                                 float* scratch, int B, int nq, int nkv, int n_ctas, bool pdl,
-                                cudaStream_t stream, cudaEvent_t ev0, cudaEvent_t ev1, bool early,
-                                const unsigned* dep_in, unsigned dep_expected, unsigned* dep_out) {
+                                cudaStream_t stream, cudaEvent_t ev0, cudaEvent_t ev1, bool early) {
     using C = AttnCfg<D>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -616,7 +598,7 @@ static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* 
                                      (const uint8_t*)kv_layer, page_table, max_pages, ctx_lens, tile_prefix,
                                      (__nv_bfloat16*)out, (__nv_bfloat16*)out_lo, reinterpret_cast<int*>(scratch),
                                      scratch + counter_floats(B, nkv), B, nq, nkv, scale_log2,
-                                     (int)(early && pdl && !ev0), dep_in, dep_expected, dep_out));
+                                     (int)(early && pdl && !ev0)));
     if (ev1) FT_CHECK_CUDA(cudaEventRecord(ev1, stream));
     return 0;
 }
@@ -624,18 +606,15 @@ static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* 
 int launch_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                        const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo, float* scratch,
                        int B, int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream,
-                       cudaEvent_t ev0, cudaEvent_t ev1, bool early, const unsigned* dep_in,
-                       unsigned dep_expected, unsigned* dep_out) {
+                       cudaEvent_t ev0, cudaEvent_t ev1, bool early) {
     FT_REQUIRE(d == 64 || d == 128, "attn_decode: head_dim %d not supported (64 or 128)", d);
     FT_REQUIRE(nq % nkv == 0 && nq / nkv <= ATTN_GMAX, "attn_decode: GQA group %d/%d not supported", nq, nkv);
     FT_REQUIRE(B >= 1 && n_ctas >= 1, "attn_decode: B=%d n_ctas=%d", B, n_ctas);
     if (d == 64)
         return launch_attn_decode_d<64>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo,
-                                        scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1, early, dep_in,
-                                        dep_expected, dep_out);
+                                        scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1, early);
     return launch_attn_decode_d<128>(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo,
-                                     scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1, early, dep_in, dep_expected,
-                                     dep_out);
+                                     scratch, B, nq, nkv, n_ctas, pdl, stream, ev0, ev1, early);
 }
 
 template <int D>
@@ -699,7 +678,7 @@ extern "C" int ft_attn_decode(const void* q, const void* kv_layer, const int* pa
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (int r = ft::launch_attn_decode_plan(ctx_lens, tile_prefix, B, nkv, scratch, false, st)) return r;
     return ft::launch_attn_decode(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo,
-                                  scratch, B, nq, nkv, d, n_ctas, false, st, nullptr, nullptr, false, nullptr, 0, nullptr);
+                                  scratch, B, nq, nkv, d, n_ctas, false, st, nullptr, nullptr, false);
 }
 
 extern "C" int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
@@ -789,5 +768,5 @@ extern "C" int ft_attn_decode_noalloc(const void* q, const void* kv_layer, const
     // previous call left behind is relied upon
     if (int r = launch_attn_decode_plan(ctx_lens, tile_prefix, B, nkv, scratch, false, st)) return r;
     return launch_attn_decode(q, kv_layer, page_table, max_pages, ctx_lens, tile_prefix, out, out_lo, scratch, B,
-                              nq, nkv, d, n_ctas, false, st, nullptr, nullptr, false, nullptr, 0, nullptr);
+                              nq, nkv, d, n_ctas, false, st, nullptr, nullptr, false);
 }

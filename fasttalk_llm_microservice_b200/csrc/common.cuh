@@ -65,29 +65,6 @@ __device__ __forceinline__ void pdl_launch_dependents() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
-// ------------------------------------------------------------------ kernel-to-kernel data flags
-// The decode step's kernels are chained with programmatic dependent launch, but
-// griddepcontrol.wait only returns once the WHOLE producer grid has retired and flushed
-// (~4-5 us per boundary on these microsecond kernels).  Inside the engine a kernel instead
-// bumps a global counter when a CTA's results are stored, and its consumer (already resident
-// thanks to PDL, weights prefetched) polls that counter: the hand-over costs one L2 round trip.
-// Safe because a PDL dependent is only scheduled once every producer CTA is running.
-__device__ __forceinline__ void dep_signal(unsigned* flag) {      // one thread per CTA, after a fence + CTA barrier
-    atomicAdd(flag, 1u);
-}
-__device__ __forceinline__ void dep_wait(const unsigned* flag, unsigned expected) {
-    unsigned v, spins = 0;
-    for (;;) {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
-        if (v >= expected) break;
-        __nanosleep(20);
-        if (++spins > (1u << 26)) __trap();      // producer never finished: fail loudly instead of hanging
-    }
-    // the data may be consumed next through the async proxy (TMA), which is ordered against the
-    // generic-proxy acquire above only by a proxy fence
-    asm volatile("fence.proxy.async;" ::: "memory");
-}
-
 // ------------------------------------------------------------------ mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(NORM_THREADS)
 embed_planes_kernel(const int* __restrict__ tokens, const __nv_bfloat16* __restrict__ embed,
                     const __nv_bfloat16* __restrict__ gamma, float* __restrict__ resid,
                     __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo,
-                    float* __restrict__ ssq, int ssq_parts, int ssq_stride, int h, unsigned* __restrict__ dep_out) {
+                    float* __restrict__ ssq, int ssq_parts, int ssq_stride, int h) {
     pdl_wait();
     pdl_launch_dependents();
     const int t = blockIdx.x;
@@ -136,11 +136,6 @@ embed_planes_kernel(const int* __restrict__ tokens, const __nv_bfloat16* __restr
         if (threadIdx.x == 0)
             for (int k = 0; k < NORM_THREADS / 32; ++k) tot += red[k];
         ssq[(size_t)threadIdx.x * ssq_stride + t] = tot;
-    }
-    if (dep_out) {
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0) dep_signal(dep_out);
     }
 }
 
@@ -325,7 +320,7 @@ int launch_rope_kv_append(const float* qkv, int n_splits, size_t split_stride, c
 
 int launch_embed_planes(const int* tokens, const void* embed, const void* gamma, float* resid, void* out,
                         void* out_lo, float* ssq, int ssq_parts, int ssq_stride, int T, int h, bool pdl,
-                        cudaStream_t stream, unsigned* dep_out) {
+                        cudaStream_t stream) {
     FT_REQUIRE(h % 4 == 0 && ssq_parts >= 1 && ssq_parts <= NORM_THREADS && T >= 1,
                "embed_planes: bad shape h=%d parts=%d T=%d", h, ssq_parts, T);
     cudaLaunchConfig_t cfg;
@@ -333,7 +328,7 @@ int launch_embed_planes(const int* tokens, const void* embed, const void* gamma,
     fill_cfg(cfg, attr, dim3(T), dim3(NORM_THREADS), 0, pdl, stream);
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, embed_planes_kernel, tokens, (const __nv_bfloat16*)embed,
                                      (const __nv_bfloat16*)gamma, resid, (__nv_bfloat16*)out,
-                                     (__nv_bfloat16*)out_lo, ssq, ssq_parts, ssq_stride, h, dep_out));
+                                     (__nv_bfloat16*)out_lo, ssq, ssq_parts, ssq_stride, h));
     return 0;
 }
 
@@ -390,7 +385,7 @@ extern "C" int ft_embed_planes(const int* tokens, const void* embed_table, const
                                void* out, void* out_lo, float* ssq, int ssq_parts, int ssq_stride, int T, int h,
                                void* stream) {
     return ft::launch_embed_planes(tokens, embed_table, gamma, resid, out, out_lo, ssq, ssq_parts, ssq_stride, T,
-                                   h, false, static_cast<cudaStream_t>(stream), nullptr);
+                                   h, false, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int ft_gather_planes(const void* x, const void* x_lo, const float* ssq, int ssq_parts, int ssq_stride,

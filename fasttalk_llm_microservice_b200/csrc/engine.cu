@@ -84,8 +84,6 @@ struct Engine {
     int ssq_parts = 0, rows_last = 0;
     float* gemm_scratch = nullptr; // split-K slabs of the fused-epilogue GEMMs (one wave of CTAs)
     int* gemm_sync = nullptr;      // their arrival counters
-    unsigned* dep_flags = nullptr; // one data flag per kernel of a decode step (common.cuh: dep_signal / dep_wait)
-    int dep_cap = 0;
     // bf16 activations feeding the GEMMs are kept as hi + lo planes (see gemm.cu)
     void *xn = nullptr, *q = nullptr, *attn_out = nullptr, *act = nullptr, *xn_last = nullptr;
     void *xn_lo = nullptr, *attn_out_lo = nullptr, *act_lo = nullptr, *xn_last_lo = nullptr;
@@ -189,28 +187,13 @@ struct Batch {
 
 // One projection with a fused epilogue.  `staged` epilogues (RESID / QKV_ROPE) split K across
 // one wave of CTAs that rendezvous in the epilogue; the others run unsplit.
-// Position in the step's chain of data flags: kernel i polls flag i-1 until the previous kernel's
-// CTAs have all signalled, and signals flag i itself.
-struct DepChain {
-    bool on = false;
-    int idx = 0;                  // flag this launch signals
-    unsigned prev_ctas = 0;       // CTAs of the previous launch (what flag idx-1 must reach)
-};
-
 static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, const CUtensorMap* xmaps_lo,
-                    int T, int n_out, int K, ft_gemm_epilogue epi, DepChain* dc = nullptr, bool last = false) {
+                    int T, int n_out, int K, ft_gemm_epilogue epi) {
     const int bn = gemm_pick_bn(T, true);
     const bool staged = epi.mode == FT_EPI_RESID || epi.mode == FT_EPI_QKV_ROPE;
     const int splits = staged ? gemm_pick_splits(n_out, T, K, e->sms, true) : 1;
     epi.scratch = e->gemm_scratch;
     epi.sync = e->gemm_sync;
-    if (dc && dc->on) {
-        epi.dep_in = e->dep_flags + dc->idx - 1;
-        epi.dep_expected = dc->prev_ctas;
-        epi.dep_out = last ? nullptr : e->dep_flags + dc->idx;
-        dc->prev_ctas = (unsigned)((n_out / 128) * ((T + bn - 1) / bn) * splits);
-        dc->idx++;
-    }
     e->st.kernel_launches++;
     return launch_gemm(mw, xmaps[bn_index(bn)], &xmaps_lo[bn_index(bn)], bn, n_out, T, K, splits, epi, e->pdl,
                        e->stream);
@@ -229,25 +212,16 @@ static int forward(Engine* e, const Batch& b) {
     auto bf16_off = [](const void* p, size_t elems) {
         return (const void*)((const uint8_t*)p + elems * 2);
     };
-    // L2 prefetch of the next projection's weights only pays when the GEMMs are latency-bound
-    const bool decode_only = b.n_tiles == 0 && T <= 128;
-    // Pure decode steps chain their kernels with polled data flags instead of full grid
-    // completion (common.cuh).  The plan kernel runs first and the embed kernel waits for it the
-    // ordinary way, so everything downstream of the embed flag also sees the plan.
-    DepChain dc;
-    dc.on = decode_only && e->pdl && !e->profile && 5 * c.layers + 4 <= e->dep_cap;
-    if (dc.on) FT_CHECK_CUDA(cudaMemsetAsync(e->dep_flags, 0, (size_t)(5 * c.layers + 4) * sizeof(unsigned), e->stream));
+    FT_TRY(launch_embed_planes(d + m.o_tokens, e->w.embed, e->w.attn_norm, e->resid, e->xn, e->xn_lo, e->ssq,
+                               e->ssq_parts, e->t_max, T, c.hidden, e->pdl, e->stream));
+    e->st.kernel_launches++;
     if (b.n_decode > 0) {
         FT_TRY(launch_attn_decode_plan(d + m.o_ctx, d + m.o_tprefix, b.n_decode, c.n_kv_heads, e->attn_scratch,
                                        e->pdl, e->stream));
         e->st.kernel_launches++;
     }
-    FT_TRY(launch_embed_planes(d + m.o_tokens, e->w.embed, e->w.attn_norm, e->resid, e->xn, e->xn_lo, e->ssq,
-                               e->ssq_parts, e->t_max, T, c.hidden, e->pdl, e->stream,
-                               dc.on ? e->dep_flags + 0 : nullptr));
-    e->st.kernel_launches++;
-    dc.idx = 1;
-    dc.prev_ctas = (unsigned)T;
+    // L2 prefetch of the next projection's weights only pays when the GEMMs are latency-bound
+    const bool decode_only = b.n_tiles == 0 && T <= 128;
     ft_gemm_epilogue rstd = {};            // fields shared by every epilogue that applies 1/rms
     rstd.ssq_in = e->ssq;
     rstd.ssq_parts = e->ssq_parts;
@@ -270,7 +244,7 @@ static int forward(Engine* e, const Batch& b) {
             ep.nq = c.n_q_heads;
             ep.nkv = c.n_kv_heads;
             ep.head_dim = c.head_dim;
-            FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, e->m_xn_lo, T, e->qkv_dim, c.hidden, ep, &dc));
+            FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, e->m_xn_lo, T, e->qkv_dim, c.hidden, ep));
         }
         if (b.n_decode > 0) {
             cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -282,12 +256,7 @@ static int forward(Engine* e, const Batch& b) {
             FT_TRY(launch_attn_decode(e->q, kv_l, d + m.o_pt, e->max_pages, d + m.o_ctx, d + m.o_tprefix,
                                       e->attn_out, e->attn_out_lo, e->attn_scratch, b.n_decode, c.n_q_heads,
                                       c.n_kv_heads, c.head_dim, e->attn_ctas, e->pdl, e->stream, ev0, ev1,
-                                      /*early=*/l > 0 && b.n_tiles == 0, dc.on ? e->dep_flags + dc.idx - 1 : nullptr,
-                                      dc.prev_ctas, dc.on ? e->dep_flags + dc.idx : nullptr));
-            if (dc.on) {
-                dc.prev_ctas = (unsigned)e->attn_ctas;
-                dc.idx++;
-            }
+                                      /*early=*/l > 0 && b.n_tiles == 0));
             e->st.kernel_launches++;
         }
         if (b.n_tiles > 0) {
@@ -310,7 +279,7 @@ static int forward(Engine* e, const Batch& b) {
                 ep.prefetch = bf16_off(e->w.wgu, (size_t)l * 2 * c.ffn * H);
                 ep.prefetch_bytes = (long long)2 * c.ffn * H * 2;
             }
-            FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, e->m_attn_lo, T, c.hidden, e->q_dim, ep, &dc));
+            FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, e->m_attn_lo, T, c.hidden, e->q_dim, ep));
         }
         {   // gate/up projection: 1/rms and SwiGLU in the epilogue, act = silu(g) * u
             ft_gemm_epilogue ep = rstd;
@@ -321,7 +290,7 @@ static int forward(Engine* e, const Batch& b) {
                 ep.prefetch = bf16_off(e->w.wd, (size_t)l * c.ffn * H);
                 ep.prefetch_bytes = (long long)c.ffn * H * 2;
             }
-            FT_TRY(run_gemm(e, e->m_wgu[l], e->m_xn, e->m_xn_lo, T, 2 * c.ffn, c.hidden, ep, &dc));
+            FT_TRY(run_gemm(e, e->m_wgu[l], e->m_xn, e->m_xn_lo, T, 2 * c.ffn, c.hidden, ep));
         }
         {
             ft_gemm_epilogue ep = {};
@@ -336,7 +305,7 @@ static int forward(Engine* e, const Batch& b) {
                 ep.prefetch = bf16_off(e->w.wqkv, (size_t)(l + 1) * e->qkv_dim * H);
                 ep.prefetch_bytes = (long long)e->qkv_dim * H * 2;
             }
-            FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, e->m_act_lo, T, c.hidden, c.ffn, ep, &dc));
+            FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, e->m_act_lo, T, c.hidden, c.ffn, ep));
         }
     }
     if (b.n_logit_rows > 0) {
@@ -356,9 +325,7 @@ static int forward(Engine* e, const Batch& b) {
             ep.ssq_in = e->ssq_last;
             ep.ssq_stride = e->rows_last;
         }
-        // the LM head is the last link of the flag chain; the sampler after it waits the ordinary way
-        FT_TRY(run_gemm(e, e->m_lm, xm, xl, b.n_logit_rows, c.vocab, c.hidden, ep,
-                        b.logit_rows_identity ? &dc : nullptr, /*last=*/true));
+        FT_TRY(run_gemm(e, e->m_lm, xm, xl, b.n_logit_rows, c.vocab, c.hidden, ep));
     }
     return 0;
 }
@@ -630,9 +597,6 @@ static int engine_init(Engine* e) {
         e->gemm_scratch = static_cast<float*>(p);
         FT_TRY(alloc_zero(&p, (size_t)2 * e->sms * 4));
         e->gemm_sync = static_cast<int*>(p);
-        e->dep_cap = 5 * c.layers + 8;
-        FT_TRY(alloc_zero(&p, (size_t)e->dep_cap * sizeof(unsigned)));
-        e->dep_flags = static_cast<unsigned*>(p);
     }
 
     // decode attention: persistent grid = SMs x resident CTAs
@@ -704,7 +668,7 @@ static void engine_free(Engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     for (auto& kv : e->sessions) delete kv.second;
     for (auto& kv : e->requests) delete kv.second;
-    cudaFree(e->kv); cudaFree(e->resid); cudaFree(e->ssq); cudaFree(e->ssq_last); cudaFree(e->gemm_scratch); cudaFree(e->gemm_sync); cudaFree(e->dep_flags); cudaFree(e->xn); cudaFree(e->q);
+    cudaFree(e->kv); cudaFree(e->resid); cudaFree(e->ssq); cudaFree(e->ssq_last); cudaFree(e->gemm_scratch); cudaFree(e->gemm_sync); cudaFree(e->xn); cudaFree(e->q);
     cudaFree(e->attn_out); cudaFree(e->act); cudaFree(e->xn_last); cudaFree(e->logits);
     cudaFree(e->xn_lo); cudaFree(e->attn_out_lo); cudaFree(e->act_lo); cudaFree(e->xn_last_lo);
     cudaFree(e->attn_scratch); cudaFree(e->meta.d);

@@ -31,7 +31,7 @@ int launch_rope_kv_append(const float* qkv, int n_splits, size_t split_stride, c
                           int nq, int nkv, int d, bool pdl, cudaStream_t stream);
 int launch_embed_planes(const int* tokens, const void* embed, const void* gamma, float* resid, void* out,
                         void* out_lo, float* ssq, int ssq_parts, int ssq_stride, int T, int h, bool pdl,
-                        cudaStream_t stream, unsigned* dep_out = nullptr);
+                        cudaStream_t stream);
 int launch_gather_planes(const void* x, const void* x_lo, const float* ssq, int ssq_parts, int ssq_stride,
                          const int* row_idx, int n_rows, int h, void* out, void* out_lo, float* ssq_out,
                          int ssq_out_stride, bool pdl, cudaStream_t stream);
@@ -47,8 +47,7 @@ int launch_attn_decode_plan(const int* ctx_lens, int* tile_prefix, int B, int nk
 int launch_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                        const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo, float* scratch,
                        int B, int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream,
-                       cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr, bool early = false,
-                       const unsigned* dep_in = nullptr, unsigned dep_expected = 0, unsigned* dep_out = nullptr);
+                       cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr, bool early = false);
 int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                         const int* req_q_start, const int* req_slot, const int* req_pos0,
                         const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq,

@@ -164,7 +164,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                 }
             }
             trace(2);
-            if (ep.dep_in) dep_wait(ep.dep_in, ep.dep_expected); else pdl_wait();
+            pdl_wait();
             trace(3);
             for (int i = 0; i < pre; ++i) {
                 uint8_t* bs = smem + (size_t)i * STAGE_BYTES + GEMM_A_BYTES;
@@ -218,13 +218,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
         const int q = warp & 3;                 // TMEM lane quarter this warp may read (warp_id % 4)
         const int et = threadIdx.x - 64;        // 0..255
         const bool reduce = (mode == FT_EPI_RESID || mode == FT_EPI_QKV_ROPE) && n_split > 1;
-        // ssq_in / resid / positions come from earlier kernels
-        if (ep.dep_in) {
-            if (et == 0) dep_wait(ep.dep_in, ep.dep_expected);
-            epi_bar_sync();
-        } else {
-            pdl_wait();
-        }
+        pdl_wait();                             // ssq_in / resid / positions come from earlier kernels
         // per-token 1/rms of the activation's source (RMSNorm deferred past the projection)
         for (int j = et; j < BN; j += GEMM_EPI_THREADS) {
             float r = 1.f;
@@ -390,11 +384,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                     cnt[1] = 0;
                 }
             }
-        }
-        if (ep.dep_out) {                       // hand the results to the next kernel of the chain
-            __threadfence();
-            epi_bar_sync();
-            if (et == 0) dep_signal(ep.dep_out);
         }
         if (et == 0) trace(8);
     }

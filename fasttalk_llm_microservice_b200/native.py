@@ -61,7 +61,6 @@ class GemmEpilogue(C.Structure):
         ("nq", C.c_int), ("nkv", C.c_int), ("head_dim", C.c_int),
         ("scratch", C.c_void_p), ("sync", C.c_void_p),
         ("prefetch", C.c_void_p), ("prefetch_bytes", C.c_longlong),
-        ("dep_in", C.c_void_p), ("dep_expected", C.c_uint), ("dep_out", C.c_void_p),
     ]
 
 

@@ -176,9 +176,6 @@ typedef struct {
     int* sync;                 /* 〃: int32 [2 * row tiles * token tiles], zero before first use (self re-arming) */
     const void* prefetch;      /* optional: a contiguous region (the NEXT projection's weights) the CTAs pull */
     long long prefetch_bytes;  /*   into L2 while this kernel sits in its dependency / epilogue latency */
-    const unsigned* dep_in;    /* engine pipeline flags (NULL = plain programmatic dependency): poll *dep_in until */
-    unsigned dep_expected;     /*   it reaches dep_expected instead of waiting for the producer grid to retire,   */
-    unsigned* dep_out;         /*   and add 1 to *dep_out once this CTA's results are stored                      */
 } ft_gemm_epilogue;
 long long ft_gemm_scratch_bytes(int n_out, int T, int K, int n_splits);
 int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int n_out, int T, int K, int n_splits,
