@@ -24,6 +24,7 @@ namespace ft {
 constexpr int ATTN_COMPUTE_WARPS = 4;
 constexpr int ATTN_THREADS = (ATTN_COMPUTE_WARPS + 1) * 32;
 constexpr int ATTN_GMAX = 8;                       // q heads per kv head supported (rows 0..7)
+constexpr int ATTN_MAX_B_SMEM = 1024;              // batches up to this size keep the tile plan in smem
 constexpr float LOG2E = 1.4426950408889634f;
 
 template <int D>
@@ -90,6 +91,19 @@ __global__ void attn_decode_plan_kernel(const int* __restrict__ ctx_lens, int* _
     }
 }
 
+// Always-on per-CTA timeline of the most recent decode-attention launch (globaltimer ns):
+// [cta][0] entry, [1] first tile landed, [2] last tile consumed, [3] exit.  Read back with
+// ft_debug_attn_trace (tuning aid, scripts/trace_attn.py).
+constexpr int ATTN_TRACE_CTAS = 1024;
+__device__ unsigned long long g_attn_trace[ATTN_TRACE_CTAS * 4];
+__device__ __forceinline__ void attn_trace(int slot) {
+    if (blockIdx.x < ATTN_TRACE_CTAS) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_attn_trace[blockIdx.x * 4 + slot] = t;
+    }
+}
+
 template <int D>
 __global__ void __launch_bounds__(ATTN_THREADS)
 attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restrict__ kv_layer,
@@ -104,6 +118,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
     uint64_t* empty_bar = full_bar + C::STAGES;
     float* merge_buf = reinterpret_cast<float*>(empty_bar + C::STAGES);
     __shared__ int s_last;
+    __shared__ int s_prefix[ATTN_MAX_B_SMEM + 1];     // tile plan, searched many times per CTA
     // `early` (engine, layers >= 1): the producer may start streaming KV tiles BEFORE the
     // programmatic-dependency wait, because everything it reads then — the tile plan, the page
     // table and every tile except the one that receives this step's token — was written by
@@ -115,6 +130,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int G = nq / nkv;
+    if (threadIdx.x == 0) { attn_trace(0); g_attn_trace[(blockIdx.x < ATTN_TRACE_CTAS ? blockIdx.x : 0) * 4 + 1] = 0; }
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < C::STAGES; ++s) {
@@ -123,10 +139,21 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
         }
         fence_mbar_init();
     }
-    __syncthreads();
     const bool is_producer = warp == ATTN_COMPUTE_WARPS;
     bool waited = false;
-    if (!(is_producer && early)) {
+    if (!early) {                       // the tile plan itself may come from the previous kernel
+        pdl_wait();
+        pdl_launch_dependents();
+        waited = true;
+    }
+    // one coalesced read of the tile plan instead of a dependent global load per search step
+    // (the start-up chain was 3.3 us of idle HBM per launch, scripts/trace_attn.py)
+    if (B <= ATTN_MAX_B_SMEM) {
+        for (int i = threadIdx.x; i <= B; i += ATTN_THREADS) s_prefix[i] = tile_prefix[i];
+        tile_prefix = s_prefix;
+    }
+    __syncthreads();
+    if (!waited && !is_producer) {
         pdl_wait();
         pdl_launch_dependents();
         waited = true;
@@ -200,6 +227,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
 
         for (int tile = seg.tile_begin; tile < seg.tile_end; ++tile) {
             mbar_wait(&full_bar[stage], phase);
+            if (threadIdx.x == 0 && blockIdx.x < ATTN_TRACE_CTAS && g_attn_trace[blockIdx.x * 4 + 1] == 0) attn_trace(1);
             const uint32_t kbase = smem_u32(smem + (size_t)stage * C::TILE_BYTES);
             const uint32_t vbase = kbase + C::SLAB_BYTES;
 
@@ -263,6 +291,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
             if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
 
+        if (threadIdx.x == 0) attn_trace(2);
         // ---- combine the four warps' partial states for this (sequence, head) segment
         l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
         l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
@@ -311,9 +340,9 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
             // The last CTA to deliver a part of this (sequence, head) merges all of them.
             const long long F0 = (long long)tile_prefix[seg.b] * nkv + (long long)seg.h * seg.tiles_b;
             const int c_first = (int)(F0 / per), c_last = (int)((F0 + seg.tiles_b - 1) / per);
-            __threadfence();
             compute_bar_sync();
             if (threadIdx.x == 0) {
+                __threadfence();            // cumulative: publishes the whole CTA's partial record
                 const int old = atomicAdd(&seg_counters[seg_idx], 1);
                 const int last = old == c_last - c_first;
                 if (last) seg_counters[seg_idx] = 0;      // re-arm for the next layer's launch
@@ -344,6 +373,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
         }
         compute_bar_sync();
     }
+    if (threadIdx.x == 0) attn_trace(3);
 }
 
 // ------------------------------------------------------------------ K6 chunked prefill
@@ -657,6 +687,13 @@ int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_tab
 }  // namespace ft
 
 // ------------------------------------------------------------------ C ABI (kernel level)
+extern "C" int ft_debug_attn_trace(unsigned long long* host_out, int n_ctas) {
+    if (n_ctas > ft::ATTN_TRACE_CTAS) n_ctas = ft::ATTN_TRACE_CTAS;
+    FT_CHECK_CUDA(cudaDeviceSynchronize());
+    FT_CHECK_CUDA(cudaMemcpyFromSymbol(host_out, ft::g_attn_trace, sizeof(unsigned long long) * 4 * n_ctas));
+    return 0;
+}
+
 extern "C" int ft_attn_decode_default_ctas(int d) {
     int dev = 0, sms = 0;
     if (cudaGetDevice(&dev) != cudaSuccess ||

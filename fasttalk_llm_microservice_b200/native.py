@@ -94,6 +94,7 @@ SIGNATURES = {
     "ft_silu_mul": (_I, [_VP, _I, _LL, _VP, _VP, _I, _I, _VP]),
     "ft_attn_decode_scratch_bytes": (_LL, [_I, _I, _I, _I, _I]),
     "ft_attn_decode_default_ctas": (_I, [_I]),
+    "ft_debug_attn_trace": (_I, [_VP, _I]),
     "ft_attn_decode": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
     "ft_attn_decode_noalloc": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
     "ft_attn_prefill": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP, _I, _VP, _VP, _I, _I, _I, _VP]),

@@ -214,6 +214,9 @@ int ft_silu_mul(const float* gu, int n_splits, long long split_stride, void* act
  * out bf16 [B][nq*d] (+ residual plane out_lo, may be NULL).  `tile_prefix` (int32 [B+1]) and
  * `scratch` (ft_attn_decode_scratch_bytes) are device work buffers the call fills. */
 long long ft_attn_decode_scratch_bytes(int B, int nkv, int group, int d, int n_ctas);
+/* Tuning aid: per-CTA globaltimer (ns) timeline of the most recent ft_attn_decode launch ->
+ * HOST uint64 [n_ctas][4]: entry, first tile landed, last tile consumed, exit. */
+int ft_debug_attn_trace(unsigned long long* host_out, int n_ctas);
 /* persistent grid size the engine uses: SM count x resident CTAs of the decode kernel */
 int ft_attn_decode_default_ctas(int d);
 int ft_attn_decode(const void* q, const void* kv_layer, const int* page_table, int max_pages,
