@@ -265,3 +265,32 @@ def test_llama1b_batched_decode_matches_oracle_logits(llama1b):
         worst = max(worst, per_pos_rel(got, ref[:got.shape[0]]))
     print(f"\n[1B batched] worst decode logit rel err {worst:.2e}")
     assert worst < LOGIT_TOL
+
+
+# ------------------------------------------------------------------ the other named architectures
+@pytest.mark.parametrize("name,n_prompt,n_new", [("llama-3.2-3b", 96, 16), ("llama-3.1-8b", 70, 12)])
+def test_larger_configs_logits_and_greedy(name, n_prompt, n_new):
+    """BASELINE configs 3-5 name Llama-3.2-3B (GQA group 3, head_dim 128) and Llama-3.1-8B (untied
+    LM head, rope factor 8): same parity bar on random-init weights of those shapes."""
+    from fasttalk_llm_microservice_b200.model_spec import SPECS
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    spec = SPECS[name]
+    w = init_weights(spec, seed=3, device="cuda")
+    eng = make_engine(spec, w, max_batch=8, max_batched_tokens=256, max_context=1024, debug_logit_rows=128)
+    try:
+        gen = torch.Generator().manual_seed(7)
+        prompt = torch.randint(0, 128000, (n_prompt,), generator=gen)
+        w32 = {k: v.float() for k, v in w.items() if k != "lm_head"}
+        w32["lm_head"] = w32["embed"] if spec.tied_embeddings else w["lm_head"].float()
+        with torch.no_grad():
+            ref_full = O.forward(w32, spec, prompt).cpu()
+            ref_tokens, ref_logits = O.greedy_generate(w32, spec, prompt, n_new, return_logits=True)
+        got = eng.debug_prefill_logits(prompt.tolist(), chunk=64)
+        describe_err(f"{name} prefill", got, ref_full)
+        assert per_pos_rel(got, ref_full) < LOGIT_TOL
+        out = eng.generate([prompt.tolist()], max_new_tokens=n_new, ignore_eos=True)[0]
+        assert_greedy_parity(name, out, ref_tokens, ref_logits)
+    finally:
+        eng.close()
+        del w32, w
+        torch.cuda.empty_cache()
