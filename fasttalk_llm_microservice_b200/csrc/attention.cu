@@ -1,6 +1,8 @@
 // K5 / K6 — attention over the paged KV cache.
 //
-// KV cache layer layout: [page][kv_head][K|V][64 tokens][D] bf16, one page = 64 tokens.  The
+// KV cache layer layout: [page][kv_head][K|V][64 tokens][D] fp16, one page = 64 tokens (q, K, V
+// and the softmax probabilities are fp16 with fp32 accumulation: same bytes as bf16, three more
+// mantissa bits, and the dtype the reference runs its engine with, docker-compose.vllm.yml:45).  The
 // K and V slabs of a (page, head) are adjacent, so one attention tile is ONE contiguous
 // 2*64*D*2-byte block that a single bulk-TMA copy (cp.async.bulk, SASS UBLKCP) drops into a
 // shared-memory stage.  The 16-byte chunks of every token row are XOR-swizzled already in HBM
@@ -106,7 +108,7 @@ __device__ __forceinline__ void attn_trace(int slot) {
 
 template <int D>
 __global__ void __launch_bounds__(ATTN_THREADS)
-attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restrict__ kv_layer,
+attn_decode_kernel(const __half* __restrict__ q, const uint8_t* __restrict__ kv_layer,
                    const int* __restrict__ page_table, int max_pages, const int* __restrict__ ctx_lens,
                    const int* __restrict__ tile_prefix, __nv_bfloat16* __restrict__ out,
                    __nv_bfloat16* __restrict__ out_lo, int* __restrict__ seg_counters,
@@ -213,7 +215,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
         // Q fragments (A operand, rows >= G are zero padding)
         uint32_t qa[D / 16][2];
         {
-            const __nv_bfloat16* qrow = q + ((size_t)seg.b * nq + (size_t)seg.h * G + g) * D;
+            const __half* qrow = q + ((size_t)seg.b * nq + (size_t)seg.h * G + g) * D;
 #pragma unroll
             for (int ks = 0; ks < D / 16; ++ks) {
                 qa[ks][0] = g < G ? *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 2 * tq) : 0u;
@@ -241,8 +243,8 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                 for (int kp = 0; kp < D / 32; ++kp) {
                     uint32_t b0, b1, b2, b3;
                     ldmatrix_x4(kbase + kv_swizzled_chunk<D>(row, kp * 4 + (lane >> 3)), b0, b1, b2, b3);
-                    mma_bf16_16816(s[j], qa[2 * kp][0], 0u, qa[2 * kp][1], 0u, b0, b1);
-                    mma_bf16_16816(s[j], qa[2 * kp + 1][0], 0u, qa[2 * kp + 1][1], 0u, b2, b3);
+                    mma_f16_16816(s[j], qa[2 * kp][0], 0u, qa[2 * kp][1], 0u, b0, b1);
+                    mma_f16_16816(s[j], qa[2 * kp + 1][0], 0u, qa[2 * kp + 1][1], 0u, b2, b3);
                 }
             }
             // mask + online softmax for row g (this lane: tokens 2tq, 2tq+1 of each 8-token group)
@@ -272,8 +274,8 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                 }
             l_run = l_run * alpha + psum;
             m_run = m_new;
-            const uint32_t pa0 = pack_bf16(p[0][0], p[0][1]);
-            const uint32_t pa2 = pack_bf16(p[1][0], p[1][1]);
+            const uint32_t pa0 = pack_f16_sat(p[0][0], p[0][1]);
+            const uint32_t pa2 = pack_f16_sat(p[1][0], p[1][1]);
 
             // O[16 x D] = alpha * O + P V
 #pragma unroll
@@ -283,8 +285,8 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
                 ldmatrix_x4_trans(vbase + kv_swizzled_chunk<D>(row, 2 * np + (lane >> 4)), b0, b1, b2, b3);
                 o[2 * np][0] *= alpha; o[2 * np][1] *= alpha;
                 o[2 * np + 1][0] *= alpha; o[2 * np + 1][1] *= alpha;
-                mma_bf16_16816(o[2 * np], pa0, 0u, pa2, 0u, b0, b1);
-                mma_bf16_16816(o[2 * np + 1], pa0, 0u, pa2, 0u, b2, b3);
+                mma_f16_16816(o[2 * np], pa0, 0u, pa2, 0u, b0, b1);
+                mma_f16_16816(o[2 * np + 1], pa0, 0u, pa2, 0u, b2, b3);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty_bar[stage]);
@@ -383,7 +385,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restric
 // cached prefix and the new tokens take the same path.
 template <int D>
 __global__ void __launch_bounds__(ATTN_THREADS)
-attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restrict__ kv_layer,
+attn_prefill_kernel(const __half* __restrict__ q, const uint8_t* __restrict__ kv_layer,
                     const int* __restrict__ page_table, int max_pages,
                     const int* __restrict__ req_q_start, const int* __restrict__ req_slot,
                     const int* __restrict__ req_pos0, const int* __restrict__ tile_req,
@@ -448,8 +450,8 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restri
     const bool va = row_a < q_len, vb = row_b < q_len;
     uint32_t qa[D / 16][4];
     {
-        const __nv_bfloat16* qa_ptr = q + ((size_t)(req_q_start[req] + row_a) * nq + head) * D;
-        const __nv_bfloat16* qb_ptr = q + ((size_t)(req_q_start[req] + row_b) * nq + head) * D;
+        const __half* qa_ptr = q + ((size_t)(req_q_start[req] + row_a) * nq + head) * D;
+        const __half* qb_ptr = q + ((size_t)(req_q_start[req] + row_b) * nq + head) * D;
 #pragma unroll
         for (int ks = 0; ks < D / 16; ++ks) {
             qa[ks][0] = va ? *reinterpret_cast<const uint32_t*>(qa_ptr + ks * 16 + 2 * tq) : 0u;
@@ -478,8 +480,8 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restri
             for (int kp = 0; kp < D / 32; ++kp) {
                 uint32_t b0, b1, b2, b3;
                 ldmatrix_x4(kbase + kv_swizzled_chunk<D>(row, kp * 4 + (lane >> 3)), b0, b1, b2, b3);
-                mma_bf16_16816(s[j], qa[2 * kp][0], qa[2 * kp][1], qa[2 * kp][2], qa[2 * kp][3], b0, b1);
-                mma_bf16_16816(s[j], qa[2 * kp + 1][0], qa[2 * kp + 1][1], qa[2 * kp + 1][2],
+                mma_f16_16816(s[j], qa[2 * kp][0], qa[2 * kp][1], qa[2 * kp][2], qa[2 * kp][3], b0, b1);
+                mma_f16_16816(s[j], qa[2 * kp + 1][0], qa[2 * kp + 1][1], qa[2 * kp + 1][2],
                                qa[2 * kp + 1][3], b2, b3);
             }
         }
@@ -523,17 +525,17 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, const uint8_t* __restri
         }
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) {               // 16 keys per k-step
-            const uint32_t pa0 = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
-            const uint32_t pa1 = pack_bf16(s[2 * kk][2], s[2 * kk][3]);
-            const uint32_t pa2 = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
-            const uint32_t pa3 = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+            const uint32_t pa0 = pack_f16_sat(s[2 * kk][0], s[2 * kk][1]);
+            const uint32_t pa1 = pack_f16_sat(s[2 * kk][2], s[2 * kk][3]);
+            const uint32_t pa2 = pack_f16_sat(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+            const uint32_t pa3 = pack_f16_sat(s[2 * kk + 1][2], s[2 * kk + 1][3]);
             const int row = kk * 16 + ((lane >> 3) & 1) * 8 + (lane & 7);
 #pragma unroll
             for (int np = 0; np < D / 16; ++np) {
                 uint32_t b0, b1, b2, b3;
                 ldmatrix_x4_trans(vbase + kv_swizzled_chunk<D>(row, 2 * np + (lane >> 4)), b0, b1, b2, b3);
-                mma_bf16_16816(o[2 * np], pa0, pa1, pa2, pa3, b0, b1);
-                mma_bf16_16816(o[2 * np + 1], pa0, pa1, pa2, pa3, b2, b3);
+                mma_f16_16816(o[2 * np], pa0, pa1, pa2, pa3, b0, b1);
+                mma_f16_16816(o[2 * np + 1], pa0, pa1, pa2, pa3, b2, b3);
             }
         }
         __syncwarp();
@@ -624,7 +626,7 @@ static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* 
     cudaLaunchAttribute attr[1];
     fill_cfg(cfg, attr, dim3(n_ctas), dim3(ATTN_THREADS), C::SMEM, pdl && !ev0, stream);
     if (ev0) FT_CHECK_CUDA(cudaEventRecord(ev0, stream));
-    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_kernel<D>, (const __nv_bfloat16*)q,
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_kernel<D>, (const __half*)q,
                                      (const uint8_t*)kv_layer, page_table, max_pages, ctx_lens, tile_prefix,
                                      (__nv_bfloat16*)out, (__nv_bfloat16*)out_lo, reinterpret_cast<int*>(scratch),
                                      scratch + counter_floats(B, nkv), B, nq, nkv, scale_log2,
@@ -663,7 +665,7 @@ static int launch_attn_prefill_d(const void* q, const void* kv_layer, const int*
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
     fill_cfg(cfg, attr, dim3(n_tiles, nq), dim3(ATTN_THREADS), C::SMEM, pdl, stream);
-    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_kernel<D>, (const __nv_bfloat16*)q,
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_kernel<D>, (const __half*)q,
                                      (const uint8_t*)kv_layer, page_table, max_pages, req_q_start, req_slot,
                                      req_pos0, tile_req, tile_q0, (__nv_bfloat16*)out, (__nv_bfloat16*)out_lo, nq,
                                      nkv, scale_log2));

@@ -4,6 +4,7 @@
 
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda.h>
 #include <stdint.h>
 
@@ -227,6 +228,25 @@ __device__ __forceinline__ void mma_bf16_16816(float* d, uint32_t a0, uint32_t a
         "{%8,%9}, {%0,%1,%2,%3};"
         : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// D(16x8, f32) += A(16x16, f16 row) * B(16x8, f16 col) — attention runs in fp16 (q, K, V and the
+// softmax probabilities), fp32 accumulate: three more mantissa bits than bf16 at the same bytes,
+// and the dtype the reference deploys its engine with (docker-compose.vllm.yml:45 --dtype float16)
+__device__ __forceinline__ void mma_f16_16816(float* d, uint32_t a0, uint32_t a1, uint32_t a2,
+                                              uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, "
+        "{%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// two fp32 -> packed fp16 pair, saturating at the fp16 range instead of producing inf
+__device__ __forceinline__ uint32_t pack_f16_sat(float lo, float hi) {
+    lo = fminf(fmaxf(lo, -65504.f), 65504.f);
+    hi = fminf(fmaxf(hi, -65504.f), 65504.f);
+    __half2 t = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&t);
 }
 
 // Byte offset of 16-byte chunk `c` of row `r` inside a [rows][D] bf16 KV slab whose chunks

@@ -160,17 +160,17 @@ gather_planes_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
 
 // ------------------------------------------------------------------ K4
 // One warp per (token, head) of the fused QKV projection output:
-//   q heads : reduce partials, RoPE (rotate_half pairs i, i+d/2), write bf16 q[t][head][d]
+//   q heads : reduce partials, RoPE (rotate_half pairs i, i+d/2), write fp16 q[t][head][d]
 //   k heads : reduce, RoPE, write into the paged cache (swizzled 16-byte chunks)
 //   v heads : reduce, write into the paged cache
-// KV cache layer layout: [page][kv_head][K|V][64 tokens][d] bf16.
+// KV cache layer layout: [page][kv_head][K|V][64 tokens][d] fp16.
 template <int D>
 __global__ void __launch_bounds__(128)
 rope_kv_append_kernel(const float* __restrict__ qkv, int n_splits, size_t split_stride,
                       const float* __restrict__ cos_t, const float* __restrict__ sin_t,
                       const int* __restrict__ positions, const int* __restrict__ seq_slots,
                       const int* __restrict__ page_table, int max_pages,
-                      __nv_bfloat16* __restrict__ q_out, __nv_bfloat16* __restrict__ kv_layer, int T,
+                      __half* __restrict__ q_out, __half* __restrict__ kv_layer, int T,
                       int nq, int nkv) {
     pdl_wait();
     pdl_launch_dependents();
@@ -211,11 +211,12 @@ rope_kv_append_kernel(const float* __restrict__ qkv, int n_splits, size_t split_
         }
     }
     if (hd < nq) {
-        __nv_bfloat16* o = q_out + (size_t)t * nq * D + (size_t)hd * D;
+        __half* o = q_out + (size_t)t * nq * D + (size_t)hd * D;
+        auto sat = [](float x) { return __float2half_rn(fminf(fmaxf(x, -65504.f), 65504.f)); };
 #pragma unroll
         for (int p = 0; p < PAIRS; ++p) {
-            o[lane + p * 32] = __float2bfloat16(lo[p]);
-            o[lane + p * 32 + HALF] = __float2bfloat16(hi[p]);
+            o[lane + p * 32] = sat(lo[p]);
+            o[lane + p * 32 + HALF] = sat(hi[p]);
         }
     } else {
         const int kvh = is_v ? hd - nq - nkv : hd - nq;
@@ -226,10 +227,9 @@ rope_kv_append_kernel(const float* __restrict__ qkv, int n_splits, size_t split_
 #pragma unroll
         for (int p = 0; p < PAIRS; ++p) {
             const int e0 = lane + p * 32, e1 = e0 + HALF;
-            *reinterpret_cast<__nv_bfloat16*>(slab + kv_swizzled_chunk<D>(r, e0 >> 3) + (e0 & 7) * 2) =
-                __float2bfloat16(lo[p]);
-            *reinterpret_cast<__nv_bfloat16*>(slab + kv_swizzled_chunk<D>(r, e1 >> 3) + (e1 & 7) * 2) =
-                __float2bfloat16(hi[p]);
+            auto sat = [](float x) { return __float2half_rn(fminf(fmaxf(x, -65504.f), 65504.f)); };
+            *reinterpret_cast<__half*>(slab + kv_swizzled_chunk<D>(r, e0 >> 3) + (e0 & 7) * 2) = sat(lo[p]);
+            *reinterpret_cast<__half*>(slab + kv_swizzled_chunk<D>(r, e1 >> 3) + (e1 & 7) * 2) = sat(hi[p]);
         }
     }
 }
@@ -309,11 +309,11 @@ int launch_rope_kv_append(const float* qkv, int n_splits, size_t split_stride, c
     if (d == 64) {
         FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, rope_kv_append_kernel<64>, qkv, n_splits, split_stride,
                                          cos_t, sin_t, positions, seq_slots, page_table, max_pages,
-                                         (__nv_bfloat16*)q_out, (__nv_bfloat16*)kv_layer, T, nq, nkv));
+                                         (__half*)q_out, (__half*)kv_layer, T, nq, nkv));
     } else {
         FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, rope_kv_append_kernel<128>, qkv, n_splits, split_stride,
                                          cos_t, sin_t, positions, seq_slots, page_table, max_pages,
-                                         (__nv_bfloat16*)q_out, (__nv_bfloat16*)kv_layer, T, nq, nkv));
+                                         (__half*)q_out, (__half*)kv_layer, T, nq, nkv));
     }
     return 0;
 }

@@ -345,8 +345,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                         val = make_float4(val.x * c.x + sg * b.x * s.x, val.y * c.y + sg * b.y * s.y,
                                           val.z * c.z + sg * b.z * s.z, val.w * c.w + sg * b.w * s.w);
                     }
+                    uint2 h4;                       // q, K and V leave as saturating fp16 (attention dtype)
+                    h4.x = pack_f16_sat(val.x, val.y);
+                    h4.y = pack_f16_sat(val.z, val.w);
                     if (region == 0) {
-                        store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.q_out), nullptr, (size_t)t * q_dim + row, val);
+                        *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ep.q_out) + (size_t)t * q_dim + row) = h4;
                     } else {
                         const int kvh = (row - q_dim - (region == 2 ? kv_dim : 0)) / d;
                         const int page = ep.page_table[(size_t)ep.seq_rows[t] * ep.max_pages + pos / kKvTile];
@@ -355,7 +358,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                                         (((size_t)page * ep.nkv + kvh) * 2 + (region == 2 ? 1 : 0)) *
                                             (size_t)(kKvTile * d * 2);
                         const int off = r * (d * 2) + ((((i >> 3) ^ (r & 7))) << 4) + (i & 7) * 2;
-                        store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(slab + off), nullptr, 0, val);
+                        *reinterpret_cast<uint2*>(slab + off) = h4;
                     }
                 } else if (mode == FT_EPI_SWIGLU) {
                     // rows 0..63 of the tile are gate features, rows 64..127 the matching up features:

@@ -117,15 +117,15 @@ def add_rmsnorm(resid: torch.Tensor, norm_w: torch.Tensor, eps: float, partials:
 
 
 def kv_cache_alloc(num_pages: int, nkv: int, d: int, device) -> torch.Tensor:
-    """One layer of paged KV cache: [page][kv_head][K|V][64][d] bf16 (swizzled rows)."""
-    return torch.zeros(num_pages, nkv, 2, KV_TILE, d, device=device, dtype=torch.bfloat16)
+    """One layer of paged KV cache: [page][kv_head][K|V][64][d] fp16 (swizzled rows)."""
+    return torch.zeros(num_pages, nkv, 2, KV_TILE, d, device=device, dtype=torch.float16)
 
 
 def rope_kv_append(qkv_partials: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, positions: torch.Tensor,
                    seq_rows: torch.Tensor, page_table: torch.Tensor, kv_layer: torch.Tensor,
                    nq: int, nkv: int, d: int) -> torch.Tensor:
     S, T, _ = qkv_partials.shape
-    q = torch.empty(T, nq, d, device=qkv_partials.device, dtype=torch.bfloat16)
+    q = torch.empty(T, nq, d, device=qkv_partials.device, dtype=torch.float16)
     N.check(N.load().ft_rope_kv_append(N.ptr(qkv_partials), S, qkv_partials.stride(0), N.ptr(cos), N.ptr(sin),
                                        N.ptr(positions), N.ptr(seq_rows), N.ptr(page_table),
                                        page_table.shape[1], N.ptr(q), N.ptr(kv_layer), T, nq, nkv, d,
@@ -144,7 +144,8 @@ def silu_mul(gu_partials: torch.Tensor):
 
 def attn_decode(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tensor, ctx_lens: torch.Tensor,
                 n_ctas: int = 0):
-    """q bf16 [B, nq, d] -> bf16 (hi, lo) planes [B, nq*d]."""
+    """q fp16 [B, nq, d], fp16 KV cache -> bf16 (hi, lo) planes [B, nq*d]."""
+    assert q.dtype == torch.float16 and kv_layer.dtype == torch.float16
     B, nq, d = q.shape
     nkv = kv_layer.shape[1]
     lib = N.load()
@@ -177,7 +178,8 @@ def attn_decode_noalloc(q: torch.Tensor, kv_layer: torch.Tensor, page_table: tor
 
 def attn_prefill(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tensor, req_q_start, req_slot,
                  req_pos0):
-    """q bf16 [T, nq, d]; request r owns rows req_q_start[r]:req_q_start[r+1].  Returns (hi, lo)."""
+    """q fp16 [T, nq, d]; request r owns rows req_q_start[r]:req_q_start[r+1].  Returns (hi, lo)."""
+    assert q.dtype == torch.float16 and kv_layer.dtype == torch.float16
     T, nq, d = q.shape
     nkv = kv_layer.shape[1]
     dev = q.device

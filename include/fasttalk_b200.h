@@ -148,7 +148,7 @@ int ft_debug_gemm_trace(unsigned long long* host_out16);
  *                       resid[t][n] += y;  out/out_lo[t][n] = hi/lo(resid * gamma[n]);
  *                       ssq_out[row_tile][t] = sum over the tile's 128 rows of resid^2
  *   FT_EPI_QKV_ROPE(4): same reduction, y *= rstd[t], RoPE on q and k rows, q -> q_out bf16
- *                       [T][nq*d], k/v -> paged KV cache layer (layout of ft_rope_kv_append)
+ *                       [T][nq*d] (fp16), k/v -> paged fp16 KV cache layer (layout of ft_rope_kv_append)
  *   FT_EPI_LOGITS  (5): out fp32 [T][n_out] = y * rstd[t]
  * rstd[t] = rsqrt(sum_p ssq_in[p * ssq_stride + t] * inv_h + eps).  x_lo is required. */
 enum { FT_EPI_PARTIAL = 0, FT_EPI_BF16 = 1, FT_EPI_SWIGLU = 2, FT_EPI_RESID = 3, FT_EPI_QKV_ROPE = 4,
@@ -169,7 +169,7 @@ typedef struct {
     const int* seq_rows;       /* QKV_ROPE: int32 [T], page-table row of each token */
     const int* page_table;     /* QKV_ROPE: int32 [rows][max_pages] */
     int max_pages;
-    void* q_out;               /* QKV_ROPE: bf16 [T][nq*d] */
+    void* q_out;               /* QKV_ROPE: fp16 [T][nq*d] */
     void* kv_layer;            /* QKV_ROPE: paged KV cache layer */
     int nq, nkv, head_dim;
     float* scratch;            /* RESID / QKV_ROPE with n_splits > 1: ft_gemm_scratch_bytes() of device memory */
@@ -198,8 +198,10 @@ int ft_add_rmsnorm(float* resid, const float* partials, int n_splits, long long 
                    void* xn_lo, const int* row_idx, int T, int h, float eps, void* stream);
 
 /* K4: split-K reduce of the fused QKV projection, RoPE on q and k (cos/sin tables fp32
- * [pos][d/2]), q -> bf16 [T][nq][d], k/v -> paged cache layer
- * [page][kv_head][K|V][64][d] bf16 with XOR-swizzled 16-byte chunks. */
+ * [pos][d/2]), q -> FP16 [T][nq][d], k/v -> paged cache layer
+ * [page][kv_head][K|V][64][d] FP16 (saturating) with XOR-swizzled 16-byte chunks.  Attention
+ * runs in fp16 with fp32 accumulation: same bytes as bf16, three more mantissa bits, and the
+ * dtype the reference deploys its engine with (docker-compose.vllm.yml:45 --dtype float16). */
 int ft_rope_kv_append(const float* qkv, int n_splits, long long split_stride, const float* cos_t,
                       const float* sin_t, const int* positions, const int* seq_rows,
                       const int* page_table, int max_pages, void* q_out, void* kv_layer, int T, int nq,
@@ -210,7 +212,7 @@ int ft_rope_kv_append(const float* qkv, int n_splits, long long split_stride, co
 int ft_silu_mul(const float* gu, int n_splits, long long split_stride, void* act, void* act_lo, int T, int f,
                 void* stream);
 
-/* K5: paged GQA decode attention, one query token per sequence.  q bf16 [B][nq][d],
+/* K5: paged GQA decode attention, one query token per sequence.  q FP16 [B][nq][d], KV cache FP16,
  * out bf16 [B][nq*d] (+ residual plane out_lo, may be NULL).  `tile_prefix` (int32 [B+1]) and
  * `scratch` (ft_attn_decode_scratch_bytes) are device work buffers the call fills. */
 long long ft_attn_decode_scratch_bytes(int B, int nkv, int group, int d, int n_ctas);

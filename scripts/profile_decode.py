@@ -30,7 +30,7 @@ eng = Engine(spec, w, EngineLimits(max_batch=a.sessions, max_batched_tokens=8192
                                    use_pdl=not a.no_pdl), eos_ids=())
 g = torch.Generator().manual_seed(1)
 for i in range(a.sessions):
-    eng.submit(f"s{i}", torch.randint(0, 128000, (a.ctx,), generator=g).tolist(), max_new_tokens=100, ignore_eos=True)
+    eng.submit(f"s{i}", torch.randint(0, 128000, (a.ctx,), generator=g).tolist(), max_new_tokens=a.steps + 64, ignore_eos=True)
 while eng.stats()["last_prefill_tokens"] > 0 or eng.stats()["steps"] == 0:
     eng.step()
 for _ in range(3):

@@ -4,7 +4,7 @@
 Tolerances: the kernels take bf16 inputs and accumulate in fp32, so where the reference is
 fed the same bf16-rounded inputs the only differences are summation order (GEMM, norms:
 1e-3 relative to the tensor's max) and bf16 rounding of outputs / of the softmax
-probabilities fed to the PV product (attention: 1e-2 relative to max |out|).  Activations
+probabilities fed to the PV product (attention runs in fp16: 2e-3 relative to max |out|).  Activations
 leave every kernel as bf16 hi + lo planes; hi + lo must match the fp32 reference to ~5e-5.
 """
 import math
@@ -149,7 +149,7 @@ def test_gemm_qkv_rope_epilogue(K, nq, nkv, d, T, Kd, splits):
     pt = torch.randperm(num_pages, device=DEV, generator=g)[:n_seq * max_pages].reshape(n_seq, max_pages).int().contiguous()
     cos, sin = rope_tables(spec, 512, device=DEV)
     kv = K.kv_cache_alloc(num_pages, nkv, d, DEV)
-    q = torch.zeros(T, nq, d, device=DEV, dtype=torch.bfloat16)
+    q = torch.zeros(T, nq, d, device=DEV, dtype=torch.float16)
     K.gemm_fused(w, x, x_lo, N.EPI_QKV_ROPE, n_splits=splits, ssq_in=ssq, ssq_parts=parts, ssq_stride=T,
                  inv_h=1.0 / Kd, eps=1e-5, rope_cos=cos, rope_sin=sin, positions=pos, seq_rows=rows, page_table=pt,
                  max_pages=max_pages, q_out=q, kv_layer=kv, nq=nq, nkv=nkv, head_dim=d)
@@ -160,14 +160,14 @@ def test_gemm_qkv_rope_epilogue(K, nq, nkv, d, T, Kd, splits):
     vr = full[:, (nq + nkv) * d:].reshape(T, nkv, d)
     c, s = O.rope_cos_sin(spec, pos.cpu().long())
     c, s = c.to(DEV), s.to(DEV)
-    assert rel_err(q, O.apply_rope(qr, c, s)) < 6e-3
+    assert rel_err(q, O.apply_rope(qr, c, s)) < 1e-3
     kref = O.apply_rope(kr, c, s)
     for t in range(T):
         page = pt[rows[t], pos[t] // 64].item()
         r = pos[t].item() % 64
         for hk in range(nkv):
-            assert rel_err(K.kv_slab_logical(kv[page, hk, 0])[r], kref[t, hk]) < 6e-3
-            assert rel_err(K.kv_slab_logical(kv[page, hk, 1])[r], vr[t, hk]) < 6e-3
+            assert rel_err(K.kv_slab_logical(kv[page, hk, 0])[r], kref[t, hk]) < 1e-3
+            assert rel_err(K.kv_slab_logical(kv[page, hk, 1])[r], vr[t, hk]) < 1e-3
 
 
 def test_gemm_logits_and_swiglu_with_rstd(K):
@@ -300,11 +300,11 @@ def build_paged_kv(K, ctx_lens, nkv, d, g, extra_pages=5):
     pt = torch.zeros(B, max_pages, dtype=torch.int32, device=DEV)
     kv = K.kv_cache_alloc(total, nkv, d, DEV)
     # poison: garbage beyond ctx must be ignored (finite, as in a recycled page)
-    kv.copy_(torch.randn(kv.shape, device=DEV, generator=g).bfloat16() * 50)
+    kv.copy_(torch.randn(kv.shape, device=DEV, generator=g).half() * 50)
     ks, vs, off = [], [], 0
     for b, c in enumerate(ctx_lens):
-        k = torch.randn(c, nkv, d, device=DEV, generator=g).bfloat16()
-        v = torch.randn(c, nkv, d, device=DEV, generator=g).bfloat16()
+        k = torch.randn(c, nkv, d, device=DEV, generator=g).half()
+        v = torch.randn(c, nkv, d, device=DEV, generator=g).half()
         ks.append(k); vs.append(v)
         for p in range(n_pages[b]):
             page = perm[off + p].item()
@@ -336,7 +336,7 @@ def test_attn_decode(K, nq, nkv, d, ctx_lens, n_ctas):
     g = torch.Generator(device=DEV).manual_seed(sum(ctx_lens) + nq + d)
     kv, pt, ks, vs = build_paged_kv(K, ctx_lens, nkv, d, g)
     B = len(ctx_lens)
-    q = torch.randn(B, nq, d, device=DEV, generator=g).bfloat16()
+    q = torch.randn(B, nq, d, device=DEV, generator=g).half()
     ctx = torch.tensor(ctx_lens, device=DEV, dtype=torch.int32)
     out, out_lo = K.attn_decode(q, kv, pt, ctx, n_ctas=n_ctas)
     torch.cuda.synchronize()
@@ -344,7 +344,7 @@ def test_attn_decode(K, nq, nkv, d, ctx_lens, n_ctas):
     out = hilo(out, out_lo)
     for b in range(B):
         ref = O.attention(q[b:b + 1].float(), ks[b].float(), vs[b].float(), ctx_lens[b] - 1)
-        assert rel_err(out[b:b + 1], ref) < 1e-2, (b, rel_err(out[b:b + 1], ref))
+        assert rel_err(out[b:b + 1], ref) < 2e-3, (b, rel_err(out[b:b + 1], ref))
     # repeat on the same scratch: the per-segment arrival counters must have re-armed themselves
     again = hilo(*K.attn_decode(q, kv, pt, ctx, n_ctas=n_ctas))
     assert torch.equal(again, out)
@@ -357,16 +357,16 @@ def test_attn_decode_cfg2_shape(K):
     g = torch.Generator(device=DEV).manual_seed(77)
     nq, nkv, d, B, ctxl = 32, 8, 64, 64, 2048
     pages = B * 32
-    kv = (torch.randn(pages, nkv, 2, 64, d, device=DEV, generator=g)).bfloat16()
+    kv = (torch.randn(pages, nkv, 2, 64, d, device=DEV, generator=g)).half()
     kv[:, :, 1] = 0.5
     pt = torch.randperm(pages, device=DEV, generator=g).int().reshape(B, 32).contiguous()
-    q = torch.randn(B, nq, d, device=DEV, generator=g).bfloat16()
+    q = torch.randn(B, nq, d, device=DEV, generator=g).half()
     ctx = torch.full((B,), ctxl, device=DEV, dtype=torch.int32)
     ctx[3] = 1999
     out = hilo(*K.attn_decode(q, kv, pt, ctx))
     assert (out - 0.5).abs().max().item() < 4e-3
     # and against the oracle on two of the sequences
-    kv2 = (torch.randn(pages, nkv, 2, 64, d, device=DEV, generator=g)).bfloat16()
+    kv2 = (torch.randn(pages, nkv, 2, 64, d, device=DEV, generator=g)).half()
     out2 = hilo(*K.attn_decode(q, kv2, pt, ctx))
     for b in (3, 40):
         n = int(ctx[b])
@@ -374,7 +374,7 @@ def test_attn_decode_cfg2_shape(K):
         kl = torch.stack([torch.stack([K.kv_slab_logical(kv2[p, h, 0]) for h in range(nkv)], 1) for p in pg]).reshape(-1, nkv, d)[:n]
         vl = torch.stack([torch.stack([K.kv_slab_logical(kv2[p, h, 1]) for h in range(nkv)], 1) for p in pg]).reshape(-1, nkv, d)[:n]
         ref = O.attention(q[b:b + 1].float(), kl.float(), vl.float(), n - 1)
-        assert rel_err(out2[b:b + 1], ref) < 1e-2
+        assert rel_err(out2[b:b + 1], ref) < 2e-3
 
 
 # ------------------------------------------------------------------ K6 prefill attention
@@ -393,13 +393,13 @@ def test_attn_prefill(K, nq, nkv, d, reqs):
     for _, n in reqs:
         q_start.append(q_start[-1] + n)
     T = q_start[-1]
-    q = torch.randn(T, nq, d, device=DEV, generator=g).bfloat16()
+    q = torch.randn(T, nq, d, device=DEV, generator=g).half()
     out = hilo(*K.attn_prefill(q, kv, pt, q_start, list(range(len(reqs))), [p for p, _ in reqs]))
     torch.cuda.synchronize()
     for r, (p0, n) in enumerate(reqs):
         ref = O.attention(q[q_start[r]:q_start[r + 1]].float(), ks[r].float(), vs[r].float(), p0)
         got = out[q_start[r]:q_start[r + 1]]
-        assert rel_err(got, ref) < 1e-2, (r, rel_err(got, ref))
+        assert rel_err(got, ref) < 2e-3, (r, rel_err(got, ref))
 
 
 # ------------------------------------------------------------------ K7 sampling

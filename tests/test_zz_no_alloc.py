@@ -12,7 +12,7 @@ import torch
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
-TOL = 1e-2          # the decode-attention tolerance of tests/test_kernels_gpu.py
+TOL = 2e-3          # the decode-attention tolerance of tests/test_kernels_gpu.py
 
 
 @pytest.fixture(scope="module")
@@ -30,14 +30,14 @@ def make_case(K, B, nq, nkv, d, ctx_lens, seed):
     g = torch.Generator(device=DEV).manual_seed(seed)
     n_pages = [-(-c // 64) for c in ctx_lens]
     total = sum(n_pages) + 3
-    kv = (torch.randn(total, nkv, 2, 64, d, device=DEV, generator=g)).bfloat16()
+    kv = (torch.randn(total, nkv, 2, 64, d, device=DEV, generator=g)).half()
     perm = torch.randperm(total, device=DEV, generator=g).int()
     pt = torch.zeros(B, max(n_pages) + 1, dtype=torch.int32, device=DEV)
     off = 0
     for b, n in enumerate(n_pages):
         pt[b, :n] = perm[off:off + n]
         off += n
-    q = torch.randn(B, nq, d, device=DEV, generator=g).bfloat16()
+    q = torch.randn(B, nq, d, device=DEV, generator=g).half()
     ctx = torch.tensor(ctx_lens, device=DEV, dtype=torch.int32)
     return q, kv, pt, ctx
 
@@ -82,10 +82,10 @@ def test_noalloc_refuses_oversized_requests(K):
     with pytest.raises(NativeError, match="exceed the built-in work area"):
         K.attn_decode_noalloc(q, kv, pt, ctx, hi, lo, n_ctas=513)
     # B * nkv = 2048 > 1024 (shape check happens before anything is launched)
-    big_q = torch.empty(256, 32, 64, device=DEV, dtype=torch.bfloat16)
+    big_q = torch.empty(256, 32, 64, device=DEV, dtype=torch.float16)
     big_ctx = torch.ones(256, device=DEV, dtype=torch.int32)
     big_pt = torch.zeros(256, 1, device=DEV, dtype=torch.int32)
-    kv8 = torch.zeros(1, 8, 2, 64, 64, device=DEV, dtype=torch.bfloat16)
+    kv8 = torch.zeros(1, 8, 2, 64, 64, device=DEV, dtype=torch.float16)
     out = torch.empty(256, 32 * 64, device=DEV, dtype=torch.bfloat16)
     with pytest.raises(NativeError, match="exceed the built-in work area"):
         K.attn_decode_noalloc(big_q, kv8, big_pt, big_ctx, out, torch.empty_like(out))
