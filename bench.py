@@ -229,6 +229,14 @@ def run_native(args, rank, world, local_rank):
     layer_kv_bytes = spec.kv_bytes_per_token() // spec.layers
     attn_bytes_per_launch = kv_tok / max(n_l, 1) * layer_kv_bytes
     attn_achieved = attn_bytes_per_launch / (attn_ms / max(n_l, 1) * 1e-3) / 1e9 if attn_ms > 0 else 0.0
+    # DRAM traffic of that kernel from the committed `ncu --set full` capture of the same workload
+    # (profiles/r01_ncu_final.md); null when the capture is for another shape
+    traffic, traffic_src = None, None
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_attn_traffic.json")
+    if MODEL == "llama-3.2-1b" and SESSIONS == 64 and CTX == 2048 and os.path.exists(tpath):
+        with open(tpath) as f:
+            tj = json.load(f)
+        traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
 
     # ---- finish the long requests, then e2e: one whole turn per session through the public API
     for r in rids:
@@ -296,7 +304,8 @@ def run_native(args, rank, world, local_rank):
                        "l2": "no flush needed: each step streams 6.8 GB >> 126 MB L2",
                        "weights": "random-init (seed per rank, std 0.02)", "sampling": "greedy, EOS ignored"},
             "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel<64>", "achieved": attn_achieved, "peak": peak,
-                         "unit": "GB/s", "frac": attn_achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": attn_achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
                          "launches_timed": n_l, "bytes_per_launch": attn_bytes_per_launch,
                          "us_per_launch": 1e3 * attn_ms / max(n_l, 1),
                          "pass": "second pass of K steps with CUDA events around each launch",
