@@ -39,7 +39,7 @@ _DONE = object()
 class _Sink:
     """Where one request's text chunks go: an asyncio queue on its loop, or a thread queue."""
     __slots__ = ("loop", "aq", "tq", "decoder", "text", "stop", "finished", "error", "rid", "start_time",
-                 "cancelled", "n_tokens")
+                 "cancelled", "n_tokens", "finish", "n_prompt")
 
     def __init__(self, loop, decoder, stop):
         self.loop = loop
@@ -48,6 +48,7 @@ class _Sink:
         self.decoder, self.stop = decoder, stop or []
         self.text, self.finished, self.error, self.rid = "", False, None, -1
         self.start_time, self.cancelled, self.n_tokens = time.time(), False, 0
+        self.finish, self.n_prompt = None, 0      # engine finish reason ("stop" | "length" | ...), prompt tokens
 
 
 class EngineRunner:
@@ -135,6 +136,7 @@ class EngineRunner:
                 tail = sink.decoder.flush()
                 if tail:
                     items.append((sink, tail))
+                sink.finish = fin
                 if fin == "error":
                     sink.error = RuntimeError("engine could not serve the request (out of KV pages)")
                 sink.finished = True
@@ -174,27 +176,35 @@ def _env_int(name, default):
 
 
 def build_runner(model: str) -> EngineRunner:
-    """Create the engine for `model` on the current CUDA device (random-init weights unless
-    $FASTTALK_WEIGHTS points at a safetensors file laid out like weights.py)."""
+    """Create the engine for `model` on GPU $FASTTALK_GPU: weights from $FASTTALK_CHECKPOINT (a
+    Hugging Face Llama directory) or $FASTTALK_WEIGHTS (stacked layout), else random-init."""
     import torch
     from .engine import Engine, EngineLimits
     from .model_spec import get_spec
     from .weights import init_weights
-    spec = get_spec(os.environ.get("FASTTALK_MODEL", model))
     dev = _env_int("FASTTALK_GPU", 0)
     if not torch.cuda.is_available():
         raise LLMServiceError("fasttalk_b200: no CUDA device; the native backend has no CPU fallback",
                               category=ErrorCategory.GPU, severity=ErrorSeverity.CRITICAL, recoverable=False)
     torch.cuda.set_device(dev)
-    wpath = os.environ.get("FASTTALK_WEIGHTS")
-    if wpath:
-        from safetensors.torch import load_file
-        w = load_file(wpath, device=f"cuda:{dev}")
-        if "lm_head" not in w:
-            w["lm_head"] = w["embed"]
+    ckpt = os.environ.get("FASTTALK_CHECKPOINT")
+    tok_path = None
+    if ckpt:                            # a Hugging Face Llama directory: config.json + *.safetensors (+ tokenizer.json)
+        from .checkpoint import load_hf_checkpoint
+        spec, w = load_hf_checkpoint(ckpt, device=f"cuda:{dev}", name=model)
+        if os.path.exists(os.path.join(ckpt, "tokenizer.json")):
+            tok_path = os.path.join(ckpt, "tokenizer.json")
     else:
-        w = init_weights(spec, seed=_env_int("FASTTALK_SEED", 0), device=f"cuda:{dev}")
-    tok = load_tokenizer(spec.vocab)
+        spec = get_spec(os.environ.get("FASTTALK_MODEL", model))
+        wpath = os.environ.get("FASTTALK_WEIGHTS")
+        if wpath:                       # one safetensors file already in weights.py's stacked layout
+            from safetensors.torch import load_file
+            w = load_file(wpath, device=f"cuda:{dev}")
+            if "lm_head" not in w:
+                w["lm_head"] = w["embed"]
+        else:
+            w = init_weights(spec, seed=_env_int("FASTTALK_SEED", 0), device=f"cuda:{dev}")
+    tok = load_tokenizer(spec.vocab, tok_path)
     lim = EngineLimits(max_batch=_env_int("FASTTALK_MAX_SESSIONS", 64),
                        max_batched_tokens=_env_int("FASTTALK_MAX_BATCHED_TOKENS", 8192),
                        max_context=_env_int("FASTTALK_MAX_CONTEXT", _env_int("DEFAULT_CONTEXT_WINDOW", 8192)))
@@ -297,10 +307,17 @@ class NativeHandler:
             pass
 
     # ------------------------------------------------------------------ generation (a1 / a2 / a3)
-    def _start(self, loop, messages, temperature, max_tokens, top_p, top_k, stop, request_id, prefix):
+    def _start(self, loop, messages, temperature, max_tokens, top_p, top_k, stop, request_id, prefix,
+               tools=None, seed=None):
         req_id = request_id or f"{prefix}-{uuid.uuid4()}"
         runner = self.runner
         tok = runner.tokenizer
+        if tools or any(not isinstance(m.get("content"), str) or m.get("role") == "tool" for m in messages):
+            from .chat_format import ChatFormatError, normalise_messages
+            try:                # tool schemas / tool turns in the history (vllm_handler.py:245-260, :425-440)
+                messages = normalise_messages(messages, tools)
+            except ChatFormatError as e:
+                raise LLMServiceError(str(e), category=ErrorCategory.VALIDATION, severity=ErrorSeverity.MEDIUM)
         tokens = tok.apply_chat_template(messages)
         eng = runner.engine
         max_ctx = getattr(getattr(eng, "limits", None), "max_context", 1 << 30)
@@ -311,20 +328,25 @@ class NativeHandler:
                 category=ErrorCategory.VALIDATION, severity=ErrorSeverity.MEDIUM)
         max_new = min(int(max_tokens), room) if max_tokens else room
         sink = _Sink(loop, tok.stream_decoder(), stop)
+        sink.n_prompt = len(tokens)
         with self._requests_lock:
             self._active_requests[req_id] = {"start_time": time.time(), "cancelled": False, "sink": sink}
         try:
             runner.submit(sink, req_id, tokens,
                           temperature=1.0 if temperature is None else float(temperature),
                           top_k=int(top_k or 0), top_p=1.0 if top_p is None else float(top_p),
-                          max_new_tokens=max_new, seed=uuid.uuid4().int & 0xFFFFFFFF)
+                          max_new_tokens=max_new,
+                          seed=(uuid.uuid4().int if seed is None else int(seed)) & 0xFFFFFFFF)
         except Exception:
             with self._requests_lock:
                 self._active_requests.pop(req_id, None)
             raise
         return req_id, sink
 
-    def _finish(self, req_id, sink):
+    def _finish(self, req_id, sink, meta=None, hit_stop=False):
+        if meta is not None:                    # what the OpenAI front reports (openai_server.py)
+            meta["finish_reason"] = "stop" if hit_stop or sink.finish != "length" else "length"
+            meta["prompt_tokens"], meta["completion_tokens"] = sink.n_prompt, sink.n_tokens
         if not sink.finished:
             self.runner.cancel(sink)
         with self._requests_lock:
@@ -354,13 +376,15 @@ class NativeHandler:
                         max_tokens: Optional[int] = None, top_p: Optional[float] = None,
                         top_k: Optional[int] = None, stop: Optional[List[str]] = None,
                         tools: Optional[List[Dict]] = None, request_id: Optional[str] = None,
+                        seed: Optional[int] = None, _meta: Optional[Dict[str, Any]] = None,
                         ) -> Generator[str, None, None]:
         """Synchronous streaming generation: vllm_handler.py:117-214 (has `tools`) and
         ollama_handler.py:110-231 (has `top_k`) in one signature."""
         req_id = sink = None
+        hit = False
         try:
             req_id, sink = self._start(None, messages, temperature, max_tokens, top_p, top_k, stop, request_id,
-                                       "native")
+                                       "native", tools, seed)
             deadline = time.time() + self.timeout
             while True:
                 try:
@@ -392,18 +416,20 @@ class NativeHandler:
                                   severity=ErrorSeverity.HIGH)
         finally:
             if sink is not None:
-                self._finish(req_id, sink)
+                self._finish(req_id, sink, _meta, hit)
 
     async def generate_stream_async(self, messages: List[Dict[str, str]], temperature: Optional[float] = None,
                                     max_tokens: Optional[int] = None, top_p: Optional[float] = None,
                                     stop: Optional[List[str]] = None, tools: Optional[List[Dict]] = None,
                                     request_id: Optional[str] = None, top_k: Optional[int] = None,
+                                    seed: Optional[int] = None, _meta: Optional[Dict[str, Any]] = None,
                                     ) -> AsyncGenerator[str, None]:
         """Async streaming generation: vllm_handler.py:216-308."""
         req_id = sink = None
+        hit = False
         try:
             req_id, sink = self._start(asyncio.get_running_loop(), messages, temperature, max_tokens, top_p,
-                                       top_k, stop, request_id, "native-async")
+                                       top_k, stop, request_id, "native-async", tools, seed)
             while True:
                 item = await asyncio.wait_for(sink.aq.get(), timeout=self.timeout)
                 if item is _DONE:
@@ -430,7 +456,7 @@ class NativeHandler:
         finally:
             # disconnects finalise the generator here: the batch slot is freed
             if sink is not None:
-                self._finish(req_id, sink)
+                self._finish(req_id, sink, _meta, hit)
 
 
 def install(into_vllm: bool = True, into_ollama: bool = True) -> None:
