@@ -138,8 +138,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
 
     if (warp == 0) {
         if (elect_one()) {
-            const uint64_t pol_w = policy_evict_first();   // weights: streamed once per step
-            const uint64_t pol_x = policy_evict_last();    // activations: re-read by every row tile
+            // One token tile (decode): weights are streamed once per step, the activations are re-read
+            // by every row tile.  Several token tiles (prefill): row tiles vary fastest, so a wave of
+            // CTAs shares one or two activation tiles and sweeps ALL of W, which the next token tile
+            // sweeps again — W is the L2-resident set (67 MB at most for the 1B gate/up projection).
+            const bool multi = gridDim.y > 1;
+            const uint64_t pol_w = multi ? policy_evict_last() : policy_evict_first();
+            const uint64_t pol_x = multi ? policy_evict_first() : policy_evict_last();
             // Weights do not depend on the previous kernel: start streaming them before the
             // programmatic-dependency wait, then add the activation tiles.
             const int pre = n_iter < stages ? n_iter : stages;
@@ -308,9 +313,46 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                 const uint2 gv = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(ep.gamma) + row);
                 gam = make_float4(bf16_lo(gv.x), bf16_hi(gv.x), bf16_lo(gv.y), bf16_hi(gv.y));
             }
-            for (int j = jbeg + ew; j < jend; j += GEMM_EPI_WARPS) {
+            // Tokens are taken four at a time per warp: the global operands of the batch (residual rows,
+            // or position -> RoPE angles / KV page) are requested first, so a 128-token prefill tile pays
+            // their latency 4 times per warp instead of 16 (ncu: the O projection spent 20 of 35 us here).
+            constexpr int U = 4;
+            const bool is_resid = mode == FT_EPI_RESID, is_rope = mode == FT_EPI_QKV_ROPE;
+            const int d_ = ep.head_dim, half_ = d_ >> 1;
+            const int q_dim_ = ep.nq * d_, kv_dim_ = ep.nkv * d_;
+            const int region = row0 < q_dim_ ? 0 : row0 < q_dim_ + kv_dim_ ? 1 : 2;   // tile-uniform
+            const int i_ = is_rope ? row % d_ : 0;
+            for (int j0 = jbeg + ew; j0 < jend; j0 += GEMM_EPI_WARPS * U) {
+                float4 pre_r[U], pre_c[U], pre_s[U];
+                int pre_pos[U], pre_page[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
+                    pre_pos[u] = 0;
+                    if (j < jend && t < T) {
+                        if (is_resid) pre_r[u] = *reinterpret_cast<const float4*>(ep.resid + (size_t)t * n_out + row);
+                        if (is_rope) pre_pos[u] = ep.positions[t];
+                    }
+                }
+                if (is_rope) {
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
+                        if (j < jend && t < T) {
+                            if (region < 2) {
+                                pre_c[u] = *reinterpret_cast<const float4*>(ep.rope_cos + (size_t)pre_pos[u] * half_ + (i_ % half_));
+                                pre_s[u] = *reinterpret_cast<const float4*>(ep.rope_sin + (size_t)pre_pos[u] * half_ + (i_ % half_));
+                            }
+                            if (region > 0)
+                                pre_page[u] = ep.page_table[(size_t)ep.seq_rows[t] * ep.max_pages + pre_pos[u] / kKvTile];
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                const int j = j0 + u * GEMM_EPI_WARPS;
                 const int t = t0 + j;
-                if (t >= T) break;
+                if (j >= jend || t >= T) break;
                 float4 y;
                 if (reduce) {
                     const float4* src = reinterpret_cast<const float4*>(slabs + (size_t)j * GEMM_BM + r4);
@@ -322,25 +364,20 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                 const float rs = rstd_s[j];
                 if (mode == FT_EPI_RESID) {
                     const size_t idx = (size_t)t * n_out + row;
-                    float4 r = *reinterpret_cast<const float4*>(ep.resid + idx);
-                    r = f4_add(r, y);
+                    float4 r = f4_add(pre_r[u], y);
                     *reinterpret_cast<float4*>(ep.resid + idx) = r;
                     store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
                                  idx, make_float4(r.x * gam.x, r.y * gam.y, r.z * gam.z, r.w * gam.w));
                     const float ss = warp_sum(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
                     if (lane == 0) ep.ssq_out[(size_t)blockIdx.x * ep.ssq_stride + t] = ss;
                 } else if (mode == FT_EPI_QKV_ROPE) {
-                    const int d = ep.head_dim, half = d >> 1;
-                    const int q_dim = ep.nq * d, kv_dim = ep.nkv * d;
-                    const int region = row0 < q_dim ? 0 : row0 < q_dim + kv_dim ? 1 : 2;   // tile-uniform
-                    const int i = row % d;
-                    const int pos = ep.positions[t];
+                    const int d = d_, half = half_, q_dim = q_dim_, kv_dim = kv_dim_, i = i_;
+                    const int pos = pre_pos[u];
                     float4 val = f4_mul(y, rs);
                     if (region < 2) {
                         // rotate_half partner (i +- d/2) sits half/4 lanes away in the same warp
                         const float4 b = f4_shfl_xor(val, half >> 2);
-                        const float4 c = *reinterpret_cast<const float4*>(ep.rope_cos + (size_t)pos * half + (i % half));
-                        const float4 s = *reinterpret_cast<const float4*>(ep.rope_sin + (size_t)pos * half + (i % half));
+                        const float4 c = pre_c[u], s = pre_s[u];
                         const float sg = i < half ? -1.f : 1.f;
                         val = make_float4(val.x * c.x + sg * b.x * s.x, val.y * c.y + sg * b.y * s.y,
                                           val.z * c.z + sg * b.z * s.z, val.w * c.w + sg * b.w * s.w);
@@ -352,7 +389,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                         *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ep.q_out) + (size_t)t * q_dim + row) = h4;
                     } else {
                         const int kvh = (row - q_dim - (region == 2 ? kv_dim : 0)) / d;
-                        const int page = ep.page_table[(size_t)ep.seq_rows[t] * ep.max_pages + pos / kKvTile];
+                        const int page = pre_page[u];
                         const int r = pos % kKvTile;
                         uint8_t* slab = reinterpret_cast<uint8_t*>(ep.kv_layer) +
                                         (((size_t)page * ep.nkv + kvh) * 2 + (region == 2 ? 1 : 0)) *
@@ -378,6 +415,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                     store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
                                  (size_t)t * n_out + row, f4_mul(y, rs));
                 }
+            }
             }
             if (reduce) {
                 // the last CTA of the row tile to finish re-arms the counters for the next launch
@@ -476,8 +514,12 @@ static int stage_plan(int n_out, int T, int K, int splits, int* stages_out, size
     const int kc = K / GEMM_BK;
     const int per_cta = (kc + splits - 1) / splits;
     const int tiles = (n_out / GEMM_BM) * ((T + BN - 1) / BN) * splits;
-    // multi-wave grids: two CTAs per SM so one CTA's epilogue overlaps the other's streaming
-    const int budget = tiles > device_sms() ? 108 * 1024 : 208 * 1024;
+    // One CTA per SM with the deepest ring that fits: measured on the 8192-token prefill step, two
+    // co-resident CTAs with two-stage rings ran the projections 1.45x slower than one CTA with four
+    // stages (the ring, not epilogue overlap, is what keeps the tensor pipe fed).
+    int budget = 208 * 1024;
+    if (const char* ov = getenv("FT_GEMM_MW_KB"))         // tuning experiments: smem budget of multi-wave grids
+        if (tiles > device_sms() && atoi(ov) >= 64 && atoi(ov) <= 208) budget = atoi(ov) * 1024;
     int stages = budget / STAGE_BYTES;
     if (stages > 12) stages = 12;
     if (const char* ov = getenv("FT_GEMM_STAGES")) {      // tuning experiments (scripts/bench_gemm.py)
@@ -504,6 +546,11 @@ static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CU
     if (!attr_set) {
         FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, HILO>,
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        // without this the driver sizes the shared-memory carve-out for ONE CTA of a ~100 KB launch and
+        // the second CTA the multi-wave plan counts on never becomes resident (ncu: occupancy limit 1)
+        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, HILO>,
+                                           cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           cudaSharedmemCarveoutMaxShared));
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
