@@ -91,6 +91,15 @@ struct Engine {
     float* attn_scratch = nullptr;
     StepMeta meta;
 
+    // tensor parallelism (2 ranks): buffers the peer writes into, and the peer's as mapped here
+    int tp = 1, vocab_local = 0;
+    float* tp_xchg = nullptr;          // [2 parities][t_max][hidden] fp32 partial rows from the peer
+    unsigned* tp_flags = nullptr;      // [kTpFlags] arrival words written by the peer
+    float* peer_xchg = nullptr;
+    unsigned* peer_flags = nullptr;
+    float* peer_logits = nullptr;
+    unsigned tp_epoch = 0;             // advances once per exchanging launch, identically on both ranks
+
     // tensor maps: weights per layer, activations per BN
     std::vector<CUtensorMap> m_wqkv, m_wo, m_wgu, m_wd;
     CUtensorMap m_lm;
@@ -114,6 +123,23 @@ struct Engine {
     long long prof_ctx_sum = 0;            // sum of context lengths of the step's decode rows
     cudaEvent_t t0 = nullptr, t1 = nullptr;
 };
+
+constexpr int kTpFlags = 16384;        // >= CTAs of any exchanging GEMM launch; the last word is the step barrier
+
+// Step barrier between the two ranks before sampling: both halves of the logits are in place.
+__global__ void tp_barrier_kernel(unsigned* peer_flag, const unsigned* flag, unsigned epoch) {
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(peer_flag), "r"(epoch) : "memory");
+        unsigned v, spins = 0;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+            if ((int)(v - epoch) >= 0) break;
+            __nanosleep(64);
+            if (++spins > (1u << 25)) __trap();
+        } while (true);
+    }
+}
 
 static int bn_index(int bn) { return bn == 16 ? 0 : bn == 32 ? 1 : bn == 64 ? 2 : 3; }
 static const int kBns[4] = {16, 32, 64, 128};
@@ -194,6 +220,18 @@ static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, 
     const int splits = staged ? gemm_pick_splits(n_out, T, K, e->sms, true) : 1;
     epi.scratch = e->gemm_scratch;
     epi.sync = e->gemm_sync;
+    if (e->tp > 1 && epi.mode == FT_EPI_RESID) {
+        // row-parallel projection: the all-reduce over the two ranks happens inside the epilogue
+        const unsigned epoch = ++e->tp_epoch;
+        const size_t half = (size_t)e->t_max * e->cfg.hidden;
+        epi.tp_peer_xchg = e->peer_xchg + (epoch & 1) * half;
+        epi.tp_xchg = e->tp_xchg + (epoch & 1) * half;
+        epi.tp_peer_flags = e->peer_flags;
+        epi.tp_flags = e->tp_flags;
+        epi.tp_epoch = epoch;
+        const int ctas = (n_out / 128) * ((T + bn - 1) / bn) * splits;
+        FT_REQUIRE(ctas < kTpFlags, "engine: %d CTAs exceed the tensor-parallel arrival words", ctas);
+    }
     e->st.kernel_launches++;
     return launch_gemm(mw, xmaps[bn_index(bn)], &xmaps_lo[bn_index(bn)], bn, n_out, T, K, splits, epi, e->pdl,
                        e->stream);
@@ -325,7 +363,18 @@ static int forward(Engine* e, const Batch& b) {
             ep.ssq_in = e->ssq_last;
             ep.ssq_stride = e->rows_last;
         }
-        FT_TRY(run_gemm(e, e->m_lm, xm, xl, b.n_logit_rows, c.vocab, c.hidden, ep));
+        if (e->tp > 1) {                 // vocabulary-parallel: each rank fills its columns on both GPUs
+            ep.out_stride = c.vocab;
+            ep.out_col0 = c.tp_rank * e->vocab_local;
+            ep.tp_peer_out = e->peer_logits;
+        }
+        FT_TRY(run_gemm(e, e->m_lm, xm, xl, b.n_logit_rows, e->vocab_local, c.hidden, ep));
+        if (e->tp > 1) {
+            const unsigned epoch = ++e->tp_epoch;
+            tp_barrier_kernel<<<1, 32, 0, e->stream>>>(e->peer_flags + kTpFlags - 1, e->tp_flags + kTpFlags - 1, epoch);
+            FT_CHECK_CUDA(cudaGetLastError());
+            e->st.kernel_launches++;
+        }
     }
     return 0;
 }
@@ -561,6 +610,10 @@ static int engine_init(Engine* e) {
     e->r_max = c.max_batch;
     e->logit_rows = std::max(c.max_batch, c.debug_logit_rows);
     e->pdl = c.use_pdl != 0;
+    e->tp = c.tp_size > 1 ? c.tp_size : 1;
+    FT_REQUIRE(e->tp <= 2 && c.tp_rank >= 0 && c.tp_rank < e->tp, "engine: tensor parallelism is built for 2 ranks");
+    FT_REQUIRE(c.vocab % (128 * e->tp) == 0, "engine: vocab must split into 128-row tiles per rank");
+    e->vocab_local = c.vocab / e->tp;
     e->kv_layer_bytes = (size_t)c.num_pages * c.n_kv_heads * 2 * kKvTile * c.head_dim * 2;
 
     const size_t T = e->t_max;
@@ -570,6 +623,12 @@ static int engine_init(Engine* e) {
     const size_t rows_last = std::max<size_t>(e->logit_rows, 256);
     FT_CHECK_CUDA(cudaMalloc(&e->q, T * e->q_dim * 2));
     FT_CHECK_CUDA(cudaMalloc(&e->logits, (size_t)e->logit_rows * c.vocab * 4));
+    if (e->tp > 1) {
+        // plain cudaMalloc: these three are exported to the peer process through cudaIpc handles
+        FT_CHECK_CUDA(cudaMalloc(&e->tp_xchg, 2 * T * c.hidden * 4));
+        FT_CHECK_CUDA(cudaMalloc(&e->tp_flags, kTpFlags * sizeof(unsigned)));
+        FT_CHECK_CUDA(cudaMemsetAsync(e->tp_flags, 0, kTpFlags * sizeof(unsigned), e->stream));
+    }
     auto alloc_zero = [&](void** p, size_t bytes) -> int {
         FT_CHECK_CUDA(cudaMalloc(p, bytes));
         FT_CHECK_CUDA(cudaMemsetAsync(*p, 0, bytes, e->stream));
@@ -640,7 +699,7 @@ static int engine_init(Engine* e) {
         FT_TRY(make_tmap_bf16_k64(&e->m_wgu[l], at(e->w.wgu, l * 2 * (size_t)c.ffn * c.hidden), 2 * c.ffn, c.hidden, 128));
         FT_TRY(make_tmap_bf16_k64(&e->m_wd[l], at(e->w.wd, l * (size_t)c.hidden * c.ffn), c.hidden, c.ffn, 128));
     }
-    FT_TRY(make_tmap_bf16_k64(&e->m_lm, e->w.lm_head, c.vocab, c.hidden, 128));
+    FT_TRY(make_tmap_bf16_k64(&e->m_lm, e->w.lm_head, e->vocab_local, c.hidden, 128));
     for (int i = 0; i < 4; ++i) {
         // activation maps span the whole buffer; rows past the step's T hold stale (finite) data
         // whose output columns the GEMM epilogue masks
@@ -670,6 +729,7 @@ static void engine_free(Engine* e) {
     for (auto& kv : e->requests) delete kv.second;
     cudaFree(e->kv); cudaFree(e->resid); cudaFree(e->ssq); cudaFree(e->ssq_last); cudaFree(e->gemm_scratch); cudaFree(e->gemm_sync); cudaFree(e->xn); cudaFree(e->q);
     cudaFree(e->attn_out); cudaFree(e->act); cudaFree(e->xn_last); cudaFree(e->logits);
+    cudaFree(e->tp_xchg); cudaFree(e->tp_flags);
     cudaFree(e->xn_lo); cudaFree(e->attn_out_lo); cudaFree(e->act_lo); cudaFree(e->xn_last_lo);
     cudaFree(e->attn_scratch); cudaFree(e->meta.d);
     if (e->meta.h) cudaFreeHost(e->meta.h);
@@ -751,9 +811,55 @@ extern "C" long long ft_engine_submit(ft_engine* h, unsigned long long key, cons
     return r->id;
 }
 
+extern "C" int ft_engine_tp_export(ft_engine* h, void** xchg, void** flags, void** logits) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e && xchg && flags && logits, "ft_engine_tp_export: bad arguments");
+    FT_REQUIRE(e->tp > 1, "ft_engine_tp_export: the engine was created without tensor parallelism");
+    FT_CHECK_CUDA(cudaStreamSynchronize(e->stream));       // the arrival words are zeroed
+    *xchg = e->tp_xchg;
+    *flags = e->tp_flags;
+    *logits = e->logits;
+    return 0;
+}
+
+extern "C" int ft_engine_tp_attach(ft_engine* h, void* peer_xchg, void* peer_flags, void* peer_logits) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e && peer_xchg && peer_flags && peer_logits, "ft_engine_tp_attach: bad arguments");
+    FT_REQUIRE(e->tp > 1, "ft_engine_tp_attach: the engine was created without tensor parallelism");
+    std::lock_guard<std::mutex> lk(e->mu);
+    e->peer_xchg = static_cast<float*>(peer_xchg);
+    e->peer_flags = static_cast<unsigned*>(peer_flags);
+    e->peer_logits = static_cast<float*>(peer_logits);
+    return 0;
+}
+
+extern "C" int ft_ipc_export(void* device_ptr, unsigned char handle_out[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    FT_REQUIRE(device_ptr && handle_out, "ft_ipc_export: bad arguments");
+    cudaIpcMemHandle_t hd;
+    FT_CHECK_CUDA(cudaIpcGetMemHandle(&hd, device_ptr));
+    memcpy(handle_out, &hd, 64);
+    return 0;
+}
+
+extern "C" int ft_ipc_open(const unsigned char handle[64], void** device_ptr_out) {
+    FT_REQUIRE(handle && device_ptr_out, "ft_ipc_open: bad arguments");
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, handle, 64);
+    FT_CHECK_CUDA(cudaIpcOpenMemHandle(device_ptr_out, hd, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+
+extern "C" int ft_ipc_close(void* device_ptr) {
+    FT_REQUIRE(device_ptr, "ft_ipc_close: null pointer");
+    FT_CHECK_CUDA(cudaIpcCloseMemHandle(device_ptr));
+    return 0;
+}
+
 extern "C" int ft_engine_step(ft_engine* h) {
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e, "ft_engine_step: null engine");
+    FT_REQUIRE(e->tp == 1 || e->peer_xchg, "ft_engine_step: tensor-parallel engine has no peer attached");
     std::lock_guard<std::mutex> lk(e->mu);
     return engine_step(e);
 }

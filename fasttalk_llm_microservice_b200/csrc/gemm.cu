@@ -40,6 +40,14 @@ constexpr int GEMM_THREADS = 64 + GEMM_EPI_THREADS;
 __device__ __forceinline__ void epi_bar_sync() {
     asm volatile("bar.sync 2, %0;" ::"n"(GEMM_EPI_THREADS) : "memory");
 }
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
     unsigned v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -313,6 +321,36 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                 const uint2 gv = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(ep.gamma) + row);
                 gam = make_float4(bf16_lo(gv.x), bf16_hi(gv.x), bf16_lo(gv.y), bf16_hi(gv.y));
             }
+            // ---- tensor-parallel exchange (RESID, 2 GPUs): this CTA's partial rows go to the peer over
+            // NVLink, the peer's twin CTA (same block index, same tile and token share) sends its own
+            const bool tp = mode == FT_EPI_RESID && ep.tp_peer_xchg != nullptr;
+            if (tp) {
+                for (int j = jbeg + ew; j < jend; j += GEMM_EPI_WARPS) {
+                    const int t = t0 + j;
+                    if (t >= T) break;
+                    float4 y;
+                    if (reduce) {
+                        const float4* src = reinterpret_cast<const float4*>(slabs + (size_t)j * GEMM_BM + r4);
+                        y = __ldcg(src);
+                        for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
+                    } else {
+                        y = *reinterpret_cast<const float4*>(stage_f + j * GEMM_BM + r4);
+                    }
+                    *reinterpret_cast<float4*>(ep.tp_peer_xchg + (size_t)t * n_out + row) = y;
+                }
+                __threadfence_system();
+                epi_bar_sync();
+                if (et == 0) {
+                    const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+                    st_release_sys_u32(ep.tp_peer_flags + cta, ep.tp_epoch);
+                    unsigned spins = 0;
+                    while ((int)(ld_acquire_sys_u32(ep.tp_flags + cta) - ep.tp_epoch) < 0) {
+                        __nanosleep(64);
+                        if (++spins > (1u << 25)) __trap();      // the peer GPU never ran this launch: fail loudly
+                    }
+                }
+                epi_bar_sync();
+            }
             // Tokens are taken four at a time per warp: the global operands of the batch (residual rows,
             // or position -> RoPE angles / KV page) are requested first, so a 128-token prefill tile pays
             // their latency 4 times per warp instead of 16 (ncu: the O projection spent 20 of 35 us here).
@@ -364,6 +402,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                 const float rs = rstd_s[j];
                 if (mode == FT_EPI_RESID) {
                     const size_t idx = (size_t)t * n_out + row;
+                    if (tp) y = f4_add(y, __ldcg(reinterpret_cast<const float4*>(ep.tp_xchg + idx)));   // a + b == b + a
                     float4 r = f4_add(pre_r[u], y);
                     *reinterpret_cast<float4*>(ep.resid + idx) = r;
                     store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
@@ -410,7 +449,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                         *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out_lo) + idx) =
                             pack_bf16(a0 - bf16_lo(h), a1 - bf16_hi(h));
                 } else if (mode == FT_EPI_LOGITS) {
-                    *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + (size_t)t * n_out + row) = f4_mul(y, rs);
+                    const size_t idx = (size_t)t * (ep.out_stride ? ep.out_stride : n_out) + ep.out_col0 + row;
+                    const float4 lg = f4_mul(y, rs);
+                    *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + idx) = lg;
+                    if (ep.tp_peer_out) *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.tp_peer_out) + idx) = lg;
                 } else {   // FT_EPI_BF16
                     store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
                                  (size_t)t * n_out + row, f4_mul(y, rs));
@@ -598,6 +640,13 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
         FT_REQUIRE(epi.scratch && epi.sync, "gemm: split-K fused epilogues need scratch and sync buffers");
     }
     FT_REQUIRE(!(hilo && bn > 128), "gemm: hi/lo activations support token tiles up to 128");
+    if (epi.tp_peer_xchg)
+        FT_REQUIRE(mode == FT_EPI_RESID && epi.tp_xchg && epi.tp_peer_flags && epi.tp_flags,
+                   "gemm: the tensor-parallel exchange belongs to the RESID epilogue and needs all four buffers");
+    if (mode == FT_EPI_LOGITS && epi.out_stride)
+        FT_REQUIRE(epi.out_stride % 4 == 0 && epi.out_col0 % 4 == 0 && epi.out_col0 + n_out <= epi.out_stride,
+                   "gemm: logits slice [%d, %d) does not fit rows of %d", epi.out_col0, epi.out_col0 + n_out,
+                   epi.out_stride);
     if (mode == FT_EPI_QKV_ROPE) {
         FT_REQUIRE(epi.head_dim == 64 || epi.head_dim == 128, "gemm: head_dim %d not supported", epi.head_dim);
         FT_REQUIRE((epi.nq * epi.head_dim) % GEMM_BM == 0 && (epi.nkv * epi.head_dim) % GEMM_BM == 0 &&

@@ -43,16 +43,25 @@ class EngineLimits:
 
 class Engine:
     def __init__(self, spec: ModelSpec, weights: Dict[str, torch.Tensor], limits: Optional[EngineLimits] = None,
-                 eos_ids: Sequence[int] = LLAMA3_EOS, device: Optional[torch.device] = None):
+                 eos_ids: Sequence[int] = LLAMA3_EOS, device: Optional[torch.device] = None,
+                 tp_rank: int = 0, tp_size: int = 1):
+        """`weights` is always the FULL model (weights.py layout); with tp_size == 2 this rank keeps
+        only its slices (tp.shard_weights) and `tp.connect(engine)` must follow on both ranks."""
         if not torch.cuda.is_available():
             raise N.NativeError("fasttalk_b200 Engine needs a CUDA device (sm_100a); there is no CPU fallback")
         self.lib = N.load()
-        self.spec = spec
+        self.full_spec, self.tp_rank, self.tp_size = spec, tp_rank, tp_size
         self.limits = lim = limits or EngineLimits()
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         torch.cuda.set_device(self.device)
+        if tp_size > 1:
+            from .tp import shard_spec, shard_weights
+            weights = shard_weights(spec, weights, tp_rank, tp_size)
+            spec = shard_spec(spec, tp_size)
+        self.spec = spec
         w = {k: v.to(self.device).contiguous() for k, v in weights.items() if k != "lm_head"}
-        w["lm_head"] = w["embed"] if weights["lm_head"] is weights["embed"] else weights["lm_head"].to(self.device).contiguous()
+        w["lm_head"] = (w["embed"] if weights["lm_head"] is weights["embed"]
+                        else weights["lm_head"].to(self.device).contiguous())
         for k, v in w.items():
             assert v.dtype == torch.bfloat16, f"weight {k} must be bf16"
         # engine-side layout of the gate/up projection (fused SwiGLU epilogue); one layer at a time
@@ -78,6 +87,7 @@ class Engine:
             cfg.eos_ids[i] = e
         cfg.use_pdl = int(lim.use_pdl)
         cfg.debug_logit_rows = lim.debug_logit_rows
+        cfg.tp_size, cfg.tp_rank = tp_size, tp_rank
         wt = N.Weights()
         for name in ("embed", "lm_head", "final_norm", "attn_norm", "wqkv", "wo", "mlp_norm", "wgu", "wd"):
             setattr(wt, name, w[name].data_ptr())

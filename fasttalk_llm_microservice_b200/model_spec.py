@@ -100,8 +100,14 @@ TINY_D128 = ModelSpec(
     rope_factor=8.0,
 )
 
+# splits over two tensor-parallel ranks in whole tiles (4 q heads, 2 kv heads, ffn 256, vocab 512 each)
+TINY_TP = ModelSpec(
+    name="tiny-tp", hidden=256, ffn=512, layers=2,
+    n_q_heads=8, n_kv_heads=4, head_dim=64, vocab=1024, tied_embeddings=False,
+)
+
 SPECS: Dict[str, ModelSpec] = {
-    s.name: s for s in (LLAMA_3_2_1B, LLAMA_3_2_3B, LLAMA_3_1_8B, TINY_D64, TINY_D128)
+    s.name: s for s in (LLAMA_3_2_1B, LLAMA_3_2_3B, LLAMA_3_1_8B, TINY_D64, TINY_D128, TINY_TP)
 }
 # the tags the reference's config uses (app/utils/config.py:86, README.md:474)
 ALIASES = {

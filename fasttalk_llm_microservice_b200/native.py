@@ -26,6 +26,7 @@ class EngineConfig(C.Structure):
         ("max_context", C.c_int), ("max_sessions", C.c_int),
         ("n_eos", C.c_int), ("eos_ids", C.c_int * 4),
         ("use_pdl", C.c_int), ("debug_logit_rows", C.c_int),
+        ("tp_size", C.c_int), ("tp_rank", C.c_int),
     ]
 
 
@@ -61,6 +62,9 @@ class GemmEpilogue(C.Structure):
         ("nq", C.c_int), ("nkv", C.c_int), ("head_dim", C.c_int),
         ("scratch", C.c_void_p), ("sync", C.c_void_p),
         ("prefetch", C.c_void_p), ("prefetch_bytes", C.c_longlong),
+        ("tp_peer_xchg", C.c_void_p), ("tp_xchg", C.c_void_p), ("tp_peer_flags", C.c_void_p),
+        ("tp_flags", C.c_void_p), ("tp_epoch", C.c_uint), ("tp_peer_out", C.c_void_p),
+        ("out_stride", C.c_int), ("out_col0", C.c_int),
     ]
 
 
@@ -82,6 +86,11 @@ SIGNATURES = {
     "ft_engine_timer": (_I, [_VP, _I, _VP]),
     "ft_engine_set_profile": (_I, [_VP, _I]),
     "ft_debug_prefill_logits": (_I, [_VP, _VP, _I, _I, _VP]),
+    "ft_engine_tp_export": (_I, [_VP, _VP, _VP, _VP]),
+    "ft_engine_tp_attach": (_I, [_VP, _VP, _VP, _VP]),
+    "ft_ipc_export": (_I, [_VP, _VP]),
+    "ft_ipc_open": (_I, [_VP, _VP]),
+    "ft_ipc_close": (_I, [_VP]),
     "ft_gemm_bf16": (_I, [_VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
     "ft_gemm_pick_splits": (_I, [_I, _I, _I, _I]),
     "ft_debug_gemm_trace": (_I, [_VP]),

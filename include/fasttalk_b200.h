@@ -44,6 +44,14 @@ typedef struct {
     int eos_ids[4];          /* stop tokens (<|eot_id|> 128009, <|end_of_text|> 128001) */
     int use_pdl;             /* programmatic dependent launch between the step's kernels */
     int debug_logit_rows;    /* rows of the logits buffer (>= max_batch); more only for ft_debug_* */
+    /* Tensor parallelism (Llama-3.1-8B, TP=2 over NVLink).  tp_size 0/1 = off, 2 = this
+     * engine is one of two ranks, one process per GPU.  n_q_heads, n_kv_heads and ffn are then this
+     * rank's SHARE (half), vocab stays the full vocabulary, and the weights are the rank's slices:
+     * wqkv rows (q | k | v of the local heads), wo columns of the local heads, wgu rows of the local
+     * half of ffn (then interleaved), wd columns of that half, lm_head rows [rank * vocab/2, ...).
+     * Both ranks must be fed the same requests in the same order and stepped together; call
+     * ft_engine_tp_export / ft_engine_tp_attach after creation, before the first step. */
+    int tp_size, tp_rank;
 } ft_engine_config;
 
 typedef struct {
@@ -74,6 +82,17 @@ typedef struct {
     int last_batch, last_prefill_tokens;
     double last_step_ms;              /* host wall time of the last ft_engine_step */
 } ft_engine_stats;
+
+/* Tensor-parallel wiring.  ft_engine_tp_export returns this engine's three peer-visible device
+ * buffers (exchange area, arrival words, logits) so the host can hand them to the other rank —
+ * ft_ipc_export / ft_ipc_open turn a device pointer into a 64-byte handle another process can map
+ * (cudaIpc*; the peer GPU must be reachable over NVLink / P2P).  ft_engine_tp_attach takes the
+ * peer's three buffers as mapped in THIS process. */
+int ft_engine_tp_export(ft_engine* e, void** xchg, void** flags, void** logits);
+int ft_engine_tp_attach(ft_engine* e, void* peer_xchg, void* peer_flags, void* peer_logits);
+int ft_ipc_export(void* device_ptr, unsigned char handle_out[64]);
+int ft_ipc_open(const unsigned char handle[64], void** device_ptr_out);
+int ft_ipc_close(void* device_ptr);
 
 /* Weights stay owned by the caller and must outlive the engine. */
 ft_engine* ft_engine_create(const ft_engine_config* cfg, const ft_weights* w);
@@ -176,6 +195,21 @@ typedef struct {
     int* sync;                 /* 〃: int32 [2 * row tiles * token tiles], zero before first use (self re-arming) */
     const void* prefetch;      /* optional: a contiguous region (the NEXT projection's weights) the CTAs pull */
     long long prefetch_bytes;  /*   into L2 while this kernel sits in its dependency / epilogue latency */
+    /* Tensor parallelism over NVLink peer memory, fused into the epilogue (2 GPUs; NULL / 0 = off).
+     * RESID: K is split across the two GPUs (row-parallel O / down projection).  Each CTA stores its
+     * fp32 partial rows straight into the PEER's exchange buffer, raises the twin CTA's flag there
+     * (release at system scope), waits for its own flag and adds what the peer stored here: the
+     * all-reduce is part of this kernel, tile by tile, no collective call.  a + b == b + a, so both
+     * GPUs end with bit-identical residuals.
+     * LOGITS: the vocabulary is split; rows go to out[t * out_stride + out_col0 + n] locally and to the
+     * same place in the peer's logits buffer (tp_peer_out). */
+    float* tp_peer_xchg;       /* RESID: peer's exchange buffer [T][n_out] fp32 (this launch's parity half) */
+    const float* tp_xchg;      /* RESID: this GPU's exchange buffer, written by the peer */
+    unsigned* tp_peer_flags;   /* RESID: peer's per-CTA arrival words (>= grid size) */
+    const unsigned* tp_flags;  /* RESID: this GPU's arrival words */
+    unsigned tp_epoch;         /* RESID: value of this launch's arrivals; must grow launch over launch */
+    void* tp_peer_out;         /* LOGITS: peer's logits buffer (same layout as out) or NULL */
+    int out_stride, out_col0;  /* LOGITS: row stride / first column of out (0, 0 = n_out, 0) */
 } ft_gemm_epilogue;
 long long ft_gemm_scratch_bytes(int n_out, int T, int K, int n_splits);
 int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int n_out, int T, int K, int n_splits,
