@@ -88,6 +88,270 @@ __device__ __forceinline__ void store_hi_lo4(__nv_bfloat16* hi, __nv_bfloat16* l
 }
 __device__ __forceinline__ float silu(float g) { return __fdividef(g, 1.f + __expf(-g)); }
 
+// Where a CTA's output tile sits and how its K range was split (the stand-alone kernel takes these
+// from the block index, the persistent kernel from its tile loop).
+struct EpiCtx {
+    int row_tile, tok_tile, split, n_split, tile_id;
+    unsigned cta_linear;     // arrival word of this CTA in the tensor-parallel exchange
+    int n_out, T;
+    bool has_acc;            // false: K range empty, the tile is all zeros
+};
+
+// per-token 1/rms of the activation's source (RMSNorm deferred past the projection), all BN tokens of the tile
+template <int BN>
+__device__ __forceinline__ void epilogue_rstd(const ft_gemm_epilogue& ep, const EpiCtx& c, float* rstd_s) {
+    const int et = threadIdx.x - 64;
+    const int t0 = c.tok_tile * BN, T = c.T;
+    // per-token 1/rms of the activation's source (RMSNorm deferred past the projection)
+    for (int j = et; j < BN; j += GEMM_EPI_THREADS) {
+        float r = 1.f;
+        const int t = t0 + j;
+        if (ep.ssq_in && t < T) {
+            float s = 0.f;
+            for (int p = 0; p < ep.ssq_parts; ++p) s += __ldcg(ep.ssq_in + (size_t)p * ep.ssq_stride + t);
+            r = rsqrtf(s * ep.inv_h + ep.eps);
+        }
+        rstd_s[j] = r;
+    }
+}
+
+// The epilogue (warps 2..9) for token columns [col0, col0 + CB) of the tile: accumulator out of TMEM,
+// split-K rendezvous (CB == BN only), fused layer step.  stage_f: [CB][128] fp32 of shared memory
+// nobody else touches while this runs; rstd_s from epilogue_rstd; the caller has waited for the
+// accumulator (tmem_acc = its first column).
+template <int BN, int CB>
+__device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const EpiCtx& c, uint32_t tmem_acc,
+                                              float* stage_f, const float* rstd_s, int col0) {
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int mode = ep.mode;
+    const int row0 = c.row_tile * GEMM_BM, t0 = c.tok_tile * BN;
+    const int split = c.split, n_split = c.n_split, n_out = c.n_out, T = c.T;
+    const int ew = warp - 2;                // 0..7
+    const int q = warp & 3;                 // TMEM lane quarter this warp may read (warp_id % 4)
+    const int et = threadIdx.x - 64;        // 0..255
+    const bool reduce = (mode == FT_EPI_RESID || mode == FT_EPI_QKV_ROPE) && n_split > 1;
+
+    // ---- phase 1: accumulator tile TMEM -> [token][row] staging
+    const int tile_id = c.tile_id;
+    float* slabs = reduce ? ep.scratch + (size_t)tile_id * n_split * (BN * GEMM_BM) : nullptr;
+    {
+        constexpr int CPW = CB >= 32 ? CB / 2 : 16;     // columns per warp: two warps share a lane quarter
+        const int cbeg = (ew >> 2) * CPW;
+        const int rl = q * 32 + lane;                   // tile row this thread reads out of TMEM
+#pragma unroll 1
+        for (int c0 = cbeg; c0 < cbeg + CPW && c0 < CB; c0 += 16) {
+            if (t0 + col0 + c0 >= T) break;
+            float v[16];
+            if (c.has_acc) {
+                tmem_ld16(tmem_acc + ((uint32_t)(q * 32) << 16) + col0 + c0, v);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = 0.f;
+            }
+            // three store flavours, each with compile-time strides so that no address
+            // arithmetic is left in the unrolled body
+            if (mode == FT_EPI_PARTIAL) {
+                float* p = reinterpret_cast<float*>(ep.out) + ((size_t)split * T + t0 + col0 + c0) * n_out + row0 + rl;
+                const int valid = T - (t0 + col0 + c0);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    if (j < valid) *p = v[j];
+                    p += n_out;
+                }
+            } else if (reduce) {
+                float* p = slabs + ((size_t)split * BN + c0) * GEMM_BM + rl;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) __stcg(p + j * GEMM_BM, v[j]);
+            } else {
+                const uint32_t a = smem_u32(stage_f) + (uint32_t)(c0 * GEMM_BM + rl) * 4;
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + j * GEMM_BM * 4), "f"(v[j]) : "memory");
+            }
+        }
+    }
+    if (et == 0) trace(7);
+
+    if (mode != FT_EPI_PARTIAL) {
+        // ---- phase 2: make the tile visible (CTA barrier, or split-K rendezvous in global memory)
+        unsigned* cnt = reinterpret_cast<unsigned*>(ep.sync) + 2 * tile_id;
+        if (reduce) {
+            __threadfence();
+            epi_bar_sync();
+            if (et == 0) {
+                atomicAdd(cnt, 1u);
+                unsigned spins = 0;
+                while (ld_acquire_u32(cnt) < (unsigned)n_split) {
+                    __nanosleep(32);
+                    if (++spins > (1u << 25)) __trap();      // a peer never arrived: fail loudly, do not hang
+                }
+            }
+            epi_bar_sync();
+            __threadfence();
+        } else {
+            epi_bar_sync();
+        }
+
+        // ---- phase 3: one token per warp, four consecutive rows per lane
+        const int jbeg = reduce ? BN * split / n_split : col0;
+        const int jend = reduce ? BN * (split + 1) / n_split : col0 + CB;
+        const int r4 = 4 * lane;
+        const int row = row0 + r4;
+        float4 gam = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (mode == FT_EPI_RESID) {
+            const uint2 gv = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(ep.gamma) + row);
+            gam = make_float4(bf16_lo(gv.x), bf16_hi(gv.x), bf16_lo(gv.y), bf16_hi(gv.y));
+        }
+        // ---- tensor-parallel exchange (RESID, 2 GPUs): this CTA's partial rows go to the peer over
+        // NVLink, the peer's twin CTA (same block index, same tile and token share) sends its own
+        const bool tp = mode == FT_EPI_RESID && ep.tp_peer_xchg != nullptr;
+        if (tp) {
+            for (int j = jbeg + ew; j < jend; j += GEMM_EPI_WARPS) {
+                const int t = t0 + j;
+                if (t >= T) break;
+                float4 y;
+                if (reduce) {
+                    const float4* src = reinterpret_cast<const float4*>(slabs + (size_t)j * GEMM_BM + r4);
+                    y = __ldcg(src);
+                    for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
+                } else {
+                    y = *reinterpret_cast<const float4*>(stage_f + (j - col0) * GEMM_BM + r4);
+                }
+                *reinterpret_cast<float4*>(ep.tp_peer_xchg + (size_t)t * n_out + row) = y;
+            }
+            __threadfence_system();
+            epi_bar_sync();
+            if (et == 0) {
+                const unsigned cta = c.cta_linear;
+                st_release_sys_u32(ep.tp_peer_flags + cta, ep.tp_epoch);
+                unsigned spins = 0;
+                while ((int)(ld_acquire_sys_u32(ep.tp_flags + cta) - ep.tp_epoch) < 0) {
+                    __nanosleep(64);
+                    if (++spins > (1u << 25)) __trap();      // the peer GPU never ran this launch: fail loudly
+                }
+            }
+            epi_bar_sync();
+        }
+        // Tokens are taken four at a time per warp: the global operands of the batch (residual rows,
+        // or position -> RoPE angles / KV page) are requested first, so a 128-token prefill tile pays
+        // their latency 4 times per warp instead of 16 (ncu: the O projection spent 20 of 35 us here).
+        constexpr int U = 4;
+        const bool is_resid = mode == FT_EPI_RESID, is_rope = mode == FT_EPI_QKV_ROPE;
+        const int d_ = ep.head_dim, half_ = d_ >> 1;
+        const int q_dim_ = ep.nq * d_, kv_dim_ = ep.nkv * d_;
+        const int region = row0 < q_dim_ ? 0 : row0 < q_dim_ + kv_dim_ ? 1 : 2;   // tile-uniform
+        const int i_ = is_rope ? row % d_ : 0;
+        for (int j0 = jbeg + ew; j0 < jend; j0 += GEMM_EPI_WARPS * U) {
+            float4 pre_r[U], pre_c[U], pre_s[U];
+            int pre_pos[U], pre_page[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
+                pre_pos[u] = 0;
+                if (j < jend && t < T) {
+                    if (is_resid) pre_r[u] = __ldcg(reinterpret_cast<const float4*>(ep.resid + (size_t)t * n_out + row));
+                    if (is_rope) pre_pos[u] = ep.positions[t];
+                }
+            }
+            if (is_rope) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
+                    if (j < jend && t < T) {
+                        if (region < 2) {
+                            pre_c[u] = *reinterpret_cast<const float4*>(ep.rope_cos + (size_t)pre_pos[u] * half_ + (i_ % half_));
+                            pre_s[u] = *reinterpret_cast<const float4*>(ep.rope_sin + (size_t)pre_pos[u] * half_ + (i_ % half_));
+                        }
+                        if (region > 0)
+                            pre_page[u] = ep.page_table[(size_t)ep.seq_rows[t] * ep.max_pages + pre_pos[u] / kKvTile];
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+            const int j = j0 + u * GEMM_EPI_WARPS;
+            const int t = t0 + j;
+            if (j >= jend || t >= T) break;
+            float4 y;
+            if (reduce) {
+                const float4* src = reinterpret_cast<const float4*>(slabs + (size_t)j * GEMM_BM + r4);
+                y = __ldcg(src);
+                for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
+            } else {
+                y = *reinterpret_cast<const float4*>(stage_f + (j - col0) * GEMM_BM + r4);
+            }
+            const float rs = rstd_s[j];
+            if (mode == FT_EPI_RESID) {
+                const size_t idx = (size_t)t * n_out + row;
+                if (tp) y = f4_add(y, __ldcg(reinterpret_cast<const float4*>(ep.tp_xchg + idx)));   // a + b == b + a
+                float4 r = f4_add(pre_r[u], y);
+                *reinterpret_cast<float4*>(ep.resid + idx) = r;
+                store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
+                             idx, make_float4(r.x * gam.x, r.y * gam.y, r.z * gam.z, r.w * gam.w));
+                const float ss = warp_sum(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
+                if (lane == 0) ep.ssq_out[(size_t)c.row_tile * ep.ssq_stride + t] = ss;
+            } else if (mode == FT_EPI_QKV_ROPE) {
+                const int d = d_, half = half_, q_dim = q_dim_, kv_dim = kv_dim_, i = i_;
+                const int pos = pre_pos[u];
+                float4 val = f4_mul(y, rs);
+                if (region < 2) {
+                    // rotate_half partner (i +- d/2) sits half/4 lanes away in the same warp
+                    const float4 b = f4_shfl_xor(val, half >> 2);
+                    const float4 c = pre_c[u], s = pre_s[u];
+                    const float sg = i < half ? -1.f : 1.f;
+                    val = make_float4(val.x * c.x + sg * b.x * s.x, val.y * c.y + sg * b.y * s.y,
+                                      val.z * c.z + sg * b.z * s.z, val.w * c.w + sg * b.w * s.w);
+                }
+                uint2 h4;                       // q, K and V leave as saturating fp16 (attention dtype)
+                h4.x = pack_f16_sat(val.x, val.y);
+                h4.y = pack_f16_sat(val.z, val.w);
+                if (region == 0) {
+                    *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ep.q_out) + (size_t)t * q_dim + row) = h4;
+                } else {
+                    const int kvh = (row - q_dim - (region == 2 ? kv_dim : 0)) / d;
+                    const int page = pre_page[u];
+                    const int r = pos % kKvTile;
+                    uint8_t* slab = reinterpret_cast<uint8_t*>(ep.kv_layer) +
+                                    (((size_t)page * ep.nkv + kvh) * 2 + (region == 2 ? 1 : 0)) *
+                                        (size_t)(kKvTile * d * 2);
+                    const int off = r * (d * 2) + ((((i >> 3) ^ (r & 7))) << 4) + (i & 7) * 2;
+                    *reinterpret_cast<uint2*>(slab + off) = h4;
+                }
+            } else if (mode == FT_EPI_SWIGLU) {
+                // rows 0..63 of the tile are gate features, rows 64..127 the matching up features:
+                // every lane finishes two features (all 32 lanes busy, no shuffles)
+                const float2 g2 = *reinterpret_cast<const float2*>(stage_f + (j - col0) * GEMM_BM + 2 * lane);
+                const float2 u2 = *reinterpret_cast<const float2*>(stage_f + (j - col0) * GEMM_BM + 64 + 2 * lane);
+                const float a0 = silu(g2.x * rs) * (u2.x * rs), a1 = silu(g2.y * rs) * (u2.y * rs);
+                const uint32_t h = pack_bf16(a0, a1);
+                const size_t idx = (size_t)t * (n_out >> 1) + c.row_tile * 64 + 2 * lane;
+                *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + idx) = h;
+                if (ep.out_lo)
+                    *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out_lo) + idx) =
+                        pack_bf16(a0 - bf16_lo(h), a1 - bf16_hi(h));
+            } else if (mode == FT_EPI_LOGITS) {
+                const size_t idx = (size_t)t * (ep.out_stride ? ep.out_stride : n_out) + ep.out_col0 + row;
+                const float4 lg = f4_mul(y, rs);
+                *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + idx) = lg;
+                if (ep.tp_peer_out) *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.tp_peer_out) + idx) = lg;
+            } else {   // FT_EPI_BF16
+                store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
+                             (size_t)t * n_out + row, f4_mul(y, rs));
+            }
+        }
+        }
+        if (reduce) {
+            // the last CTA of the row tile to finish re-arms the counters for the next launch
+            epi_bar_sync();
+            if (et == 0 && atomicAdd(cnt + 1, 1u) == (unsigned)n_split - 1) {
+                cnt[0] = 0;
+                cnt[1] = 0;
+            }
+        }
+    }
+}
+
 template <int BN, bool HILO>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
@@ -118,7 +382,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
     const int kc_begin = (int)(((long long)k_chunks * split) / n_split);
     const int kc_end = (int)(((long long)k_chunks * (split + 1)) / n_split);
     const int n_iter = kc_end - kc_begin;
-    const int mode = ep.mode;
     if (threadIdx.x == 0) trace(0);
 
     if (warp == 0 && lane == 0) {
@@ -227,248 +490,21 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
         }
     } else {
         // ================================================================ epilogue warps (2..9)
-        const int ew = warp - 2;                // 0..7
-        const int q = warp & 3;                 // TMEM lane quarter this warp may read (warp_id % 4)
-        const int et = threadIdx.x - 64;        // 0..255
-        const bool reduce = (mode == FT_EPI_RESID || mode == FT_EPI_QKV_ROPE) && n_split > 1;
         pdl_wait();                             // ssq_in / resid / positions come from earlier kernels
-        // per-token 1/rms of the activation's source (RMSNorm deferred past the projection)
-        for (int j = et; j < BN; j += GEMM_EPI_THREADS) {
-            float r = 1.f;
-            const int t = t0 + j;
-            if (ep.ssq_in && t < T) {
-                float s = 0.f;
-                for (int p = 0; p < ep.ssq_parts; ++p) s += __ldcg(ep.ssq_in + (size_t)p * ep.ssq_stride + t);
-                r = rsqrtf(s * ep.inv_h + ep.eps);
-            }
-            rstd_s[j] = r;
-        }
+        EpiCtx c;
+        c.row_tile = blockIdx.x; c.tok_tile = blockIdx.y; c.split = split; c.n_split = n_split;
+        c.tile_id = blockIdx.y * gridDim.x + blockIdx.x;
+        c.cta_linear = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        c.n_out = n_out; c.T = T; c.has_acc = n_iter > 0;
+        epilogue_rstd<BN>(ep, c, rstd_s);
         if (n_iter > 0) {
             mbar_wait(tmem_full_bar, 0);
             tc_fence_after();
         }
-        if (et == 0) trace(6);
-
-        // ---- phase 1: accumulator tile TMEM -> [token][row] staging
-        const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
-        float* stage_f = reinterpret_cast<float*>(smem);   // pipeline stages are idle once the MMAs retired
-        float* slabs = reduce ? ep.scratch + (size_t)tile_id * n_split * (BN * GEMM_BM) : nullptr;
-        {
-            constexpr int CPW = BN >= 32 ? BN / 2 : 16;     // columns per warp: two warps share a lane quarter
-            const int cbeg = (ew >> 2) * CPW;
-            const int rl = q * 32 + lane;                   // tile row this thread reads out of TMEM
-#pragma unroll 1
-            for (int c0 = cbeg; c0 < cbeg + CPW && c0 < BN; c0 += 16) {
-                if (t0 + c0 >= T) break;
-                float v[16];
-                if (n_iter > 0) {
-                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + c0, v);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) v[j] = 0.f;
-                }
-                // three store flavours, each with compile-time strides so that no address
-                // arithmetic is left in the unrolled body
-                if (mode == FT_EPI_PARTIAL) {
-                    float* p = reinterpret_cast<float*>(ep.out) + ((size_t)split * T + t0 + c0) * n_out + row0 + rl;
-                    const int valid = T - (t0 + c0);
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        if (j < valid) *p = v[j];
-                        p += n_out;
-                    }
-                } else if (reduce) {
-                    float* p = slabs + ((size_t)split * BN + c0) * GEMM_BM + rl;
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) __stcg(p + j * GEMM_BM, v[j]);
-                } else {
-                    const uint32_t a = smem_u32(stage_f) + (uint32_t)(c0 * GEMM_BM + rl) * 4;
-#pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        asm volatile("st.shared.f32 [%0], %1;" ::"r"(a + j * GEMM_BM * 4), "f"(v[j]) : "memory");
-                }
-            }
-        }
-        if (et == 0) trace(7);
-
-        if (mode != FT_EPI_PARTIAL) {
-            // ---- phase 2: make the tile visible (CTA barrier, or split-K rendezvous in global memory)
-            unsigned* cnt = reinterpret_cast<unsigned*>(ep.sync) + 2 * tile_id;
-            if (reduce) {
-                __threadfence();
-                epi_bar_sync();
-                if (et == 0) {
-                    atomicAdd(cnt, 1u);
-                    unsigned spins = 0;
-                    while (ld_acquire_u32(cnt) < (unsigned)n_split) {
-                        __nanosleep(32);
-                        if (++spins > (1u << 25)) __trap();      // a peer never arrived: fail loudly, do not hang
-                    }
-                }
-                epi_bar_sync();
-                __threadfence();
-            } else {
-                epi_bar_sync();
-            }
-
-            // ---- phase 3: one token per warp, four consecutive rows per lane
-            const int jbeg = reduce ? BN * split / n_split : 0;
-            const int jend = reduce ? BN * (split + 1) / n_split : BN;
-            const int r4 = 4 * lane;
-            const int row = row0 + r4;
-            float4 gam = make_float4(1.f, 1.f, 1.f, 1.f);
-            if (mode == FT_EPI_RESID) {
-                const uint2 gv = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(ep.gamma) + row);
-                gam = make_float4(bf16_lo(gv.x), bf16_hi(gv.x), bf16_lo(gv.y), bf16_hi(gv.y));
-            }
-            // ---- tensor-parallel exchange (RESID, 2 GPUs): this CTA's partial rows go to the peer over
-            // NVLink, the peer's twin CTA (same block index, same tile and token share) sends its own
-            const bool tp = mode == FT_EPI_RESID && ep.tp_peer_xchg != nullptr;
-            if (tp) {
-                for (int j = jbeg + ew; j < jend; j += GEMM_EPI_WARPS) {
-                    const int t = t0 + j;
-                    if (t >= T) break;
-                    float4 y;
-                    if (reduce) {
-                        const float4* src = reinterpret_cast<const float4*>(slabs + (size_t)j * GEMM_BM + r4);
-                        y = __ldcg(src);
-                        for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
-                    } else {
-                        y = *reinterpret_cast<const float4*>(stage_f + j * GEMM_BM + r4);
-                    }
-                    *reinterpret_cast<float4*>(ep.tp_peer_xchg + (size_t)t * n_out + row) = y;
-                }
-                __threadfence_system();
-                epi_bar_sync();
-                if (et == 0) {
-                    const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-                    st_release_sys_u32(ep.tp_peer_flags + cta, ep.tp_epoch);
-                    unsigned spins = 0;
-                    while ((int)(ld_acquire_sys_u32(ep.tp_flags + cta) - ep.tp_epoch) < 0) {
-                        __nanosleep(64);
-                        if (++spins > (1u << 25)) __trap();      // the peer GPU never ran this launch: fail loudly
-                    }
-                }
-                epi_bar_sync();
-            }
-            // Tokens are taken four at a time per warp: the global operands of the batch (residual rows,
-            // or position -> RoPE angles / KV page) are requested first, so a 128-token prefill tile pays
-            // their latency 4 times per warp instead of 16 (ncu: the O projection spent 20 of 35 us here).
-            constexpr int U = 4;
-            const bool is_resid = mode == FT_EPI_RESID, is_rope = mode == FT_EPI_QKV_ROPE;
-            const int d_ = ep.head_dim, half_ = d_ >> 1;
-            const int q_dim_ = ep.nq * d_, kv_dim_ = ep.nkv * d_;
-            const int region = row0 < q_dim_ ? 0 : row0 < q_dim_ + kv_dim_ ? 1 : 2;   // tile-uniform
-            const int i_ = is_rope ? row % d_ : 0;
-            for (int j0 = jbeg + ew; j0 < jend; j0 += GEMM_EPI_WARPS * U) {
-                float4 pre_r[U], pre_c[U], pre_s[U];
-                int pre_pos[U], pre_page[U];
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
-                    pre_pos[u] = 0;
-                    if (j < jend && t < T) {
-                        if (is_resid) pre_r[u] = *reinterpret_cast<const float4*>(ep.resid + (size_t)t * n_out + row);
-                        if (is_rope) pre_pos[u] = ep.positions[t];
-                    }
-                }
-                if (is_rope) {
-#pragma unroll
-                    for (int u = 0; u < U; ++u) {
-                        const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
-                        if (j < jend && t < T) {
-                            if (region < 2) {
-                                pre_c[u] = *reinterpret_cast<const float4*>(ep.rope_cos + (size_t)pre_pos[u] * half_ + (i_ % half_));
-                                pre_s[u] = *reinterpret_cast<const float4*>(ep.rope_sin + (size_t)pre_pos[u] * half_ + (i_ % half_));
-                            }
-                            if (region > 0)
-                                pre_page[u] = ep.page_table[(size_t)ep.seq_rows[t] * ep.max_pages + pre_pos[u] / kKvTile];
-                        }
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                const int j = j0 + u * GEMM_EPI_WARPS;
-                const int t = t0 + j;
-                if (j >= jend || t >= T) break;
-                float4 y;
-                if (reduce) {
-                    const float4* src = reinterpret_cast<const float4*>(slabs + (size_t)j * GEMM_BM + r4);
-                    y = __ldcg(src);
-                    for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
-                } else {
-                    y = *reinterpret_cast<const float4*>(stage_f + j * GEMM_BM + r4);
-                }
-                const float rs = rstd_s[j];
-                if (mode == FT_EPI_RESID) {
-                    const size_t idx = (size_t)t * n_out + row;
-                    if (tp) y = f4_add(y, __ldcg(reinterpret_cast<const float4*>(ep.tp_xchg + idx)));   // a + b == b + a
-                    float4 r = f4_add(pre_r[u], y);
-                    *reinterpret_cast<float4*>(ep.resid + idx) = r;
-                    store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
-                                 idx, make_float4(r.x * gam.x, r.y * gam.y, r.z * gam.z, r.w * gam.w));
-                    const float ss = warp_sum(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
-                    if (lane == 0) ep.ssq_out[(size_t)blockIdx.x * ep.ssq_stride + t] = ss;
-                } else if (mode == FT_EPI_QKV_ROPE) {
-                    const int d = d_, half = half_, q_dim = q_dim_, kv_dim = kv_dim_, i = i_;
-                    const int pos = pre_pos[u];
-                    float4 val = f4_mul(y, rs);
-                    if (region < 2) {
-                        // rotate_half partner (i +- d/2) sits half/4 lanes away in the same warp
-                        const float4 b = f4_shfl_xor(val, half >> 2);
-                        const float4 c = pre_c[u], s = pre_s[u];
-                        const float sg = i < half ? -1.f : 1.f;
-                        val = make_float4(val.x * c.x + sg * b.x * s.x, val.y * c.y + sg * b.y * s.y,
-                                          val.z * c.z + sg * b.z * s.z, val.w * c.w + sg * b.w * s.w);
-                    }
-                    uint2 h4;                       // q, K and V leave as saturating fp16 (attention dtype)
-                    h4.x = pack_f16_sat(val.x, val.y);
-                    h4.y = pack_f16_sat(val.z, val.w);
-                    if (region == 0) {
-                        *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ep.q_out) + (size_t)t * q_dim + row) = h4;
-                    } else {
-                        const int kvh = (row - q_dim - (region == 2 ? kv_dim : 0)) / d;
-                        const int page = pre_page[u];
-                        const int r = pos % kKvTile;
-                        uint8_t* slab = reinterpret_cast<uint8_t*>(ep.kv_layer) +
-                                        (((size_t)page * ep.nkv + kvh) * 2 + (region == 2 ? 1 : 0)) *
-                                            (size_t)(kKvTile * d * 2);
-                        const int off = r * (d * 2) + ((((i >> 3) ^ (r & 7))) << 4) + (i & 7) * 2;
-                        *reinterpret_cast<uint2*>(slab + off) = h4;
-                    }
-                } else if (mode == FT_EPI_SWIGLU) {
-                    // rows 0..63 of the tile are gate features, rows 64..127 the matching up features:
-                    // every lane finishes two features (all 32 lanes busy, no shuffles)
-                    const float2 g2 = *reinterpret_cast<const float2*>(stage_f + j * GEMM_BM + 2 * lane);
-                    const float2 u2 = *reinterpret_cast<const float2*>(stage_f + j * GEMM_BM + 64 + 2 * lane);
-                    const float a0 = silu(g2.x * rs) * (u2.x * rs), a1 = silu(g2.y * rs) * (u2.y * rs);
-                    const uint32_t h = pack_bf16(a0, a1);
-                    const size_t idx = (size_t)t * (n_out >> 1) + blockIdx.x * 64 + 2 * lane;
-                    *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + idx) = h;
-                    if (ep.out_lo)
-                        *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out_lo) + idx) =
-                            pack_bf16(a0 - bf16_lo(h), a1 - bf16_hi(h));
-                } else if (mode == FT_EPI_LOGITS) {
-                    const size_t idx = (size_t)t * (ep.out_stride ? ep.out_stride : n_out) + ep.out_col0 + row;
-                    const float4 lg = f4_mul(y, rs);
-                    *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + idx) = lg;
-                    if (ep.tp_peer_out) *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.tp_peer_out) + idx) = lg;
-                } else {   // FT_EPI_BF16
-                    store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
-                                 (size_t)t * n_out + row, f4_mul(y, rs));
-                }
-            }
-            }
-            if (reduce) {
-                // the last CTA of the row tile to finish re-arms the counters for the next launch
-                epi_bar_sync();
-                if (et == 0 && atomicAdd(cnt + 1, 1u) == (unsigned)n_split - 1) {
-                    cnt[0] = 0;
-                    cnt[1] = 0;
-                }
-            }
-        }
-        if (et == 0) trace(8);
+        if (threadIdx.x == 64) trace(6);
+        // the pipeline stages are idle once the MMAs retired: the staging tile aliases them
+        gemm_epilogue<BN, BN>(ep, c, tmem_base, reinterpret_cast<float*>(smem), rstd_s, 0);
+        if (threadIdx.x == 64) trace(8);
     }
 
     tc_fence_before();
@@ -478,6 +514,167 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
         tmem_dealloc(tmem_base, TMEM_COLS);
     }
     if (threadIdx.x == 0) trace(9);
+}
+
+// ------------------------------------------------------------------ persistent variant (multi-wave grids)
+// Grids with more tiles than SMs — the prefill projections (up to 8192 tiles) and the LM head (1002
+// row tiles) — run as one CTA per SM that walks tiles (row tiles fastest).  What the walk buys over
+// one CTA per tile: the TMA ring never drains between tiles, TMEM holds TWO accumulators so the MMAs
+// of tile i+1 run while the epilogue warps are still finishing tile i, and barriers / TMEM are set up
+// once.  The epilogue works on 64 token columns at a time through its own 32 KB staging buffer (the
+// ring is busy with the next tile), which leaves four 48 KB stages for 128-token tiles.  K is never
+// split here (every tile's epilogue is self-contained).
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_persistent_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x,
+                       const __grid_constant__ CUtensorMap map_x_lo, const __grid_constant__ ft_gemm_epilogue ep,
+                       int n_out, int T, int k_chunks, int stages) {
+    constexpr int CB = BN < 64 ? BN : 64;
+    constexpr int B_PLANE = BN * GEMM_BK * 2;
+    constexpr int STAGE_BYTES = GEMM_A_BYTES + 2 * B_PLANE;
+    constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    float* stage_f = reinterpret_cast<float*>(smem + (size_t)stages * STAGE_BYTES);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stage_f) + CB * GEMM_BM * 4);
+    uint64_t* empty_bar = full_bar + stages;
+    uint64_t* tmem_full_bar = empty_bar + stages;        // [2]
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;        // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+    float* rstd_s = reinterpret_cast<float*>(tmem_slot + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int n_row_tiles = n_out / GEMM_BM;
+    const int n_tok_tiles = (T + BN - 1) / BN;
+    const int n_tiles = n_row_tiles * n_tok_tiles;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_w);
+        tma_prefetch_desc(&map_x);
+        tma_prefetch_desc(&map_x_lo);
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&tmem_full_bar[a], 1);
+            mbar_init(&tmem_empty_bar[a], 1);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, TMEM_COLS);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        if (elect_one()) {
+            // several token tiles: W is the L2-resident set; one token tile (LM head): W streams once
+            const bool multi = n_tok_tiles > 1;
+            const uint64_t pol_w = multi ? policy_evict_last() : policy_evict_first();
+            const uint64_t pol_x = multi ? policy_evict_first() : policy_evict_last();
+            int it = 0;
+            bool waited = false;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int row0 = (tile % n_row_tiles) * GEMM_BM, t0 = (tile / n_row_tiles) * BN;
+                int i = 0;
+                if (!waited) {
+                    // weights do not depend on the previous kernel: request the first ring-full before the wait
+                    const int pre = k_chunks < stages ? k_chunks : stages;
+                    for (int j = 0; j < pre; ++j) {
+                        mbar_expect_tx(&full_bar[j], STAGE_BYTES);
+                        tma_tile_2d(smem + (size_t)j * STAGE_BYTES, &map_w, j * GEMM_BK, row0, &full_bar[j], pol_w);
+                    }
+                    pdl_wait();
+                    waited = true;
+                    for (int j = 0; j < pre; ++j) {
+                        uint8_t* bs = smem + (size_t)j * STAGE_BYTES + GEMM_A_BYTES;
+                        tma_tile_2d(bs, &map_x, j * GEMM_BK, t0, &full_bar[j], pol_x);
+                        tma_tile_2d(bs + B_PLANE, &map_x_lo, j * GEMM_BK, t0, &full_bar[j], pol_x);
+                    }
+                    i = pre;
+                    it = pre;
+                }
+                for (; i < k_chunks; ++i, ++it) {
+                    const int slot = it % stages;
+                    if (it >= stages) mbar_wait(&empty_bar[slot], ((it / stages) - 1) & 1);
+                    mbar_expect_tx(&full_bar[slot], STAGE_BYTES);
+                    uint8_t* st = smem + (size_t)slot * STAGE_BYTES;
+                    tma_tile_2d(st, &map_w, i * GEMM_BK, row0, &full_bar[slot], pol_w);
+                    tma_tile_2d(st + GEMM_A_BYTES, &map_x, i * GEMM_BK, t0, &full_bar[slot], pol_x);
+                    tma_tile_2d(st + GEMM_A_BYTES + B_PLANE, &map_x_lo, i * GEMM_BK, t0, &full_bar[slot], pol_x);
+                }
+            }
+            if (!waited) pdl_wait();
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN);
+            int ct = 0;
+            uint32_t use = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++use) {
+                const uint32_t acc = use & 1;
+                if (use >= 2) {                       // the epilogue must have emptied this accumulator
+                    mbar_wait(&tmem_empty_bar[acc], ((use >> 1) - 1) & 1);
+                    tc_fence_after();
+                }
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int i = 0; i < k_chunks; ++i, ++ct) {
+                    const int slot = ct % stages;
+                    mbar_wait(&full_bar[slot], (ct / stages) & 1);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + (size_t)slot * STAGE_BYTES);
+                    const uint64_t a_desc = umma_desc_k128(a_addr);
+                    const uint64_t b_desc = umma_desc_k128(a_addr + GEMM_A_BYTES);
+                    const uint64_t l_desc = umma_desc_k128(a_addr + GEMM_A_BYTES + B_PLANE);
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; ++k)
+                        umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (i | k) != 0);
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; ++k)
+                        umma_bf16(d_tmem, a_desc + 2 * k, l_desc + 2 * k, idesc, 1u);
+                    umma_commit(&empty_bar[slot]);
+                }
+                umma_commit(&tmem_full_bar[acc]);
+            }
+        }
+    } else {
+        const int et = threadIdx.x - 64;
+        pdl_wait();
+        uint32_t use = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++use) {
+            const uint32_t acc = use & 1;
+            EpiCtx c;
+            c.row_tile = tile % n_row_tiles; c.tok_tile = tile / n_row_tiles; c.split = 0; c.n_split = 1;
+            c.tile_id = tile; c.cta_linear = (unsigned)tile;
+            c.n_out = n_out; c.T = T; c.has_acc = true;
+            epilogue_rstd<BN>(ep, c, rstd_s);
+            mbar_wait(&tmem_full_bar[acc], (use >> 1) & 1);
+            tc_fence_after();
+            for (int col0 = 0; col0 < BN; col0 += CB) {
+                if (c.tok_tile * BN + col0 >= T) break;
+                gemm_epilogue<BN, CB>(ep, c, tmem_base + acc * BN, stage_f, rstd_s, col0);
+                tc_fence_before();
+                epi_bar_sync();                       // staging (and, after the last half, the accumulator) is free
+            }
+            if (et == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
 }
 
 // ------------------------------------------------------------------ host side
@@ -614,6 +811,44 @@ static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CU
     return 0;
 }
 
+template <int BN>
+static int launch_persistent_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap& mxl, int n_out,
+                                int T, int K, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream) {
+    constexpr int CB = BN < 64 ? BN : 64;
+    constexpr int STAGE_BYTES = GEMM_A_BYTES + 2 * BN * GEMM_BK * 2;
+    constexpr int STAGING = CB * GEMM_BM * 4;
+    const size_t fixed = 1024 + 256 + BN * 4 + STAGING;
+    int stages = (int)((227 * 1024 - fixed) / STAGE_BYTES);
+    if (stages > 12) stages = 12;
+    if (stages > K / GEMM_BK && K / GEMM_BK >= 2) stages = K / GEMM_BK;
+    FT_REQUIRE(stages >= 2, "gemm (persistent): no room for a two-stage ring");
+    const size_t smem = (size_t)stages * STAGE_BYTES + STAGING + 1024 + (2 * stages + 4) * 8 + 16 + BN * 4 + 16;
+    FT_REQUIRE(smem <= 227 * 1024, "gemm (persistent): %zu bytes of shared memory needed", smem);
+    static bool attr_set = false;
+    if (!attr_set) {
+        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_persistent_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           227 * 1024));
+        attr_set = true;
+    }
+    const int tiles = (n_out / GEMM_BM) * ((T + BN - 1) / BN);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(tiles < device_sms() ? tiles : device_sms());
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    int na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_persistent_kernel<BN>, mw, mx, mxl, epi, n_out, T, K / GEMM_BK, stages));
+    return 0;
+}
+
 size_t gemm_scratch_floats(int n_out, int T, int splits, bool hilo) {
     const int bn = gemm_pick_bn(T, hilo);
     return (size_t)(n_out / GEMM_BM) * ((T + bn - 1) / bn) * splits * bn * GEMM_BM;
@@ -652,6 +887,19 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
         FT_REQUIRE((epi.nq * epi.head_dim) % GEMM_BM == 0 && (epi.nkv * epi.head_dim) % GEMM_BM == 0 &&
                        n_out == (epi.nq + 2 * epi.nkv) * epi.head_dim,
                    "gemm: q / kv widths must be multiples of 128 and add up to n_out");
+    }
+    // more tiles than SMs, K unsplit: one persistent CTA per SM walks the tiles
+    static const bool no_persistent = getenv("FT_GEMM_NO_PERSISTENT") != nullptr;     // A/B switch (scripts/)
+    // (not for K > 4096: a 128-chunk mainloop hides nothing behind its epilogue, and the ring competing
+    //  with the overlapped epilogue's traffic ran the 1B down projection 1.2x slower than tile-per-CTA)
+    if (hilo && splits == 1 && mode != FT_EPI_PARTIAL && !no_persistent && K <= 4096 &&
+        (n_out / GEMM_BM) * ((T + bn - 1) / bn) > device_sms()) {
+        switch (bn) {
+            case 16: return launch_persistent_bn<16>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
+            case 32: return launch_persistent_bn<32>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
+            case 64: return launch_persistent_bn<64>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
+            case 128: return launch_persistent_bn<128>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
+        }
     }
 #define FT_GEMM_CASE(BN_)                                                                              \
     case BN_:                                                                                          \
