@@ -283,6 +283,18 @@ def run_native(args, rank, world, local_rank):
     e_steps = e1["steps"] - e0["steps"]
     e2e_value = world * n_out / e2e_s
 
+    # ---- cold TTFT: one 2048-token conversation nobody has cached, alone on the GPU
+    def ttft_once(key, toks):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        rid = eng.submit(key, toks, max_new_tokens=1, ignore_eos=True)
+        while True:
+            eng.step()
+            if any(r == rid and t >= 0 for r, t, fin in eng.drain()):
+                return 1e3 * (time.perf_counter() - t0)
+    cold = sorted(ttft_once(f"cold{j}", rand_tokens(1000 + j, CTX)) for j in range(5))
+    ttft_cold_ms = cold[len(cold) // 2]
+
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import cpu_baseline as cb
@@ -323,7 +335,8 @@ def run_native(args, rank, world, local_rank):
                     "ttft_ms_p50": 1e3 * pct(list(first.values()), 0.5), "ttft_ms_p99": 1e3 * pct(list(first.values()), 0.99),
                     "itl_ms_p50": 1e3 * pct(gaps, 0.5), "itl_ms_p99": 1e3 * pct(gaps, 0.99),
                     "prefix_hit_tokens": e1["prefix_hit_tokens"] - e0["prefix_hit_tokens"]},
-            "latency": {"itl_ms_p50_decode": ms / K},
+            "latency": {"itl_ms_p50_decode": ms / K, "ttft_ms_cold_2048_single": ttft_cold_ms,
+                        "ttft_ms_warm_p50_64_sessions": 1e3 * pct(list(first.values()), 0.5)},
             "gpu_launches": launches,
             "clocks": clk,
         }
