@@ -292,7 +292,8 @@ def run_native(args, rank, world, local_rank):
             eng.step()
             if any(r == rid and t >= 0 for r, t, fin in eng.drain()):
                 return 1e3 * (time.perf_counter() - t0)
-    cold = sorted(ttft_once(f"cold{j}", rand_tokens(1000 + j, CTX)) for j in range(5))
+    gcold = torch.Generator().manual_seed(99 + rank)
+    cold = sorted(ttft_once(f"cold{j}", torch.randint(0, 128000, (CTX,), generator=gcold).tolist()) for j in range(5))
     ttft_cold_ms = cold[len(cold) // 2]
 
     cpu_base = None
