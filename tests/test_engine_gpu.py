@@ -267,6 +267,53 @@ def test_llama1b_batched_decode_matches_oracle_logits(llama1b):
     assert worst < LOGIT_TOL
 
 
+def test_llama1b_config2_full_size_64_sessions_2k_history(llama1b):
+    """BASELINE config 2 at its full size — the shape bench.py times: 64 sessions, each with a
+    2048-token history, decoding together.  Checked sessions: the first decode-step logits (at
+    context 2048) against the fp32 oracle, the greedy continuation against the oracle's, and the
+    size-independent property that a session's tokens do not depend on its 63 neighbours."""
+    spec, w32, eng = llama1b
+    gen = torch.Generator().manual_seed(2048)
+    prompts = [torch.randint(0, 128000, (2048,), generator=gen) for _ in range(64)]
+    n_new = 80          # session 0 still decodes when session 63 joins: 64 rows decode together for 16 steps
+    rids = [eng.submit(f"full{i}", p.tolist(), max_new_tokens=n_new, ignore_eos=True) for i, p in enumerate(prompts)]
+    check = {rids[0]: 0, rids[31]: 31, rids[63]: 63}
+    toks = {r: [] for r in rids}
+    first_logits = {}
+    live = set(rids)
+    from fasttalk_llm_microservice_b200.native import NativeError
+    while live:
+        eng.step()
+        for r in check:
+            if r in live and len(toks[r]) == 1 and r not in first_logits:    # row of the first pure-decode step
+                try:
+                    first_logits[r] = eng.logits(r)
+                except NativeError:
+                    pass
+        for r, t, fin in eng.drain():
+            toks[r].append(t)
+            if fin:
+                live.discard(r)
+    assert all(len(v) == n_new for v in toks.values())
+    worst = 0.0
+    for r, i in check.items():
+        with torch.no_grad():
+            ref_tokens, ref_logits = O.greedy_generate(w32, spec, prompts[i], n_new, return_logits=True)
+        n_ok = assert_greedy_parity(f"1B cfg2 session {i}", toks[r], ref_tokens, ref_logits)
+        if n_ok >= 2 and r in first_logits:           # logits of decode step 1 (teacher-forced on an agreed token)
+            e = per_pos_rel(first_logits[r][None], ref_logits[1].cpu()[None])
+            worst = max(worst, e)
+            assert e < LOGIT_TOL, (i, e)
+        eng.close_session(f"full{i}")
+        solo = eng.generate([prompts[i].tolist()], max_new_tokens=n_new, ignore_eos=True)[0]
+        n_solo = assert_greedy_parity(f"1B cfg2 session {i} alone", solo, ref_tokens, ref_logits)
+        # alone or among 63 neighbours: the same tokens, up to the first near-tie of the oracle itself
+        assert solo[:min(n_ok, n_solo)] == toks[r][:min(n_ok, n_solo)]
+    print(f"\n[1B cfg2 full size] worst decode-step logit rel err at ctx 2049: {worst:.2e}")
+    for i in range(64):
+        eng.close_session(f"full{i}")
+
+
 # ------------------------------------------------------------------ the other named architectures
 @pytest.mark.parametrize("name,n_prompt,n_new", [("llama-3.2-3b", 96, 16), ("llama-3.1-8b", 70, 12)])
 def test_larger_configs_logits_and_greedy(name, n_prompt, n_new):
