@@ -125,9 +125,29 @@ sample_kernel(const float* __restrict__ logits, int V, const float* __restrict__
     // ---- max (+ argmax, lowest index on ties)
     float best = -INFINITY;
     int best_i = 0x7fffffff;
-    for (int i = threadIdx.x; i < V; i += SAMPLE_THREADS) {
-        const float v = x[i];
-        if (v > best) { best = v; best_i = i; }      // ascending i per thread: first max wins
+    if ((V & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+        // 16-byte loads, four in flight per thread: the row is 513 KB behind ONE CTA, so it is the
+        // number of outstanding loads, not arithmetic, that sets this pass's time
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        const int n4 = V >> 2;
+        auto take = [&](const float4& v, int i4) {      // ascending index order inside the thread
+            if (v.x > best) { best = v.x; best_i = 4 * i4; }
+            if (v.y > best) { best = v.y; best_i = 4 * i4 + 1; }
+            if (v.z > best) { best = v.z; best_i = 4 * i4 + 2; }
+            if (v.w > best) { best = v.w; best_i = 4 * i4 + 3; }
+        };
+        int i = threadIdx.x;
+        for (; i + 3 * SAMPLE_THREADS < n4; i += 4 * SAMPLE_THREADS) {
+            const float4 a = __ldcg(x4 + i), b4 = __ldcg(x4 + i + SAMPLE_THREADS),
+                         c4 = __ldcg(x4 + i + 2 * SAMPLE_THREADS), d4 = __ldcg(x4 + i + 3 * SAMPLE_THREADS);
+            take(a, i); take(b4, i + SAMPLE_THREADS); take(c4, i + 2 * SAMPLE_THREADS); take(d4, i + 3 * SAMPLE_THREADS);
+        }
+        for (; i < n4; i += SAMPLE_THREADS) take(__ldcg(x4 + i), i);
+    } else {
+        for (int i = threadIdx.x; i < V; i += SAMPLE_THREADS) {
+            const float v = x[i];
+            if (v > best) { best = v; best_i = i; }      // ascending i per thread: first max wins
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
