@@ -84,6 +84,7 @@ struct Engine {
     int ssq_parts = 0, rows_last = 0;
     float* gemm_scratch = nullptr; // split-K slabs of the fused-epilogue GEMMs (one wave of CTAs)
     int* gemm_sync = nullptr;      // their arrival counters
+    int sync_parity = 0;           // which word of each counter pair the next split-K launch uses
     // bf16 activations feeding the GEMMs are kept as hi + lo planes (see gemm.cu)
     void *xn = nullptr, *q = nullptr, *attn_out = nullptr, *act = nullptr, *xn_last = nullptr;
     void *xn_lo = nullptr, *attn_out_lo = nullptr, *act_lo = nullptr, *xn_last_lo = nullptr;
@@ -220,6 +221,11 @@ static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, 
     const int splits = staged ? gemm_pick_splits(n_out, T, K, e->sms, true) : 1;
     epi.scratch = e->gemm_scratch;
     epi.sync = e->gemm_sync;
+    if (staged && splits > 1) {              // launches are stream-ordered and each epilogue waits for its predecessor
+        epi.sync_mode = 1 + e->sync_parity;
+        epi.sync_slots = e->sms;
+        e->sync_parity ^= 1;
+    }
     if (e->tp > 1 && epi.mode == FT_EPI_RESID) {
         // row-parallel projection: the all-reduce over the two ranks happens inside the epilogue
         const unsigned epoch = ++e->tp_epoch;

@@ -27,6 +27,7 @@
 #include "ft_internal.h"
 
 #include <stdlib.h>
+#include <string.h>
 
 namespace ft {
 
@@ -57,11 +58,21 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
 // Always-on, nearly free timeline of CTA (0,0,0) of the most recent GEMM launch (globaltimer ns):
 // read back with ft_debug_gemm_trace (tuning aid, scripts/trace_gemm.py).
 __device__ unsigned long long g_gemm_trace[16];
-__device__ __forceinline__ void trace(int slot) {
-    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+// ... and of the last 256 launches (ft_debug_gemm_trace_hist): row = launch number mod 256.  Launches
+// overlap under PDL, so a launch's row index is fixed at entry and carried in shared memory.
+constexpr int GEMM_TRACE_HIST = 256;
+__device__ unsigned long long g_gemm_trace_hist[GEMM_TRACE_HIST * 16];
+__device__ unsigned int g_gemm_trace_n;
+__device__ __forceinline__ int trace_begin() {       // thread 0 of every CTA; returns -1 for untraced CTAs
+    if (blockIdx.x != 0 || blockIdx.y != 0 || blockIdx.z != 0) return -1;
+    return (int)(atomicAdd(&g_gemm_trace_n, 1u) % GEMM_TRACE_HIST);
+}
+__device__ __forceinline__ void trace(int slot, int base) {
+    if (base >= 0) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         g_gemm_trace[slot] = t;
+        g_gemm_trace_hist[base * 16 + slot] = t;
     }
 }
 
@@ -86,6 +97,23 @@ __device__ __forceinline__ void store_hi_lo4(__nv_bfloat16* hi, __nv_bfloat16* l
         *reinterpret_cast<uint2*>(lo + idx) = l;
     }
 }
+// explicit shared-memory loads: the staging / rstd pointers reach the epilogue as generic pointers, and
+// generic loads interleaved with global stores cost ~0.5 us per token row here (scripts/trace_decode_gemms.py)
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ float2 lds_f2(uint32_t a) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ float lds_f(uint32_t a) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+    return v;
+}
 __device__ __forceinline__ float silu(float g) { return __fdividef(g, 1.f + __expf(-g)); }
 
 // Where a CTA's output tile sits and how its K range was split (the stand-alone kernel takes these
@@ -93,8 +121,10 @@ __device__ __forceinline__ float silu(float g) { return __fdividef(g, 1.f + __ex
 struct EpiCtx {
     int row_tile, tok_tile, split, n_split, tile_id;
     unsigned cta_linear;     // arrival word of this CTA in the tensor-parallel exchange
+    unsigned n_ctas;         // CTAs of the launch (tiles x splits)
     int n_out, T;
     bool has_acc;            // false: K range empty, the tile is all zeros
+    int trace_base;          // row of the launch in the trace history, -1 = this CTA is not traced
 };
 
 // per-token 1/rms of the activation's source (RMSNorm deferred past the projection), all BN tokens of the tile
@@ -119,12 +149,12 @@ __device__ __forceinline__ void epilogue_rstd(const ft_gemm_epilogue& ep, const 
 // split-K rendezvous (CB == BN only), fused layer step.  stage_f: [CB][128] fp32 of shared memory
 // nobody else touches while this runs; rstd_s from epilogue_rstd; the caller has waited for the
 // accumulator (tmem_acc = its first column).
-template <int BN, int CB>
-__device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const EpiCtx& c, uint32_t tmem_acc,
-                                              float* stage_f, const float* rstd_s, int col0) {
+template <int BN, int CB, int MODE>
+__device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, const EpiCtx& c, uint32_t tmem_acc,
+                                                float* stage_f, const float* rstd_s, int col0) {
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int mode = ep.mode;
+    constexpr int mode = MODE;      // compile-time: the token loop carries no dispatch (see gemm_epilogue below)
     const int row0 = c.row_tile * GEMM_BM, t0 = c.tok_tile * BN;
     const int split = c.split, n_split = c.n_split, n_out = c.n_out, T = c.T;
     const int ew = warp - 2;                // 0..7
@@ -171,29 +201,39 @@ __device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const 
             }
         }
     }
-    if (et == 0) trace(7);
+    if (et == 0) trace(7, c.trace_base);
 
     if (mode != FT_EPI_PARTIAL) {
         // ---- phase 2: make the tile visible (CTA barrier, or split-K rendezvous in global memory)
+        // Arrival word of the row tile.  sync_mode 0: word 0 counts arrivals and re-arms itself (word 1 counts
+        // CTAs that are done; the last one zeroes both) — any launch order works.  sync_mode 1 / 2: launches that
+        // share the buffer alternate between word 0 and word 1 and every CTA zeroes the OTHER word on its way
+        // out of the rendezvous, which takes the returning atomic off the kernel's tail (engine).
         unsigned* cnt = reinterpret_cast<unsigned*>(ep.sync) + 2 * tile_id;
+        const int par = ep.sync_mode;
+        unsigned* arrive = par ? cnt + (par - 1) : cnt;
         if (reduce) {
-            __threadfence();
-            epi_bar_sync();
+            epi_bar_sync();                  // every warp's slab stores precede thread 0's release below
             if (et == 0) {
-                atomicAdd(cnt, 1u);
+                __threadfence();             // cumulative over the CTA (bar.sync above), as in attention.cu
+                atomicAdd(arrive, 1u);
                 unsigned spins = 0;
-                while (ld_acquire_u32(cnt) < (unsigned)n_split) {
+                while (ld_acquire_u32(arrive) < (unsigned)n_split) {
                     __nanosleep(32);
                     if (++spins > (1u << 25)) __trap();      // a peer never arrived: fail loudly, do not hang
                 }
+                if (par)                     // nobody looks at the other words during this launch: zero ALL of them,
+                    for (unsigned k = c.cta_linear; k < (unsigned)ep.sync_slots; k += c.n_ctas)   // not just this tile's
+                        reinterpret_cast<unsigned*>(ep.sync)[2 * k + (2 - par)] = 0;
             }
             epi_bar_sync();
-            __threadfence();
         } else {
             epi_bar_sync();
         }
 
         // ---- phase 3: one token per warp, four consecutive rows per lane
+        if (et == 0) trace(11, c.trace_base);      // rendezvous passed / tile staged: token loop starts
+        const uint32_t stage_a = smem_u32(stage_f), rstd_a = smem_u32(rstd_s);
         const int jbeg = reduce ? BN * split / n_split : col0;
         const int jend = reduce ? BN * (split + 1) / n_split : col0 + CB;
         const int r4 = 4 * lane;
@@ -216,7 +256,7 @@ __device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const 
                     y = __ldcg(src);
                     for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
                 } else {
-                    y = *reinterpret_cast<const float4*>(stage_f + (j - col0) * GEMM_BM + r4);
+                    y = lds_f4(stage_a + (uint32_t)((j - col0) * GEMM_BM + r4) * 4);
                 }
                 *reinterpret_cast<float4*>(ep.tp_peer_xchg + (size_t)t * n_out + row) = y;
             }
@@ -236,7 +276,7 @@ __device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const 
         // Tokens are taken four at a time per warp: the global operands of the batch (residual rows,
         // or position -> RoPE angles / KV page) are requested first, so a 128-token prefill tile pays
         // their latency 4 times per warp instead of 16 (ncu: the O projection spent 20 of 35 us here).
-        constexpr int U = 4;
+        constexpr int U = BN >= 128 ? 4 : 1;
         const bool is_resid = mode == FT_EPI_RESID, is_rope = mode == FT_EPI_QKV_ROPE;
         const int d_ = ep.head_dim, half_ = d_ >> 1;
         const int q_dim_ = ep.nq * d_, kv_dim_ = ep.nkv * d_;
@@ -279,9 +319,9 @@ __device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const 
                 y = __ldcg(src);
                 for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
             } else {
-                y = *reinterpret_cast<const float4*>(stage_f + (j - col0) * GEMM_BM + r4);
+                y = lds_f4(stage_a + (uint32_t)((j - col0) * GEMM_BM + r4) * 4);
             }
-            const float rs = rstd_s[j];
+            const float rs = lds_f(rstd_a + (uint32_t)j * 4);
             if (mode == FT_EPI_RESID) {
                 const size_t idx = (size_t)t * n_out + row;
                 if (tp) y = f4_add(y, __ldcg(reinterpret_cast<const float4*>(ep.tp_xchg + idx)));   // a + b == b + a
@@ -321,8 +361,8 @@ __device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const 
             } else if (mode == FT_EPI_SWIGLU) {
                 // rows 0..63 of the tile are gate features, rows 64..127 the matching up features:
                 // every lane finishes two features (all 32 lanes busy, no shuffles)
-                const float2 g2 = *reinterpret_cast<const float2*>(stage_f + (j - col0) * GEMM_BM + 2 * lane);
-                const float2 u2 = *reinterpret_cast<const float2*>(stage_f + (j - col0) * GEMM_BM + 64 + 2 * lane);
+                const float2 g2 = lds_f2(stage_a + (uint32_t)((j - col0) * GEMM_BM + 2 * lane) * 4);
+                const float2 u2 = lds_f2(stage_a + (uint32_t)((j - col0) * GEMM_BM + 64 + 2 * lane) * 4);
                 const float a0 = silu(g2.x * rs) * (u2.x * rs), a1 = silu(g2.y * rs) * (u2.y * rs);
                 const uint32_t h = pack_bf16(a0, a1);
                 const size_t idx = (size_t)t * (n_out >> 1) + c.row_tile * 64 + 2 * lane;
@@ -341,7 +381,7 @@ __device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const 
             }
         }
         }
-        if (reduce) {
+        if (reduce && !par) {
             // the last CTA of the row tile to finish re-arms the counters for the next launch
             epi_bar_sync();
             if (et == 0 && atomicAdd(cnt + 1, 1u) == (unsigned)n_split - 1) {
@@ -349,6 +389,23 @@ __device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const 
                 cnt[1] = 0;
             }
         }
+    }
+}
+
+// One specialised copy of the epilogue per mode, chosen once per tile: with the mode a run-time value
+// the token loop went through a jump table in constant memory on every row, and with ~0.7 KB of kernel
+// parameters re-read by uniform loads around it the loop ran at ~0.4 us per token row
+// (scripts/trace_decode_gemms.py: 3.4 us for 8 SwiGLU rows with no global access in them).
+template <int BN, int CB>
+__device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const EpiCtx& c, uint32_t tmem_acc,
+                                              float* stage_f, const float* rstd_s, int col0) {
+    switch (ep.mode) {
+        case FT_EPI_PARTIAL: gemm_epilogue_m<BN, CB, FT_EPI_PARTIAL>(ep, c, tmem_acc, stage_f, rstd_s, col0); break;
+        case FT_EPI_BF16: gemm_epilogue_m<BN, CB, FT_EPI_BF16>(ep, c, tmem_acc, stage_f, rstd_s, col0); break;
+        case FT_EPI_SWIGLU: gemm_epilogue_m<BN, CB, FT_EPI_SWIGLU>(ep, c, tmem_acc, stage_f, rstd_s, col0); break;
+        case FT_EPI_RESID: gemm_epilogue_m<BN, CB, FT_EPI_RESID>(ep, c, tmem_acc, stage_f, rstd_s, col0); break;
+        case FT_EPI_QKV_ROPE: gemm_epilogue_m<BN, CB, FT_EPI_QKV_ROPE>(ep, c, tmem_acc, stage_f, rstd_s, col0); break;
+        default: gemm_epilogue_m<BN, CB, FT_EPI_LOGITS>(ep, c, tmem_acc, stage_f, rstd_s, col0); break;
     }
 }
 
@@ -382,7 +439,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
     const int kc_begin = (int)(((long long)k_chunks * split) / n_split);
     const int kc_end = (int)(((long long)k_chunks * (split + 1)) / n_split);
     const int n_iter = kc_end - kc_begin;
-    if (threadIdx.x == 0) trace(0);
+    int& s_trace_base = *reinterpret_cast<int*>(tmem_slot + 1);     // spare word of the dynamic shared memory
+    if (threadIdx.x == 0) {
+        s_trace_base = trace_begin();
+        trace(0, s_trace_base);
+        if (s_trace_base >= 0) g_gemm_trace_hist[s_trace_base * 16 + 10] = ((unsigned long long)ep.mode << 32) | (unsigned)n_out;
+    }
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
@@ -403,7 +465,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    if (threadIdx.x == 0) trace(1);
+    if (threadIdx.x == 0) trace(1, s_trace_base);
 
     pdl_launch_dependents();
 
@@ -439,9 +501,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                     if (sz) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(base + off), "r"(sz) : "memory");
                 }
             }
-            trace(2);
+            trace(2, s_trace_base);
             pdl_wait();
-            trace(3);
+            trace(3, s_trace_base);
             for (int i = 0; i < pre; ++i) {
                 uint8_t* bs = smem + (size_t)i * STAGE_BYTES + GEMM_A_BYTES;
                 tma_tile_2d(bs, &map_x, (kc_begin + i) * GEMM_BK, t0, &full_bar[i], pol_x);
@@ -468,7 +530,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
             uint32_t ph = 0;
             for (int i = 0; i < n_iter; ++i) {
                 mbar_wait(&full_bar[s], ph);
-                if (i == 0) trace(4);
+                if (i == 0) trace(4, s_trace_base);
                 tc_fence_after();
                 const uint32_t a_addr = smem_u32(smem + (size_t)s * STAGE_BYTES);
                 const uint64_t a_desc = umma_desc_k128(a_addr);
@@ -485,7 +547,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                 umma_commit(&empty_bar[s]);               // frees the smem stage when MMAs retire
                 if (++s == stages) { s = 0; ph ^= 1; }
             }
-            trace(5);
+            trace(5, s_trace_base);
             umma_commit(tmem_full_bar);
         }
     } else {
@@ -495,16 +557,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
         c.row_tile = blockIdx.x; c.tok_tile = blockIdx.y; c.split = split; c.n_split = n_split;
         c.tile_id = blockIdx.y * gridDim.x + blockIdx.x;
         c.cta_linear = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-        c.n_out = n_out; c.T = T; c.has_acc = n_iter > 0;
+        c.n_ctas = gridDim.x * gridDim.y * gridDim.z;
+        c.n_out = n_out; c.T = T; c.has_acc = n_iter > 0; c.trace_base = s_trace_base;
         epilogue_rstd<BN>(ep, c, rstd_s);
         if (n_iter > 0) {
             mbar_wait(tmem_full_bar, 0);
             tc_fence_after();
         }
-        if (threadIdx.x == 64) trace(6);
+        if (threadIdx.x == 64) trace(6, s_trace_base);
         // the pipeline stages are idle once the MMAs retired: the staging tile aliases them
         gemm_epilogue<BN, BN>(ep, c, tmem_base, reinterpret_cast<float*>(smem), rstd_s, 0);
-        if (threadIdx.x == 64) trace(8);
+        if (threadIdx.x == 64) trace(8, s_trace_base);
     }
 
     tc_fence_before();
@@ -513,7 +576,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
         tc_fence_after();
         tmem_dealloc(tmem_base, TMEM_COLS);
     }
-    if (threadIdx.x == 0) trace(9);
+    if (threadIdx.x == 0) trace(9, s_trace_base);
 }
 
 // ------------------------------------------------------------------ persistent variant (multi-wave grids)
@@ -654,8 +717,8 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
             const uint32_t acc = use & 1;
             EpiCtx c;
             c.row_tile = tile % n_row_tiles; c.tok_tile = tile / n_row_tiles; c.split = 0; c.n_split = 1;
-            c.tile_id = tile; c.cta_linear = (unsigned)tile;
-            c.n_out = n_out; c.T = T; c.has_acc = true;
+            c.tile_id = tile; c.cta_linear = (unsigned)tile; c.n_ctas = (unsigned)n_tiles;
+            c.n_out = n_out; c.T = T; c.has_acc = true; c.trace_base = -1;
             epilogue_rstd<BN>(ep, c, rstd_s);
             mbar_wait(&tmem_full_bar[acc], (use >> 1) & 1);
             tc_fence_after();
@@ -873,6 +936,9 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
         FT_REQUIRE(ctas <= device_sms(), "gemm: %d CTAs do not fit one wave of %d SMs (split-K rendezvous)", ctas,
                    device_sms());
         FT_REQUIRE(epi.scratch && epi.sync, "gemm: split-K fused epilogues need scratch and sync buffers");
+        FT_REQUIRE(epi.sync_mode >= 0 && epi.sync_mode <= 2 &&
+                       (epi.sync_mode == 0 || epi.sync_slots >= (n_out / GEMM_BM) * ((T + bn - 1) / bn)),
+                   "gemm: sync_mode %d needs sync_slots covering the launch's tiles", epi.sync_mode);
     }
     FT_REQUIRE(!(hilo && bn > 128), "gemm: hi/lo activations support token tiles up to 128");
     if (epi.tp_peer_xchg)
@@ -956,6 +1022,20 @@ extern "C" int ft_debug_gemm_trace(unsigned long long* host_out16) {
     FT_CHECK_CUDA(cudaDeviceSynchronize());
     FT_CHECK_CUDA(cudaMemcpyFromSymbol(host_out16, ft::g_gemm_trace, sizeof(unsigned long long) * 16));
     return 0;
+}
+
+extern "C" int ft_debug_gemm_trace_hist(unsigned long long* host_out, int n_rows) {
+    FT_REQUIRE(host_out && n_rows >= 1 && n_rows <= ft::GEMM_TRACE_HIST, "ft_debug_gemm_trace_hist: bad arguments");
+    FT_CHECK_CUDA(cudaDeviceSynchronize());
+    unsigned int n = 0;
+    FT_CHECK_CUDA(cudaMemcpyFromSymbol(&n, ft::g_gemm_trace_n, sizeof(n)));
+    static unsigned long long all[ft::GEMM_TRACE_HIST * 16];
+    FT_CHECK_CUDA(cudaMemcpyFromSymbol(all, ft::g_gemm_trace_hist, sizeof(all)));
+    for (int i = 0; i < n_rows; ++i) {          // oldest first: the last n_rows launches
+        const unsigned row = (n - (unsigned)n_rows + (unsigned)i) % ft::GEMM_TRACE_HIST;
+        memcpy(host_out + (size_t)i * 16, all + (size_t)row * 16, 16 * sizeof(unsigned long long));
+    }
+    return (int)(n < (unsigned)n_rows ? n : (unsigned)n_rows);
 }
 
 extern "C" long long ft_gemm_scratch_bytes(int n_out, int T, int K, int n_splits) {

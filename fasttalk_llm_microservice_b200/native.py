@@ -64,7 +64,7 @@ class GemmEpilogue(C.Structure):
         ("prefetch", C.c_void_p), ("prefetch_bytes", C.c_longlong),
         ("tp_peer_xchg", C.c_void_p), ("tp_xchg", C.c_void_p), ("tp_peer_flags", C.c_void_p),
         ("tp_flags", C.c_void_p), ("tp_epoch", C.c_uint), ("tp_peer_out", C.c_void_p),
-        ("out_stride", C.c_int), ("out_col0", C.c_int),
+        ("out_stride", C.c_int), ("out_col0", C.c_int), ("sync_mode", C.c_int), ("sync_slots", C.c_int),
     ]
 
 
@@ -94,6 +94,7 @@ SIGNATURES = {
     "ft_gemm_bf16": (_I, [_VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
     "ft_gemm_pick_splits": (_I, [_I, _I, _I, _I]),
     "ft_debug_gemm_trace": (_I, [_VP]),
+    "ft_debug_gemm_trace_hist": (_I, [_VP, _I]),
     "ft_gemm_scratch_bytes": (_LL, [_I, _I, _I, _I]),
     "ft_gemm_fused": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, _VP, _VP]),
     "ft_embed_planes": (_I, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _VP]),

@@ -154,6 +154,9 @@ int ft_gemm_pick_splits(int n_out, int T, int K, int hilo);
  * uint64[16]: 0 entry, 1 set-up done, 2 weights requested, 3 dependency wait passed, 4 first stage
  * landed, 5 last MMA issued, 6 accumulator ready, 7 epilogue stores issued, 8 reduce done, 9 exit. */
 int ft_debug_gemm_trace(unsigned long long* host_out16);
+/* The same timeline for the last n_rows (<= 256) tile-per-CTA GEMM launches, oldest first -> HOST
+ * uint64 [n_rows][16]; word 10 of a row = (epilogue mode << 32) | n_out.  Returns rows filled. */
+int ft_debug_gemm_trace_hist(unsigned long long* host_out, int n_rows);
 
 /* K3 with the fused epilogues the engine uses.  RMSNorm is applied AFTER the projection: the
  * activation planes hold resid * gamma (un-normalised), the per-token 1/rms is a scalar that
@@ -210,6 +213,11 @@ typedef struct {
     unsigned tp_epoch;         /* RESID: value of this launch's arrivals; must grow launch over launch */
     void* tp_peer_out;         /* LOGITS: peer's logits buffer (same layout as out) or NULL */
     int out_stride, out_col0;  /* LOGITS: row stride / first column of out (0, 0 = n_out, 0) */
+    int sync_mode;             /* split-K arrival words: 0 = self re-arming (any launch order); 1 / 2 = this launch
+                                  counts on word 0 / 1 of each pair and zeroes word 1 / 0 of ALL sync_slots pairs —
+                                  launches sharing `sync` must alternate 1, 2, 1, ... and each must complete before
+                                  the next one's epilogue starts (stream order + the epilogue's dependency wait) */
+    int sync_slots;            /* sync_mode 1 / 2: counter pairs in `sync` */
 } ft_gemm_epilogue;
 long long ft_gemm_scratch_bytes(int n_out, int T, int K, int n_splits);
 int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int n_out, int T, int K, int n_splits,

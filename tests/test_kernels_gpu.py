@@ -446,3 +446,32 @@ def test_sample_full_vocab_row(K):
     for b in range(4):
         ref = O.sampling_support(logits[b].cpu(), 0.7, 0, 0.9)
         assert ref[tok[b].item()] > 0
+
+
+def test_gemm_split_k_alternating_arrival_words(K):
+    """ft_gemm_epilogue.sync_mode 1 / 2 (what the engine uses): launches that share one `sync` buffer alternate
+    between the two words of each counter pair and clear the other for ALL slots, whatever their tile counts —
+    a 24-tile launch, two 16-tile launches, 24 tiles again, ... must all match the self re-arming mode."""
+    from fasttalk_llm_microservice_b200 import native as N
+    g = torch.Generator(device=DEV).manual_seed(77)
+    T = 64
+    shapes = [(3072, 2048), (2048, 2048), (2048, 8192), (3072, 2048), (2048, 8192), (2048, 2048), (3072, 2048)]
+    sync = torch.zeros(2 * 148, device=DEV, dtype=torch.int32)
+    scratch = torch.empty(148 * 128 * 128, device=DEV, dtype=torch.float32)
+    par = 0
+    for rep, (n_out, Kd) in enumerate(shapes * 2):
+        w = (torch.randn(n_out, Kd, device=DEV, generator=g) * 0.05).bfloat16()
+        x, x_lo = K.split_hi_lo(torch.randn(T, Kd, device=DEV, generator=g))
+        gamma = (1 + 0.1 * torch.randn(n_out, device=DEV, generator=g)).bfloat16()
+        resid0 = torch.randn(T, n_out, device=DEV, generator=g)
+        outs = []
+        for mode in ("alt", "self"):
+            z = lambda: torch.zeros(T, n_out, device=DEV, dtype=torch.bfloat16)
+            o = dict(resid=resid0.clone(), out=z(), out_lo=z(), ssq_out=torch.zeros(n_out // 128, T, device=DEV))
+            extra = dict(sync=sync, scratch=scratch, sync_mode=1 + par, sync_slots=148) if mode == "alt" else {}
+            K.gemm_fused(w, x, x_lo, N.EPI_RESID, gamma=gamma, ssq_stride=T, **o, **extra)
+            torch.cuda.synchronize()
+            outs.append(o)
+        par ^= 1
+        for k in ("resid", "out", "out_lo", "ssq_out"):
+            assert torch.equal(outs[0][k], outs[1][k]), (rep, k)
