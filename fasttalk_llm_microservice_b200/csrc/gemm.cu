@@ -116,6 +116,25 @@ __device__ __forceinline__ float lds_f(uint32_t a) {
 }
 __device__ __forceinline__ float silu(float g) { return __fdividef(g, 1.f + __expf(-g)); }
 
+// Sum of one token row's four floats over the n_split partial slabs.  All loads of a group of eight are
+// issued before the first add: with a run-time trip count the compiler chained load -> add -> load, one L2
+// round trip per slab (a 6-way QKV split spent ~3 us here).
+template <int BN>
+__device__ __forceinline__ float4 sum_slabs(const float* first, int n_split) {
+    const float4* src = reinterpret_cast<const float4*>(first);
+    constexpr size_t STRIDE = (size_t)BN * GEMM_BM / 4;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int p0 = 0; p0 < n_split; p0 += 8) {
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            v[k] = p0 + k < n_split ? __ldcg(src + (size_t)(p0 + k) * STRIDE) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc = f4_add(acc, v[k]);     // fixed order: slab 0, 1, 2, ...
+    }
+    return acc;
+}
+
 // Where a CTA's output tile sits and how its K range was split (the stand-alone kernel takes these
 // from the block index, the persistent kernel from its tile loop).
 struct EpiCtx {
@@ -161,6 +180,50 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
     const int q = warp & 3;                 // TMEM lane quarter this warp may read (warp_id % 4)
     const int et = threadIdx.x - 64;        // 0..255
     const bool reduce = (mode == FT_EPI_RESID || mode == FT_EPI_QKV_ROPE) && n_split > 1;
+
+    // ---- this CTA's share of the tile's tokens, and the global operands of the first token batch: residual
+    // rows, or position -> RoPE angles / KV page.  They depend on nothing this launch computes, so they are
+    // requested BEFORE the accumulator is touched and their L2 latency hides behind phases 1 and 2 (1.5 us of
+    // the 3.4 us a QKV tile's token loop took, scripts/trace_decode_gemms.py).  Tokens are taken U at a time
+    // per warp; later batches are requested while the current one is being finished.
+    const int jbeg = reduce ? BN * split / n_split : col0;
+    const int jend = reduce ? BN * (split + 1) / n_split : col0 + CB;
+    const int r4 = 4 * lane;
+    const int row = row0 + r4;
+    constexpr int U = BN >= 128 ? 4 : 1;
+    constexpr bool is_resid = mode == FT_EPI_RESID, is_rope = mode == FT_EPI_QKV_ROPE;
+    const int d_ = ep.head_dim, half_ = d_ >> 1;
+    const int q_dim_ = ep.nq * d_, kv_dim_ = ep.nkv * d_;
+    const int region = row0 < q_dim_ ? 0 : row0 < q_dim_ + kv_dim_ ? 1 : 2;   // tile-uniform
+    const int i_ = is_rope ? row % d_ : 0;
+    float4 pre_r[U], pre_c[U], pre_s[U];
+    int pre_pos[U], pre_page[U];
+    auto prefetch = [&](int j0) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
+            pre_pos[u] = 0;
+            if (j < jend && t < T) {
+                if (is_resid) pre_r[u] = __ldcg(reinterpret_cast<const float4*>(ep.resid + (size_t)t * n_out + row));
+                if (is_rope) pre_pos[u] = ep.positions[t];
+            }
+        }
+        if (is_rope) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
+                if (j < jend && t < T) {
+                    if (region < 2) {
+                        pre_c[u] = *reinterpret_cast<const float4*>(ep.rope_cos + (size_t)pre_pos[u] * half_ + (i_ % half_));
+                        pre_s[u] = *reinterpret_cast<const float4*>(ep.rope_sin + (size_t)pre_pos[u] * half_ + (i_ % half_));
+                    }
+                    if (region > 0)
+                        pre_page[u] = ep.page_table[(size_t)ep.seq_rows[t] * ep.max_pages + pre_pos[u] / kKvTile];
+                }
+            }
+        }
+    };
+    if (mode != FT_EPI_PARTIAL) prefetch(jbeg + ew);
 
     // ---- phase 1: accumulator tile TMEM -> [token][row] staging
     const int tile_id = c.tile_id;
@@ -234,10 +297,6 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
         // ---- phase 3: one token per warp, four consecutive rows per lane
         if (et == 0) trace(11, c.trace_base);      // rendezvous passed / tile staged: token loop starts
         const uint32_t stage_a = smem_u32(stage_f), rstd_a = smem_u32(rstd_s);
-        const int jbeg = reduce ? BN * split / n_split : col0;
-        const int jend = reduce ? BN * (split + 1) / n_split : col0 + CB;
-        const int r4 = 4 * lane;
-        const int row = row0 + r4;
         float4 gam = make_float4(1.f, 1.f, 1.f, 1.f);
         if (mode == FT_EPI_RESID) {
             const uint2 gv = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(ep.gamma) + row);
@@ -252,9 +311,7 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 if (t >= T) break;
                 float4 y;
                 if (reduce) {
-                    const float4* src = reinterpret_cast<const float4*>(slabs + (size_t)j * GEMM_BM + r4);
-                    y = __ldcg(src);
-                    for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
+                    y = sum_slabs<BN>(slabs + (size_t)j * GEMM_BM + r4, n_split);
                 } else {
                     y = lds_f4(stage_a + (uint32_t)((j - col0) * GEMM_BM + r4) * 4);
                 }
@@ -273,41 +330,7 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
             }
             epi_bar_sync();
         }
-        // Tokens are taken four at a time per warp: the global operands of the batch (residual rows,
-        // or position -> RoPE angles / KV page) are requested first, so a 128-token prefill tile pays
-        // their latency 4 times per warp instead of 16 (ncu: the O projection spent 20 of 35 us here).
-        constexpr int U = BN >= 128 ? 4 : 1;
-        const bool is_resid = mode == FT_EPI_RESID, is_rope = mode == FT_EPI_QKV_ROPE;
-        const int d_ = ep.head_dim, half_ = d_ >> 1;
-        const int q_dim_ = ep.nq * d_, kv_dim_ = ep.nkv * d_;
-        const int region = row0 < q_dim_ ? 0 : row0 < q_dim_ + kv_dim_ ? 1 : 2;   // tile-uniform
-        const int i_ = is_rope ? row % d_ : 0;
         for (int j0 = jbeg + ew; j0 < jend; j0 += GEMM_EPI_WARPS * U) {
-            float4 pre_r[U], pre_c[U], pre_s[U];
-            int pre_pos[U], pre_page[U];
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
-                pre_pos[u] = 0;
-                if (j < jend && t < T) {
-                    if (is_resid) pre_r[u] = __ldcg(reinterpret_cast<const float4*>(ep.resid + (size_t)t * n_out + row));
-                    if (is_rope) pre_pos[u] = ep.positions[t];
-                }
-            }
-            if (is_rope) {
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
-                    if (j < jend && t < T) {
-                        if (region < 2) {
-                            pre_c[u] = *reinterpret_cast<const float4*>(ep.rope_cos + (size_t)pre_pos[u] * half_ + (i_ % half_));
-                            pre_s[u] = *reinterpret_cast<const float4*>(ep.rope_sin + (size_t)pre_pos[u] * half_ + (i_ % half_));
-                        }
-                        if (region > 0)
-                            pre_page[u] = ep.page_table[(size_t)ep.seq_rows[t] * ep.max_pages + pre_pos[u] / kKvTile];
-                    }
-                }
-            }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
             const int j = j0 + u * GEMM_EPI_WARPS;
@@ -315,9 +338,7 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
             if (j >= jend || t >= T) break;
             float4 y;
             if (reduce) {
-                const float4* src = reinterpret_cast<const float4*>(slabs + (size_t)j * GEMM_BM + r4);
-                y = __ldcg(src);
-                for (int p = 1; p < n_split; ++p) y = f4_add(y, __ldcg(src + (size_t)p * (BN * GEMM_BM / 4)));
+                y = sum_slabs<BN>(slabs + (size_t)j * GEMM_BM + r4, n_split);
             } else {
                 y = lds_f4(stage_a + (uint32_t)((j - col0) * GEMM_BM + r4) * 4);
             }
@@ -380,6 +401,7 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                              (size_t)t * n_out + row, f4_mul(y, rs));
             }
         }
+        if (j0 + GEMM_EPI_WARPS * U < jend) prefetch(j0 + GEMM_EPI_WARPS * U);
         }
         if (reduce && !par) {
             // the last CTA of the row tile to finish re-arms the counters for the next launch
