@@ -355,16 +355,33 @@ attn_decode_kernel(const __half* __restrict__ q, const uint8_t* __restrict__ kv_
                 __threadfence();
                 for (int e = threadIdx.x; e < G * D; e += ATTN_COMPUTE_WARPS * 32) {
                     const int hg = e / D, dim = e % D;
-                    float M = -INFINITY;
-                    for (int c = c_first; c <= c_last; ++c)
-                        M = fmaxf(M, __ldcg(scratch + ((size_t)(c + seg_idx) * ATTN_GMAX + hg) * C::REC + D));
-                    const float Mu = M == -INFINITY ? 0.f : M;
-                    float L = 0.f, O = 0.f;
-                    for (int c = c_first; c <= c_last; ++c) {
-                        const float* rec = scratch + ((size_t)(c + seg_idx) * ATTN_GMAX + hg) * C::REC;
-                        const float sc = exp2f(__ldcg(rec + D) - Mu);
-                        L += __ldcg(rec + D + 1) * sc;
-                        O += __ldcg(rec + dim) * sc;
+                    // all parts' (m, l, o) requested before the first is used: chained, a two-part merge
+                    // was four L2 round trips at the very end of the kernel
+                    float M = -INFINITY, L = 0.f, O = 0.f;
+                    for (int cb = c_first; cb <= c_last; cb += 4) {
+                        float pm[4], pl[4], po[4];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float* rec = scratch + ((size_t)(cb + k + seg_idx) * ATTN_GMAX + hg) * C::REC;
+                            const bool on = cb + k <= c_last;
+                            pm[k] = on ? __ldcg(rec + D) : -INFINITY;
+                            pl[k] = on ? __ldcg(rec + D + 1) : 0.f;
+                            po[k] = on ? __ldcg(rec + dim) : 0.f;
+                        }
+                        float Mn = M;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) Mn = fmaxf(Mn, pm[k]);
+                        const float Mu = Mn == -INFINITY ? 0.f : Mn;
+                        const float keep = exp2f(M - Mu);              // rescale what earlier groups of parts gave
+                        L *= keep;
+                        O *= keep;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float sc = exp2f(pm[k] - Mu);
+                            L += pl[k] * sc;
+                            O += po[k] * sc;
+                        }
+                        M = Mn;
                     }
                     const float r = O / L;
                     const __nv_bfloat16 hb = __float2bfloat16(r);
