@@ -317,14 +317,14 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 }
                 *reinterpret_cast<float4*>(ep.tp_peer_xchg + (size_t)t * n_out + row) = y;
             }
-            __threadfence_system();
-            epi_bar_sync();
+            epi_bar_sync();                  // every warp's peer stores precede thread 0's system-scope release
             if (et == 0) {
                 const unsigned cta = c.cta_linear;
+                __threadfence_system();      // cumulative over the CTA (bar.sync above)
                 st_release_sys_u32(ep.tp_peer_flags + cta, ep.tp_epoch);
                 unsigned spins = 0;
                 while ((int)(ld_acquire_sys_u32(ep.tp_flags + cta) - ep.tp_epoch) < 0) {
-                    __nanosleep(64);
+                    __nanosleep(32);
                     if (++spins > (1u << 25)) __trap();      // the peer GPU never ran this launch: fail loudly
                 }
             }
