@@ -855,7 +855,9 @@ static int stage_plan(int n_out, int T, int K, int splits, int* stages_out, size
     // decode-attention CTA (96 KB ring) become resident on the same SM while this launch is still running:
     // the attention after the QKV projection starts streaming KV early, the O projection after it loads its
     // weights before the attention's last CTAs leave (1.724 -> 1.702 ms per 64-session step).
-    if (per_cta <= 6 && stages > 2) stages = 2;
+    // (only when there is an attention worth overlapping: with a handful of rows the deep ring wins, it has all
+    //  of the CTA's chunks in flight at once)
+    if (per_cta <= 6 && T > 16 && stages > 2) stages = 2;
     if (stages < 2) stages = 2;
     // the epilogue parks a [BN][128] fp32 tile in the (idle) pipeline memory
     while ((size_t)stages * STAGE_BYTES < (size_t)BN * GEMM_BM * 4) ++stages;
