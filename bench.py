@@ -256,26 +256,30 @@ def run_native(args, rank, world, local_rank):
     e0 = eng.stats()
     barrier()
     t_start = time.perf_counter()
-    rid_of, first, last, gaps, n_out = {}, {}, {}, [], 0
+    import numpy as np
+    rids_t = []
     for i in range(SESSIONS):          # host token buffers in; the engine uploads what it needs
         full = base[i] + rand_tokens(i, TURN_NEW)
-        rid_of[eng.submit(f"t{i}", full, max_new_tokens=TURN_GEN, ignore_eos=True)] = i
-    live = set(rid_of)
-    while live:
+        rids_t.append(eng.submit(f"t{i}", full, max_new_tokens=TURN_GEN, ignore_eos=True))
+    rid0 = min(rids_t)
+    assert rids_t == list(range(rid0, rid0 + SESSIONS))
+    # per-request arrival stamps kept in arrays: the loop below is what a streaming host does per step
+    t_first = np.full(SESSIONS, -1.0)
+    t_last = np.zeros(SESSIONS)
+    gaps, n_out, n_live = [], 0, SESSIONS
+    while n_live:
         eng.step()
         now = time.perf_counter()
         n, rq, tk, fn = eng.drain_arrays()
-        for j in range(n):
-            r = int(rq[j])
-            if int(tk[j]) >= 0:
-                n_out += 1
-                if r in last:
-                    gaps.append(now - last[r])
-                else:
-                    first[r] = now - t_start
-                last[r] = now
-            if int(fn[j]):
-                live.discard(r)
+        idx = (rq[:n] - rid0).astype(np.int64)
+        got = idx[tk[:n] >= 0]
+        n_out += int(got.size)
+        seen = t_first[got] >= 0
+        gaps.extend((now - t_last[got[seen]]).tolist())
+        t_first[got[~seen]] = now - t_start
+        t_last[got] = now
+        n_live -= int(np.count_nonzero(fn[:n]))
+    first = {i: float(t_first[i]) for i in range(SESSIONS)}
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t_start
     e2e_s = max_over_ranks(e2e_s)

@@ -53,6 +53,9 @@ for i, e in enumerate(step):
     k[0] += 1; k[1] += d; k[2] += gap
     prev_end = max(prev_end, e.time_range.end)
 print(f"step span {step[-1].time_range.end - t0:.1f} us")
+if len(starts) >= 3:
+    gaps = [evs[starts[i + 1]].time_range.start - max(e.time_range.end for e in evs[starts[i]:starts[i + 1]]) for i in range(len(starts) - 1)]
+    print("GPU idle between steps (last kernel end -> next embed start), us:", [round(g, 1) for g in gaps])
 for n, (c, d, gp) in agg.items():
     print(f"{n:60s} n={c:3d} dur avg {d / c:7.2f}  gap-before avg {gp / c:6.2f}")
 eng.close()
