@@ -161,10 +161,72 @@ def cfg5():
     return res
 
 
+def _http_client_proc(port, n_streams, hist_chars, gen, q, tag):
+    """One client process: n_streams concurrent SSE streams, counts chunks without parsing JSON."""
+    import asyncio, httpx, time
+
+    async def one(i, hc, out):
+        body = {"model": "m", "stream": True, "temperature": 0.0, "max_tokens": gen,
+                "messages": [{"role": "system", "content": f"{tag}-{i:03d}"}, {"role": "user", "content": "h" * hist_chars}]}
+        t0 = time.perf_counter(); first = None; n = 0
+        async with hc.stream("POST", f"http://127.0.0.1:{port}/v1/chat/completions", json=body) as r:
+            async for line in r.aiter_lines():
+                if line.startswith("data: {") and '"content":"' in line and '"content":""' not in line:
+                    n += 1
+                    first = first or time.perf_counter() - t0
+        out.append((n, first, time.perf_counter() - t0))
+
+    async def main():
+        out = []
+        async with httpx.AsyncClient(timeout=600, limits=httpx.Limits(max_connections=n_streams + 4)) as hc:
+            await asyncio.gather(*[one(i, hc, out) for i in range(n_streams)])
+        return out
+    q.put(asyncio.run(main()))
+
+
+def cfg2_http():
+    """cfg 2 through boundary B: 64 concurrent SSE streams (4 client processes x 16) against ONE server process."""
+    import multiprocessing as mp, uvicorn
+    from fasttalk_llm_microservice_b200.handler import EngineRunner, NativeHandler
+    from fasttalk_llm_microservice_b200.openai_server import create_app
+    from fasttalk_llm_microservice_b200.tokenizer import ByteTokenizer
+    spec = get_spec("llama-3.2-1b")
+    eng = Engine(spec, init_weights(spec, seed=0, device="cuda"), EngineLimits(max_batch=64, max_batched_tokens=8192, max_context=4096), eos_ids=())
+    runner = EngineRunner(eng, ByteTokenizer(spec.vocab))
+    h = NativeHandler(model="llama3.2:1b", runner=runner)
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    server = uvicorn.Server(uvicorn.Config(create_app(h), host="127.0.0.1", port=port, log_level="error", lifespan="off"))
+    server.install_signal_handlers = lambda: None
+    th = threading.Thread(target=server.run, daemon=True); th.start()
+    while not server.started:
+        time.sleep(0.02)
+    ctx = mp.get_context("spawn")
+    res = {}
+    for tag, gen in (("warm", 8), ("run", 256)):          # first pass warms the server; histories differ per pass
+        q = ctx.Queue()
+        ps = [ctx.Process(target=_http_client_proc, args=(port, 16, 2000, gen, q, f"{tag}{k}")) for k in range(4)]
+        t0 = time.perf_counter()
+        for p_ in ps: p_.start()
+        rows = [r for _ in ps for r in q.get(timeout=600)]
+        for p_ in ps: p_.join()
+        wall = time.perf_counter() - t0
+        res[tag] = (rows, wall)
+    rows, wall = res["run"]
+    chunks = sum(r[0] for r in rows)
+    stream_s = max(r[2] for r in rows)
+    ttft = sorted(r[1] for r in rows)
+    out = {"config": "cfg2 over the OpenAI wire: llama-3.2-1b, 64 SSE streams (4 client processes), ~2k-token cold histories, 256 tokens each",
+           "chunks": chunks, "slowest_stream_s": stream_s, "tok_s_streamed": chunks / stream_s,
+           "ttft_ms_p50": 1e3 * ttft[len(ttft) // 2], "wall_incl_process_spawn_s": wall}
+    server.should_exit = True
+    th.join(timeout=5)
+    runner.shutdown(); eng.close()
+    return out
+
 if __name__ == "__main__":
     build.build()
     which = sys.argv[1:] or ["cfg1", "cfg3", "cfg5"]
     for name in which:
-        r = {"cfg1": cfg1, "cfg3": cfg3, "cfg5": cfg5}[name]()
+        r = {"cfg1": cfg1, "cfg3": cfg3, "cfg5": cfg5, "cfg2_http": cfg2_http}[name]()
         print("CFG " + json.dumps(r), flush=True)
         torch.cuda.empty_cache()
