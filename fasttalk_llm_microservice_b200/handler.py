@@ -63,6 +63,12 @@ class EngineRunner:
         self._stop = False
         self.last_step_time = time.time()
         self.error: Optional[BaseException] = None
+        # Detokenising and posting a step's tokens is Python work (a few hundred microseconds at 64 sessions);
+        # it runs on its own thread so that the engine thread is back inside ft_engine_step — which releases
+        # the GIL — right away, and the GPU does not idle while tokens are being delivered.
+        self._dq: "queue.SimpleQueue" = queue.SimpleQueue()
+        self._dthread = threading.Thread(target=self._dispatch_loop, name="fasttalk-b200-dispatch", daemon=True)
+        self._dthread.start()
         self._thread = threading.Thread(target=self._run, name="fasttalk-b200-engine", daemon=True)
         self._thread.start()
 
@@ -92,6 +98,18 @@ class EngineRunner:
         self._stop = True
         self._wake.set()
         self._thread.join(timeout=5)
+        self._dq.put(None)
+        self._dthread.join(timeout=5)
+
+    def _dispatch_loop(self):
+        while True:
+            events = self._dq.get()
+            if events is None:
+                return
+            try:
+                self._dispatch(events)
+            except Exception as e:  # noqa: BLE001 - a broken consumer must not stop delivery to the others
+                logger.error(f"token dispatch failed: {e}")
 
     # ---- engine thread
     def _run(self):
@@ -106,7 +124,8 @@ class EngineRunner:
                 produced = self.engine.step()
                 self.last_step_time = time.time()
                 events = self.engine.drain()
-                self._dispatch(events)
+                if events:
+                    self._dq.put(events)
                 if not produced and not events:
                     time.sleep(0.0005)          # waiting on admission / nothing runnable yet
         except BaseException as e:  # noqa: BLE001 - surface engine failures to every waiter
