@@ -64,7 +64,7 @@ class ModelSpec:
         return 2 * self.param_count()
 
     def kv_bytes_per_token(self) -> int:
-        """bf16 K+V bytes one cached token occupies over all layers."""
+        """16-bit (fp16 in the cache, bf16 in SURVEY.md §8d: same size) K+V bytes one cached token occupies over all layers."""
         return 2 * self.layers * self.n_kv_heads * self.head_dim * 2
 
     def decode_step_bytes(self, ctx_lens) -> int:

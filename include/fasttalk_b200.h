@@ -169,7 +169,7 @@ int ft_debug_gemm_trace_hist(unsigned long long* host_out, int n_rows);
  *                       of the tokens:
  *                       resid[t][n] += y;  out/out_lo[t][n] = hi/lo(resid * gamma[n]);
  *                       ssq_out[row_tile][t] = sum over the tile's 128 rows of resid^2
- *   FT_EPI_QKV_ROPE(4): same reduction, y *= rstd[t], RoPE on q and k rows, q -> q_out bf16
+ *   FT_EPI_QKV_ROPE(4): same reduction, y *= rstd[t], RoPE on q and k rows, q -> q_out
  *                       [T][nq*d] (fp16), k/v -> paged fp16 KV cache layer (layout of ft_rope_kv_append)
  *   FT_EPI_LOGITS  (5): out fp32 [T][n_out] = y * rstd[t]
  * rstd[t] = rsqrt(sum_p ssq_in[p * ssq_stride + t] * inv_h + eps).  x_lo is required. */
