@@ -201,6 +201,53 @@ def test_eos_stops():
     eng.close()
 
 
+def test_page_pressure_evicts_idle_sessions_lru_and_refuses_what_can_never_fit():
+    """KV pages run out: idle sessions' caches are given up least-recently-used first, running ones never; an
+    evicted conversation still gets the same answer when it comes back (cold again); a prompt larger than the
+    whole cache ends with finish reason "error" instead of stalling the queue."""
+    from fasttalk_llm_microservice_b200.model_spec import SPECS
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    spec = SPECS["tiny-d64"]
+    w = init_weights(spec, seed=4, std=0.08, norm_jitter=0.1)
+    eng = make_engine(spec, w, max_batch=4, max_batched_tokens=256, max_context=1024, num_pages=12, max_sessions=16)
+    big = make_engine(spec, w, max_batch=4, max_batched_tokens=256, max_context=1024)     # no pressure: the reference answers
+    try:
+        gen = torch.Generator().manual_seed(5)
+        prompts = {k: torch.randint(0, spec.vocab, (n,), generator=gen).tolist()
+                   for k, n in (("A", 200), ("B", 250), ("C", 190), ("D", 300))}
+        want = {k: big.generate([p], 6, sessions=[f"w{k}"])[0] for k, p in prompts.items()}
+        total = eng.stats()["total_pages"]
+        assert total == 12
+        assert eng.generate([prompts["A"]], 6, sessions=["A"])[0] == want["A"]        # 4 pages stay cached
+        assert eng.generate([prompts["B"]], 6, sessions=["B"])[0] == want["B"]        # 4 more
+        assert eng.stats()["free_pages"] == total - 8
+        hits = eng.stats()["prefix_hit_tokens"]
+        assert eng.generate([prompts["B"] + want["B"] + [7, 8, 9]], 4, sessions=["B"])    # B is now the most recent
+        assert eng.stats()["prefix_hit_tokens"] - hits >= 250
+        # B now holds 5 pages, A 4: C needs 4 of the 3 that are free -> A, the least recently used, goes
+        assert eng.generate([prompts["C"]], 6, sessions=["C"])[0] == want["C"]
+        assert eng.stats()["free_pages"] == total - 5 - 4          # B and C hold pages, A's are gone
+        # D needs 5 pages, 3 are free -> B goes (C was used after it)
+        assert eng.generate([prompts["D"]], 6, sessions=["D"])[0] == want["D"]
+        assert eng.stats()["free_pages"] == total - 4 - 5          # C and D
+        hits = eng.stats()["prefix_hit_tokens"]
+        assert eng.generate([prompts["A"]], 6, sessions=["A"])[0] == want["A"]        # cold again, same tokens
+        assert eng.stats()["prefix_hit_tokens"] == hits
+        # 13 pages worth of prompt can never fit 12 pages
+        rid = eng.submit("huge", torch.randint(0, spec.vocab, (800,), generator=gen).tolist(), max_new_tokens=4)
+        fins = []
+        for _ in range(50):
+            eng.step()
+            fins += [f for r, t, f in eng.drain() if r == rid and f]
+            if fins:
+                break
+        assert fins == ["error"]
+        assert eng.generate([prompts["C"]], 6, sessions=["C2"])[0] == want["C"]       # and the engine carries on
+    finally:
+        eng.close()
+        big.close()
+
+
 # ------------------------------------------------------------------ the named architecture
 @pytest.fixture(scope="module")
 def llama1b():
