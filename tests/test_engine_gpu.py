@@ -361,6 +361,40 @@ def test_llama1b_config2_full_size_64_sessions_2k_history(llama1b):
         eng.close_session(f"full{i}")
 
 
+def test_llama1b_long_context_8k_window():
+    """BASELINE config 4's window on the 1B weights: an 8300-token history (past the 8192 original RoPE range,
+    130 KV pages, chunked prefill in 8192-token steps), last-position logits and 8 greedy tokens vs the oracle."""
+    from fasttalk_llm_microservice_b200.model_spec import LLAMA_3_2_1B as spec
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    w = init_weights(spec, seed=1, device="cuda")
+    eng = make_engine(spec, w, max_batch=2, max_batched_tokens=8192, max_context=8448, debug_logit_rows=0)
+    try:
+        w32 = {k: v.float() for k, v in w.items() if k != "lm_head"}
+        w32["lm_head"] = w32["embed"]
+        prompt = torch.randint(0, 128000, (8300,), generator=torch.Generator().manual_seed(8))
+        with torch.no_grad():
+            ref_tokens, ref_logits = O.greedy_generate(w32, spec, prompt, 8, return_logits=True)
+        rid = eng.submit("long", prompt.tolist(), max_new_tokens=8, ignore_eos=True)
+        out, first = [], None
+        while len(out) < 8:
+            eng.step()
+            if first is None and eng.stats()["last_prefill_tokens"] > 0:
+                try:
+                    first = eng.logits(rid)          # the step that finished the prompt: logits at position 8299
+                except Exception:
+                    pass
+            out += [t for r, t, f in eng.drain() if t >= 0]
+        assert first is not None
+        err = per_pos_rel(first[None], ref_logits[0].cpu()[None])
+        print(f"\n[1B ctx 8300] last-position logit rel err {err:.2e}")
+        assert err < LOGIT_TOL
+        assert_greedy_parity("1B ctx 8300", out, ref_tokens, ref_logits)
+    finally:
+        eng.close()
+        del w32, w
+        torch.cuda.empty_cache()
+
+
 # ------------------------------------------------------------------ the other named architectures
 @pytest.mark.parametrize("name,n_prompt,n_new", [("llama-3.2-3b", 96, 16), ("llama-3.1-8b", 70, 12)])
 def test_larger_configs_logits_and_greedy(name, n_prompt, n_new):
