@@ -72,6 +72,27 @@ def main():
     assert toks[0] == toks[1], "the two ranks sampled different tokens"
     st = eng.stats()
     dist.barrier()
+    # ---- the serving arrangement: rank 0 drives through TPLeader, rank 1 only replays (tp.follower_loop)
+    if rank == 0:
+        lead = tp.TPLeader(eng)
+        rids = [lead.submit(f"lead{i}", p, max_new_tokens=a.new, ignore_eos=True) for i, p in enumerate(prompts)]
+        got = {r: [] for r in rids}
+        live = set(rids)
+        lead.cancel(rids[1])                       # a cancel travels with the next step like everything else
+        while live:
+            lead.step()
+            for r, t, fin in lead.drain():
+                if t >= 0:
+                    got[r].append(t)
+                if fin:
+                    live.discard(r)
+        lead.shutdown()
+        assert got[rids[0]] == out[0] and got[rids[2]] == out[2], "leader/follower run differs from the lock-step run"
+        assert got[rids[1]] == []
+    else:
+        n_steps = tp.follower_loop(eng)
+        assert n_steps > 0
+    dist.barrier()
     if rank == 0:
         one = Engine(spec, w, lim, eos_ids=())
         same = one.generate(prompts, a.new)
