@@ -53,3 +53,15 @@ def test_engine_refuses_without_gpu():
     from fasttalk_llm_microservice_b200.model_spec import TINY_D64
     with pytest.raises(native.NativeError):
         Engine(TINY_D64, {})
+
+
+def test_header_is_plain_c():
+    """include/fasttalk_b200.h is the boundary a C / cgo / JNI host binds: it must compile as C99 on its own."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc on this box")
+    hdr = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "fasttalk_b200.h")
+    r = subprocess.run(["gcc", "-fsyntax-only", "-x", "c", "-std=c99", "-Wall", "-Werror", hdr],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
