@@ -65,3 +65,25 @@ def test_header_is_plain_c():
     r = subprocess.run(["gcc", "-fsyntax-only", "-x", "c", "-std=c99", "-Wall", "-Werror", hdr],
                        capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
+
+
+def test_a_c_host_links_and_runs(tmp_path):
+    """gcc + the header + the .so is all a compiled host needs; the ctypes struct mirrors have the C sizes."""
+    import ctypes as C
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc on this box")
+    build.build()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    libdir = os.path.dirname(native.LIB_PATH)
+    exe = str(tmp_path / "host")
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", os.path.join(root, "tests", "c_host", "host.c"),
+                        "-I", os.path.join(root, "include"), "-L", libdir, "-lfasttalk_b200",
+                        "-Wl,-rpath," + libdir, "-o", exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "C_HOST_OK" in r.stdout, r.stdout + r.stderr
+    sizes = dict(kv.split("=") for kv in r.stdout.split() if kv.startswith(("epilogue=", "config=")))
+    assert int(sizes["epilogue"]) == C.sizeof(native.GemmEpilogue)
+    assert int(sizes["config"]) == C.sizeof(native.EngineConfig)
