@@ -240,7 +240,7 @@ static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, 
     }
     e->st.kernel_launches++;
     return launch_gemm(mw, xmaps[bn_index(bn)], &xmaps_lo[bn_index(bn)], bn, n_out, T, K, splits, epi, e->pdl,
-                       e->stream);
+                       e->stream, &xmaps[bn_index(64)], &xmaps_lo[bn_index(64)]);
 }
 
 // The norm-deferred layer chain (5 kernels per layer):

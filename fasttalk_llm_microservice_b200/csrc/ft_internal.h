@@ -17,8 +17,10 @@ int gemm_pick_bn(int T, bool hilo);
 int gemm_pick_splits(int n_out, int T, int K, int num_sms, bool hilo);
 size_t gemm_scratch_floats(int n_out, int T, int splits, bool hilo);   // split-K slabs of one launch
 // Modes and fields: ft_gemm_epilogue in include/fasttalk_b200.h.
+// mx_half / mx_lo_half: the same activations with 64-row boxes (only used with bn == 128, for the CTA-pair kernel)
 int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap* mx_lo, int bn, int n_out,
-                int T, int K, int splits, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream);
+                int T, int K, int splits, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream,
+                const CUtensorMap* mx_half = nullptr, const CUtensorMap* mx_lo_half = nullptr);
 
 // ---- elementwise.cu
 int launch_add_rmsnorm(float* resid, const float* partials, int n_splits, size_t split_stride,

@@ -762,6 +762,152 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
     }
 }
 
+// ------------------------------------------------------------------ CTA-pair variant (cta_group::2) for prefill
+// Two SMs of a TPC form a cluster and issue ONE 256 x 128 MMA per step: each CTA holds its own 128 weight
+// rows (A) and only HALF of the 128-token activation tile (B, 64 tokens x hi/lo); the tensor core reads the
+// other half from the peer's shared memory.  Per flop that is half the activation traffic into each SM's
+// shared memory, 32 KB instead of 48 KB per stage (six stages instead of four), and one MMA issue stream for
+// two SMs.  Everything else is the persistent kernel: tile walk (here over row-tile PAIRS), two accumulators
+// per CTA, per-mode epilogue on the CTA's own 128 rows.  Barriers: TMA of both CTAs counts on the LEADER's
+// full barrier; tcgen05.commit multicasts "stage free" / "accumulator ready" to both; both epilogues report
+// "accumulator drained" to the leader.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x_half,
+                 const __grid_constant__ CUtensorMap map_x_lo_half, const __grid_constant__ ft_gemm_epilogue ep,
+                 int n_out, int T, int k_chunks, int stages) {
+    constexpr int BN = 128, HALF = 64, CB = 64;
+    constexpr int B_PLANE = HALF * GEMM_BK * 2;
+    constexpr int STAGE_BYTES = GEMM_A_BYTES + 2 * B_PLANE;          // per CTA
+    constexpr uint32_t TMEM_COLS = 2 * BN;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    float* stage_f = reinterpret_cast<float*>(smem + (size_t)stages * STAGE_BYTES);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(stage_f) + CB * GEMM_BM * 4);
+    uint64_t* empty_bar = full_bar + stages;
+    uint64_t* tmem_full_bar = empty_bar + stages;        // [2]
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;        // [2], the leader's copy counts both CTAs
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+    float* rstd_s = reinterpret_cast<float*>(tmem_slot + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const int n_row_pairs = n_out / (2 * GEMM_BM);
+    const int n_tok_tiles = (T + BN - 1) / BN;
+    const int n_work = n_row_pairs * n_tok_tiles;
+    const int cl = (int)cluster_id_x(), n_cl = (int)gridDim.x / 2;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_w);
+        tma_prefetch_desc(&map_x_half);
+        tma_prefetch_desc(&map_x_lo_half);
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&tmem_full_bar[a], 1);
+            mbar_init(&tmem_empty_bar[a], 2);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc_pair(tmem_slot, TMEM_COLS);
+        tmem_relinquish_pair();
+    }
+    tc_fence_before();
+    cluster_sync_all();                     // both CTAs' barriers and TMEM exist before anything crosses over
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        if (elect_one()) {
+            const bool multi = n_tok_tiles > 1;
+            const uint64_t pol_w = multi ? policy_evict_last() : policy_evict_first();
+            const uint64_t pol_x = multi ? policy_evict_first() : policy_evict_last();
+            pdl_wait();
+            int it = 0;
+            for (int w = cl; w < n_work; w += n_cl) {
+                const int row0 = (2 * (w % n_row_pairs) + rank) * GEMM_BM;
+                const int tok0 = (w / n_row_pairs) * BN + rank * HALF;       // this CTA's half of the token tile
+                for (int i = 0; i < k_chunks; ++i, ++it) {
+                    const int slot = it % stages;
+                    if (it >= stages) mbar_wait(&empty_bar[slot], ((it / stages) - 1) & 1);
+                    if (rank == 0) mbar_expect_tx(&full_bar[slot], 2 * STAGE_BYTES);      // both CTAs' bytes
+                    uint8_t* st = smem + (size_t)slot * STAGE_BYTES;
+                    tma_tile_2d_pair(st, &map_w, i * GEMM_BK, row0, &full_bar[slot], pol_w);
+                    tma_tile_2d_pair(st + GEMM_A_BYTES, &map_x_half, i * GEMM_BK, tok0, &full_bar[slot], pol_x);
+                    tma_tile_2d_pair(st + GEMM_A_BYTES + B_PLANE, &map_x_lo_half, i * GEMM_BK, tok0, &full_bar[slot],
+                                     pol_x);
+                }
+            }
+        }
+    } else if (warp == 1 && rank == 0) {
+        if (elect_one()) {
+            constexpr uint32_t idesc = umma_idesc_bf16(2 * GEMM_BM, BN);
+            int ct = 0;
+            uint32_t use = 0;
+            for (int w = cl; w < n_work; w += n_cl, ++use) {
+                const uint32_t acc = use & 1;
+                if (use >= 2) {
+                    mbar_wait(&tmem_empty_bar[acc], ((use >> 1) - 1) & 1);
+                    tc_fence_after();
+                }
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int i = 0; i < k_chunks; ++i, ++ct) {
+                    const int slot = ct % stages;
+                    mbar_wait(&full_bar[slot], (ct / stages) & 1);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + (size_t)slot * STAGE_BYTES);
+                    const uint64_t a_desc = umma_desc_k128(a_addr);
+                    const uint64_t b_desc = umma_desc_k128(a_addr + GEMM_A_BYTES);
+                    const uint64_t l_desc = umma_desc_k128(a_addr + GEMM_A_BYTES + B_PLANE);
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; ++k)
+                        umma_bf16_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (i | k) != 0);
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; ++k)
+                        umma_bf16_pair(d_tmem, a_desc + 2 * k, l_desc + 2 * k, idesc, 1u);
+                    umma_commit_pair(&empty_bar[slot]);
+                }
+                umma_commit_pair(&tmem_full_bar[acc]);
+            }
+        }
+    } else if (warp >= 2) {
+        const int et = threadIdx.x - 64;
+        pdl_wait();
+        uint32_t use = 0;
+        for (int w = cl; w < n_work; w += n_cl, ++use) {
+            const uint32_t acc = use & 1;
+            EpiCtx c;
+            c.row_tile = 2 * (w % n_row_pairs) + rank; c.tok_tile = w / n_row_pairs; c.split = 0; c.n_split = 1;
+            c.tile_id = c.tok_tile * (n_out / GEMM_BM) + c.row_tile; c.cta_linear = (unsigned)c.tile_id;
+            c.n_ctas = (unsigned)(n_work * 2);
+            c.n_out = n_out; c.T = T; c.has_acc = true; c.trace_base = -1;
+            epilogue_rstd<BN>(ep, c, rstd_s);
+            mbar_wait(&tmem_full_bar[acc], (use >> 1) & 1);
+            tc_fence_after();
+            for (int col0 = 0; col0 < BN; col0 += CB) {
+                if (c.tok_tile * BN + col0 >= T) break;
+                gemm_epilogue<BN, CB>(ep, c, tmem_base + acc * BN, stage_f, rstd_s, col0);
+                tc_fence_before();
+                epi_bar_sync();
+            }
+            if (et == 0) mbar_arrive_leader(&tmem_empty_bar[acc]);
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, TMEM_COLS);
+    }
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                     const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -941,13 +1087,60 @@ static int launch_persistent_bn(const CUtensorMap& mw, const CUtensorMap& mx, co
     return 0;
 }
 
+static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const CUtensorMap& mxl_half, int n_out, int T,
+                       int K, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream) {
+    constexpr int STAGE_BYTES = GEMM_A_BYTES + 2 * 64 * GEMM_BK * 2;
+    constexpr int STAGING = 64 * GEMM_BM * 4;
+    const size_t fixed = 1024 + 256 + 128 * 4 + STAGING;
+    int stages = (int)((227 * 1024 - fixed) / STAGE_BYTES);
+    if (stages > 8) stages = 8;
+    if (stages > K / GEMM_BK && K / GEMM_BK >= 2) stages = K / GEMM_BK;
+    const size_t smem = (size_t)stages * STAGE_BYTES + STAGING + 1024 + (2 * stages + 4) * 8 + 16 + 128 * 4 + 16;
+    FT_REQUIRE(smem <= 227 * 1024, "gemm (pair): %zu bytes of shared memory needed", smem);
+    static int max_clusters = 0;
+    if (!max_clusters) {
+        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        cudaLaunchConfig_t q = {};
+        q.gridDim = dim3(device_sms() & ~1);
+        q.blockDim = dim3(GEMM_THREADS);
+        q.dynamicSmemBytes = smem;
+        cudaLaunchAttribute qa[1];
+        qa[0].id = cudaLaunchAttributeClusterDimension;
+        qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+        q.attrs = qa;
+        q.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel, &q) != cudaSuccess || n <= 0) n = device_sms() / 2;
+        max_clusters = n;
+    }
+    const int n_work = (n_out / (2 * GEMM_BM)) * ((T + 127) / 128);
+    const int clusters = n_work < max_clusters ? n_work : max_clusters;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * clusters);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    int na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_pair_kernel, mw, mx_half, mxl_half, epi, n_out, T, K / GEMM_BK, stages));
+    return 0;
+}
+
 size_t gemm_scratch_floats(int n_out, int T, int splits, bool hilo) {
     const int bn = gemm_pick_bn(T, hilo);
     return (size_t)(n_out / GEMM_BM) * ((T + bn - 1) / bn) * splits * bn * GEMM_BM;
 }
 
 int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap* mx_lo, int bn, int n_out,
-                int T, int K, int splits, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream) {
+                int T, int K, int splits, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream,
+                const CUtensorMap* mx_half, const CUtensorMap* mx_lo_half) {
     FT_REQUIRE(n_out % GEMM_BM == 0, "gemm: n_out=%d must be a multiple of %d", n_out, GEMM_BM);
     FT_REQUIRE(K % GEMM_BK == 0, "gemm: K=%d must be a multiple of %d", K, GEMM_BK);
     FT_REQUIRE(T >= 1, "gemm: T=%d", T);
@@ -987,8 +1180,13 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
     static const bool no_persistent = getenv("FT_GEMM_NO_PERSISTENT") != nullptr;     // A/B switch (scripts/)
     // (not for K > 4096: a 128-chunk mainloop hides nothing behind its epilogue, and the ring competing
     //  with the overlapped epilogue's traffic ran the 1B down projection 1.2x slower than tile-per-CTA)
-    if (hilo && splits == 1 && mode != FT_EPI_PARTIAL && !no_persistent && K <= 4096 &&
-        (n_out / GEMM_BM) * ((T + bn - 1) / bn) > device_sms()) {
+    const bool multiwave = hilo && splits == 1 && mode != FT_EPI_PARTIAL && !no_persistent &&
+                           (n_out / GEMM_BM) * ((T + bn - 1) / bn) > device_sms();
+    // 128-token tiles with the 64-token maps at hand: CTA pairs (cta_group::2), two row tiles per MMA
+    static const bool no_pair = getenv("FT_GEMM_NO_PAIR") != nullptr;                 // A/B switch (scripts/)
+    if (multiwave && !no_pair && bn == 128 && mx_half && mx_lo_half && n_out % (2 * GEMM_BM) == 0)
+        return launch_pair(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream);
+    if (multiwave && K <= 4096) {
         switch (bn) {
             case 16: return launch_persistent_bn<16>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
             case 32: return launch_persistent_bn<32>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
@@ -1032,8 +1230,14 @@ extern "C" int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int
     if (int r = make_tmap_bf16_k64(&mx, x, T, K, bn)) return r;
     if (hilo)
         if (int r = make_tmap_bf16_k64(&mxl, x_lo, T, K, bn)) return r;
+    CUtensorMap mxh, mxlh;
+    const bool halves = hilo && bn == 128;
+    if (halves) {
+        if (int r = make_tmap_bf16_k64(&mxh, x, T, K, 64)) return r;
+        if (int r = make_tmap_bf16_k64(&mxlh, x_lo, T, K, 64)) return r;
+    }
     return launch_gemm(mw, mx, hilo ? &mxl : nullptr, bn, n_out, T, K, n_splits, *epi, false,
-                       static_cast<cudaStream_t>(stream));
+                       static_cast<cudaStream_t>(stream), halves ? &mxh : nullptr, halves ? &mxlh : nullptr);
 }
 
 extern "C" int ft_gemm_bf16(const void* w, const void* x, const void* x_lo, void* out, void* out_lo,

@@ -475,3 +475,39 @@ def test_gemm_split_k_alternating_arrival_words(K):
         par ^= 1
         for k in ("resid", "out", "out_lo", "ssq_out"):
             assert torch.equal(outs[0][k], outs[1][k]), (rep, k)
+
+
+def test_gemm_multiwave_prefill_shapes(K):
+    """More tiles than SMs (the prefill regime): the persistent / CTA-pair kernels against torch, 128-token
+    tiles with a ragged last one, RESID + SWIGLU + LOGITS epilogues."""
+    from fasttalk_llm_microservice_b200 import native as N
+    from fasttalk_llm_microservice_b200.weights import interleave_gate_up
+    g = torch.Generator(device=DEV).manual_seed(91)
+    T, h, f = 1100, 2048, 2048
+    x, x_lo = K.split_hi_lo(torch.randn(T, h, device=DEV, generator=g))
+    xf = hilo(x, x_lo)
+    ssq = torch.rand(h // 128, T, device=DEV, generator=g) * 128
+    rstd = torch.rsqrt(ssq.sum(0) / h + 1e-5)
+    rs = dict(ssq_in=ssq, ssq_parts=h // 128, ssq_stride=T, inv_h=1.0 / h, eps=1e-5)
+    # RESID: 16 row tiles x 9 token tiles
+    w = (torch.randn(h, h, device=DEV, generator=g) * 0.03).bfloat16()
+    gamma = (1 + 0.1 * torch.randn(h, device=DEV, generator=g)).bfloat16()
+    resid = torch.randn(T, h, device=DEV, generator=g)
+    ref = resid + xf @ w.float().T
+    out, out_lo = torch.zeros(T, h, device=DEV, dtype=torch.bfloat16), torch.zeros(T, h, device=DEV, dtype=torch.bfloat16)
+    so = torch.zeros(h // 128, T, device=DEV)
+    K.gemm_fused(w, x, x_lo, N.EPI_RESID, n_splits=1, resid=resid, gamma=gamma, out=out, out_lo=out_lo, ssq_out=so,
+                 ssq_stride=T)
+    torch.cuda.synchronize()
+    assert rel_err(resid, ref) < 1e-3 and rel_err(hilo(out, out_lo), ref * gamma.float()) < 1e-3
+    assert rel_err(so, (ref ** 2).reshape(T, h // 128, 128).sum(-1).T) < 2e-3
+    # SWIGLU: 32 row tiles x 9 token tiles
+    wgu = (torch.randn(2 * f, h, device=DEV, generator=g) * 0.03).bfloat16()
+    act, act_lo = torch.zeros(T, f, device=DEV, dtype=torch.bfloat16), torch.zeros(T, f, device=DEV, dtype=torch.bfloat16)
+    K.gemm_fused(interleave_gate_up(wgu), x, x_lo, N.EPI_SWIGLU, out=act, out_lo=act_lo, **rs)
+    assert rel_err(hilo(act, act_lo), O.swiglu((xf @ wgu.float().T) * rstd[:, None])) < 5e-4
+    # LOGITS: 40 row tiles x 9 token tiles
+    wl = (torch.randn(5120, h, device=DEV, generator=g) * 0.03).bfloat16()
+    logits = torch.zeros(T, 5120, device=DEV)
+    K.gemm_fused(wl, x, x_lo, N.EPI_LOGITS, out=logits, **rs)
+    assert rel_err(logits, (xf @ wl.float().T) * rstd[:, None]) < 1e-3
