@@ -771,11 +771,12 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 // per CTA, per-mode epilogue on the CTA's own 128 rows.  Barriers: TMA of both CTAs counts on the LEADER's
 // full barrier; tcgen05.commit multicasts "stage free" / "accumulator ready" to both; both epilogues report
 // "accumulator drained" to the leader.
+template <int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x_half,
                  const __grid_constant__ CUtensorMap map_x_lo_half, const __grid_constant__ ft_gemm_epilogue ep,
                  int n_out, int T, int k_chunks, int stages) {
-    constexpr int BN = 128, HALF = 64, CB = 64;
+    constexpr int HALF = BN / 2, CB = 64;      // BN = 128 or 256 tokens per tile, half of them in each CTA
     constexpr int B_PLANE = HALF * GEMM_BK * 2;
     constexpr int STAGE_BYTES = GEMM_A_BYTES + 2 * B_PLANE;          // per CTA
     constexpr uint32_t TMEM_COLS = 2 * BN;
@@ -1087,19 +1088,20 @@ static int launch_persistent_bn(const CUtensorMap& mw, const CUtensorMap& mx, co
     return 0;
 }
 
+template <int BN>
 static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const CUtensorMap& mxl_half, int n_out, int T,
                        int K, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream) {
-    constexpr int STAGE_BYTES = GEMM_A_BYTES + 2 * 64 * GEMM_BK * 2;
+    constexpr int STAGE_BYTES = GEMM_A_BYTES + 2 * (BN / 2) * GEMM_BK * 2;
     constexpr int STAGING = 64 * GEMM_BM * 4;
-    const size_t fixed = 1024 + 256 + 128 * 4 + STAGING;
+    const size_t fixed = 1024 + 256 + BN * 4 + STAGING;
     int stages = (int)((227 * 1024 - fixed) / STAGE_BYTES);
     if (stages > 8) stages = 8;
     if (stages > K / GEMM_BK && K / GEMM_BK >= 2) stages = K / GEMM_BK;
-    const size_t smem = (size_t)stages * STAGE_BYTES + STAGING + 1024 + (2 * stages + 4) * 8 + 16 + 128 * 4 + 16;
+    const size_t smem = (size_t)stages * STAGE_BYTES + STAGING + 1024 + (2 * stages + 4) * 8 + 16 + BN * 4 + 16;
     FT_REQUIRE(smem <= 227 * 1024, "gemm (pair): %zu bytes of shared memory needed", smem);
     static int max_clusters = 0;
     if (!max_clusters) {
-        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         cudaLaunchConfig_t q = {};
         q.gridDim = dim3(device_sms() & ~1);
         q.blockDim = dim3(GEMM_THREADS);
@@ -1110,10 +1112,10 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
         q.attrs = qa;
         q.numAttrs = 1;
         int n = 0;
-        if (cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel, &q) != cudaSuccess || n <= 0) n = device_sms() / 2;
+        if (cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel<BN>, &q) != cudaSuccess || n <= 0) n = device_sms() / 2;
         max_clusters = n;
     }
-    const int n_work = (n_out / (2 * GEMM_BM)) * ((T + 127) / 128);
+    const int n_work = (n_out / (2 * GEMM_BM)) * ((T + BN - 1) / BN);
     const int clusters = n_work < max_clusters ? n_work : max_clusters;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * clusters);
@@ -1129,7 +1131,7 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_pair_kernel, mw, mx_half, mxl_half, epi, n_out, T, K / GEMM_BK, stages));
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_pair_kernel<BN>, mw, mx_half, mxl_half, epi, n_out, T, K / GEMM_BK, stages));
     return 0;
 }
 
@@ -1184,8 +1186,16 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
                            (n_out / GEMM_BM) * ((T + bn - 1) / bn) > device_sms();
     // 128-token tiles with the 64-token maps at hand: CTA pairs (cta_group::2), two row tiles per MMA
     static const bool no_pair = getenv("FT_GEMM_NO_PAIR") != nullptr;                 // A/B switch (scripts/)
-    if (multiwave && !no_pair && bn == 128 && mx_half && mx_lo_half && n_out % (2 * GEMM_BM) == 0)
-        return launch_pair(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream);
+    if (multiwave && !no_pair && bn == 128 && mx_half && mx_lo_half && n_out % (2 * GEMM_BM) == 0) {
+        // 256-token tiles (each CTA holds 128 of them: the bn == 128 maps ARE the half maps) when there are enough tokens
+        // — the 256 x 256 MMA reads each weight tile once per 256 tokens (gate/up: 753 -> 706 us), but halves the
+        // number of work units: only when at least eight rounds of them remain per cluster (measured: with 3–5
+        // rounds the down and QKV projections lose more to the last, partly empty round than the shape gains)
+        const long long work256 = (long long)(n_out / (2 * GEMM_BM)) * ((T + 255) / 256);
+        if (work256 >= 8LL * (device_sms() / 2))
+            return launch_pair<256>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
+        return launch_pair<128>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream);
+    }
     if (multiwave && K <= 4096) {
         switch (bn) {
             case 16: return launch_persistent_bn<16>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
