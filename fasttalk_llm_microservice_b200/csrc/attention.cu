@@ -39,6 +39,16 @@ struct AttnCfg {
                                    (size_t)ATTN_COMPUTE_WARPS * ATTN_GMAX * REC * 4 + 128;
 };
 
+// Prefill attention is bound by its per-warp ldmatrix -> mma -> exp2 chains, not by the KV stream: a short ring
+// (64 KB at d = 64) and <= 136 registers let THREE CTAs share an SM (12 compute warps instead of 8).
+template <int D>
+struct PrefillCfg {
+    static constexpr int TILE_BYTES = AttnCfg<D>::TILE_BYTES;
+    static constexpr int SLAB_BYTES = AttnCfg<D>::SLAB_BYTES;
+    static constexpr int STAGES = D == 64 ? 4 : 3;     // d = 128 keeps two CTAs per SM (its rows need the registers)
+    static constexpr size_t SMEM = (size_t)STAGES * TILE_BYTES + 2 * STAGES * 8 + 128;
+};
+
 __device__ __forceinline__ void compute_bar_sync() {
     asm volatile("bar.sync 1, %0;" ::"n"(ATTN_COMPUTE_WARPS * 32) : "memory");
 }
@@ -401,14 +411,14 @@ attn_decode_kernel(const __half* __restrict__ q, const uint8_t* __restrict__ kv_
 // come from the paged cache (the chunk's own K/V were appended by rope_kv_append before), so a
 // cached prefix and the new tokens take the same path.
 template <int D>
-__global__ void __launch_bounds__(ATTN_THREADS)
+__global__ void __launch_bounds__(ATTN_THREADS, D == 64 ? 3 : 2)
 attn_prefill_kernel(const __half* __restrict__ q, const uint8_t* __restrict__ kv_layer,
                     const int* __restrict__ page_table, int max_pages,
                     const int* __restrict__ req_q_start, const int* __restrict__ req_slot,
                     const int* __restrict__ req_pos0, const int* __restrict__ tile_req,
                     const int* __restrict__ tile_q0, __nv_bfloat16* __restrict__ out,
                     __nv_bfloat16* __restrict__ out_lo, int nq, int nkv, float scale_log2) {
-    using C = AttnCfg<D>;
+    using C = PrefillCfg<D>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)C::STAGES * C::TILE_BYTES);
@@ -671,11 +681,13 @@ static int launch_attn_prefill_d(const void* q, const void* kv_layer, const int*
                                  const int* req_q_start, const int* req_slot, const int* req_pos0,
                                  const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo,
                                  int nq, int nkv, bool pdl, cudaStream_t stream) {
-    using C = AttnCfg<D>;
+    using C = PrefillCfg<D>;
     static bool attr_set = false;
     if (!attr_set) {
         FT_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)C::SMEM));
+        FT_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                           cudaSharedmemCarveoutMaxShared));
         attr_set = true;
     }
     const float scale_log2 = LOG2E / sqrtf((float)D);
