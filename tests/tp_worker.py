@@ -37,11 +37,14 @@ def main():
     spec = get_spec(a.model)
     tiny = spec.hidden <= 512
     w = init_weights(spec, seed=21, std=0.08 if tiny else 0.02, norm_jitter=0.1 if tiny else 0.0)   # CPU generator: same on both ranks
-    lim = EngineLimits(max_batch=8, max_batched_tokens=256, max_context=1024, debug_logit_rows=64)
+    # the named models also get one long prompt in a single step: > 148 tiles per projection, i.e. the CTA-pair
+    # kernel with the exchange in its epilogue
+    lim = EngineLimits(max_batch=8, max_batched_tokens=256 if tiny else 2048, max_context=1024 if tiny else 4096,
+                       debug_logit_rows=64)
     eng = Engine(spec, w, lim, eos_ids=(), tp_rank=rank, tp_size=2)
     tp.connect(eng)
     g = torch.Generator().manual_seed(5)
-    prompts = [torch.randint(0, spec.vocab, (n,), generator=g).tolist() for n in (40, 7, 130)]
+    prompts = [torch.randint(0, spec.vocab, (n,), generator=g).tolist() for n in ((40, 7, 130) if tiny else (40, 7, 130, 1500))]
 
     # ---- prefill logits vs the oracle, chunked (several exchanging launches per layer) and in one go
     wd = {k: v.cuda() for k, v in w.items()}
