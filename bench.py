@@ -59,45 +59,104 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
+    """SM clock and clock-event reasons sampled DURING the timed region.
+
+    In-process NVML (nvidia_ml_py) on a thread, one sample every 5 ms; the NVML calls release the GIL
+    and never touch the CUDA stream.  Round 1 spawned `nvidia-smi -lms 100` right before the timer:
+    the tool's start-up (driver attach, ~0.3 s of host and PCIe activity) overlapped the whole 40 ms
+    window of a 20-step run and only two samples ever landed.  start() is now called well before the
+    timed region; mark()/unmark() bracket the region so only samples taken inside it are reported.
+    Falls back to the nvidia-smi subprocess (also started early) when NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, index: int):
-        self.index, self.samples, self.proc = index, [], None
+    def __init__(self, index: int, period_s: float = 0.005):
+        self.index, self.period = index, period_s
+        self.samples = []               # (t, sm_mhz, max_mhz, [reasons], power_w)
+        self.proc, self.thread, self.run, self.how = None, None, False, None
+        self.t_in, self.t_out = None, None
+
+    def _physical_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if self.index < len(ids) and ids[self.index].isdigit():
+                return int(ids[self.index])
+        return self.index
 
     def start(self):
         try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self._physical_index())
+            mx = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            bits = [(nv.nvmlClocksEventReasonHwSlowdown, "hw_slowdown"),
+                    (nv.nvmlClocksEventReasonHwThermalSlowdown, "hw_thermal_slowdown"),
+                    (nv.nvmlClocksEventReasonSwThermalSlowdown, "sw_thermal_slowdown"),
+                    (nv.nvmlClocksEventReasonSwPowerCap, "sw_power_cap")]
+
+            def loop():
+                while self.run:
+                    try:
+                        sm = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                        r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                        pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                        self.samples.append((time.perf_counter(), sm, mx, [n for b, n in bits if r & b], pw))
+                    except Exception:
+                        pass
+                    time.sleep(self.period)
+            self.run, self.how = True, "nvml in-process, 5 ms period"
+            self.thread = threading.Thread(target=loop, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.run = False
+        try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index),
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                 str(self._physical_index()), "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.how = "nvidia-smi -lms 20 subprocess"
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
 
     def _read(self):
         for line in self.proc.stdout:
-            self.samples.append(line.strip())
-
-    def stop(self):
-        if self.proc:
-            time.sleep(0.15)
-            self.proc.terminate()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
-            f = [x.strip() for x in s.split(",")]
+            f = [x.strip() for x in line.split(",")]
             if len(f) < 6:
                 continue
             try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
+                self.samples.append((time.perf_counter(), float(f[0]), float(f[1]),
+                                     [n for n, v in zip(self.NAMES, f[2:6]) if v.lower().startswith("active")], None))
             except ValueError:
                 continue
-            for n, v in zip(names, f[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+
+    def mark(self):
+        self.t_in = time.perf_counter()
+
+    def unmark(self):
+        self.t_out = time.perf_counter()
+
+    def stop(self):
+        self.run = False
+        if self.thread:
+            self.thread.join(timeout=1.0)
+        if self.proc:
+            self.proc.terminate()
+        lo = self.t_in if self.t_in is not None else 0.0
+        hi = self.t_out if self.t_out is not None else float("inf")
+        inside = [x for x in self.samples if lo <= x[0] <= hi]
+        if not inside and self.samples and self.t_in is not None:      # window shorter than one period: nearest samples
+            mid = 0.5 * (lo + (hi if hi != float("inf") else lo))
+            inside = sorted(self.samples, key=lambda x: abs(x[0] - mid))[:2]
+        sm = [x[1] for x in inside]
+        reasons = sorted({r for x in inside for r in x[3]})
+        pw = [x[4] for x in inside if x[4] is not None]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_min_mhz": min(sm) if sm else None,
+                "sm_max_mhz": max(x[2] for x in inside) if inside else None, "reasons": reasons,
+                "samples": len(sm), "samples_total": len(self.samples), "power_w_max": max(pw) if pw else None,
+                "how": self.how}
 
 
 def pct(xs, q):
@@ -187,22 +246,39 @@ def run_native(args, rank, world, local_rank):
         eng.step()
     eng.drain()
 
+    # ---- settle: the set-up above prefilled 131k tokens on the tensor cores at the board's power limit; the
+    # power controller keeps SM clocks capped for a while afterwards.  Start the clock sampler here and give the
+    # board SETTLE_S of idle before the warm-up, so that the timed steps below run at the clocks a server that has
+    # been decoding for a while sees.  Nothing is timed here; warm-up and the timed region are as passed.
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    time.sleep(args.settle)
+
     # ---- value: K decode steps, CUDA events on the engine stream
     for _ in range(W):
         eng.step()
     eng.drain()
+    eng.step_times_ms()
     st0 = eng.stats()
-    clocks = ClockSampler(local_rank)
     barrier()
-    clocks.start()
+    clocks.mark()
     eng.timer_start()
     for _ in range(K):
         eng.step()
     ms = eng.timer_stop_ms()
+    clocks.unmark()
     barrier()
     clk = clocks.stop()
+    per_step = eng.step_times_ms()[-K:]
     st1 = eng.stats()
+    ms_rank = ms
     ms = max_over_ranks(ms)
+    rank_ms = None
+    if dist:
+        t = torch.zeros(world, device="cuda", dtype=torch.float64)
+        t[rank] = ms_rank / K
+        dist.all_reduce(t)
+        rank_ms = [round(float(x), 4) for x in t.tolist()]
     tokens = st1["decode_tokens"] - st0["decode_tokens"]
     assert tokens == SESSIONS * K, (tokens, SESSIONS, K)
     value = world * tokens / (ms * 1e-3)
@@ -212,6 +288,14 @@ def run_native(args, rank, world, local_rank):
     peak, peak_src = measured_peaks()
     step_achieved = step_bytes * K / (ms * 1e-3) / 1e9
     eng.drain()
+    step_stats = None
+    if per_step:
+        sp = sorted(per_step)
+        step_stats = {"min": sp[0], "median": sp[len(sp) // 2], "max": sp[-1], "sum": sum(per_step),
+                      "host_gap_ms_per_step": (ms_rank - sum(per_step)) / K,
+                      "first5": [round(x, 4) for x in per_step[:5]],
+                      "what": "device ms of each timed step (events around upload..sampled-token copy), rank 0; "
+                              "host_gap = (timed total - their sum) / K = GPU idle between steps"}
 
     # ---- roofline of the dominant kernel: second pass, events around every launch
     eng.set_profile(True)
@@ -344,6 +428,9 @@ def run_native(args, rank, world, local_rank):
                         "ttft_ms_warm_p50_64_sessions": 1e3 * pct(list(first.values()), 0.5)},
             "gpu_launches": launches,
             "clocks": clk,
+            "step_ms": step_stats,
+            "rank_ms_per_step": rank_ms,
+            "settle_s": args.settle,
         }
         print(json.dumps(line), flush=True)
     eng.close()
@@ -359,6 +446,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--settle", type=float, default=2.0,
+                    help="idle seconds between the set-up prefill and the warm-up (power-cap recovery; untimed)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

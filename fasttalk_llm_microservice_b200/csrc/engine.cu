@@ -123,7 +123,11 @@ struct Engine {
     int prof_used = 0;
     long long prof_ctx_sum = 0;            // sum of context lengths of the step's decode rows
     cudaEvent_t t0 = nullptr, t1 = nullptr;
+    // device time of every step (events on the engine stream around upload .. sampled-token copy)
+    cudaEvent_t s0 = nullptr, s1 = nullptr;
+    std::deque<float> step_gpu_ms;         // most recent kStepTimes steps, oldest first
 };
+constexpr size_t kStepTimes = 4096;
 
 constexpr int kTpFlags = 16384;        // >= CTAs of any exchanging GEMM launch; the last word is the step barrier
 
@@ -525,6 +529,7 @@ static int engine_step(Engine* e) {
     for (Request* r : pre) if (r->logits_row >= 0) put_sampling(r);
 
     e->prof_used = 0;
+    FT_CHECK_CUDA(cudaEventRecord(e->s0, e->stream));
     FT_TRY(upload_meta(e));
     FT_TRY(forward(e, b));
     if (b.n_logit_rows > 0) {
@@ -537,8 +542,16 @@ static int engine_step(Engine* e) {
         FT_CHECK_CUDA(cudaMemcpyAsync(h + m.o_sampled, m.d + m.o_sampled, b.n_logit_rows * sizeof(int),
                                       cudaMemcpyDeviceToHost, e->stream));
     }
+    FT_CHECK_CUDA(cudaEventRecord(e->s1, e->stream));
     FT_CHECK_CUDA(cudaStreamSynchronize(e->stream));
     e->st.d2h_bytes += (long long)b.n_logit_rows * sizeof(int);
+    {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e->s0, e->s1) == cudaSuccess) {
+            if (e->step_gpu_ms.size() >= kStepTimes) e->step_gpu_ms.pop_front();
+            e->step_gpu_ms.push_back(ms);
+        }
+    }
     for (int l = 0; l < e->prof_used; ++l) {
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, e->prof_ev[2 * l], e->prof_ev[2 * l + 1]) == cudaSuccess) {
@@ -722,6 +735,8 @@ static int engine_init(Engine* e) {
     for (auto& ev : e->prof_ev) FT_CHECK_CUDA(cudaEventCreate(&ev));
     FT_CHECK_CUDA(cudaEventCreate(&e->t0));
     FT_CHECK_CUDA(cudaEventCreate(&e->t1));
+    FT_CHECK_CUDA(cudaEventCreate(&e->s0));
+    FT_CHECK_CUDA(cudaEventCreate(&e->s1));
     e->free_pages.reserve(c.num_pages);
     for (int p = c.num_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
     e->st.total_pages = c.num_pages;
@@ -742,6 +757,8 @@ static void engine_free(Engine* e) {
     for (auto ev : e->prof_ev) if (ev) cudaEventDestroy(ev);
     if (e->t0) cudaEventDestroy(e->t0);
     if (e->t1) cudaEventDestroy(e->t1);
+    if (e->s0) cudaEventDestroy(e->s0);
+    if (e->s1) cudaEventDestroy(e->s1);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -956,6 +973,17 @@ extern "C" int ft_engine_timer(ft_engine* h, int stop, float* ms_out) {
     FT_CHECK_CUDA(cudaEventSynchronize(e->t1));
     FT_CHECK_CUDA(cudaEventElapsedTime(ms_out, e->t0, e->t1));
     return 0;
+}
+
+extern "C" int ft_engine_step_times(ft_engine* h, float* ms_out, int cap) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e && ms_out && cap >= 0, "ft_engine_step_times: bad arguments");
+    std::lock_guard<std::mutex> lk(e->mu);
+    while ((int)e->step_gpu_ms.size() > cap) e->step_gpu_ms.pop_front();
+    int n = 0;
+    for (float v : e->step_gpu_ms) ms_out[n++] = v;
+    e->step_gpu_ms.clear();
+    return n;
 }
 
 extern "C" int ft_engine_get_logits(ft_engine* h, long long req, float* host_out) {

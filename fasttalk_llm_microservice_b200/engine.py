@@ -165,6 +165,12 @@ class Engine:
         N.check(self.lib.ft_engine_timer(self._h, 1, C.byref(ms)), "ft_engine_timer")
         return float(ms.value)
 
+    def step_times_ms(self, cap: int = 4096) -> List[float]:
+        """Device time of each step since the last call (oldest first, the engine keeps 4096)."""
+        buf = np.empty(cap, dtype=np.float32)
+        n = N.check(self.lib.ft_engine_step_times(self._h, buf.ctypes.data, cap), "ft_engine_step_times")
+        return buf[:n].tolist()
+
     def set_profile(self, on: bool):
         N.check(self.lib.ft_engine_set_profile(self._h, int(on)), "ft_engine_set_profile")
 

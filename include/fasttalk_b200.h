@@ -128,6 +128,11 @@ int ft_engine_stats_get(ft_engine* e, ft_engine_stats* out);
  * the device time between the two.  With profiling on, every decode-attention launch is bracketed
  * by events and accumulated into ft_engine_stats (this breaks PDL overlap around that kernel). */
 int ft_engine_timer(ft_engine* e, int stop, float* ms_out);
+/* Device time (ms, CUDA events on the engine's stream: metadata upload .. sampled-token copy) of each
+ * of the most recent steps, oldest first, at most `cap` (the engine keeps 4096) -> HOST float array;
+ * returns how many were written and forgets them.  The difference between ft_engine_timer's total and
+ * their sum is the time the GPU waited for the host between steps. */
+int ft_engine_step_times(ft_engine* e, float* ms_out, int cap);
 int ft_engine_set_profile(ft_engine* e, int on);
 /* fp32 logits [vocab] of `req` from the most recent step it took part in -> HOST buffer. */
 int ft_engine_get_logits(ft_engine* e, long long req, float* host_out);
