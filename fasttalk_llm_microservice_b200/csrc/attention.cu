@@ -642,11 +642,11 @@ static int launch_attn_decode_d(const void* q, const void* kv_layer, const int* 
                                 float* scratch, int B, int nq, int nkv, int n_ctas, bool pdl,
                                 cudaStream_t stream, cudaEvent_t ev0, cudaEvent_t ev1, bool early) {
     using C = AttnCfg<D>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceFlag attr_set;
+    if (!attr_set.done()) {
         FT_CHECK_CUDA(cudaFuncSetAttribute(attn_decode_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)C::SMEM));
-        attr_set = true;
+        attr_set.mark();
     }
     const float scale_log2 = LOG2E / sqrtf((float)D);
     cudaLaunchConfig_t cfg;
@@ -682,13 +682,13 @@ static int launch_attn_prefill_d(const void* q, const void* kv_layer, const int*
                                  const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo,
                                  int nq, int nkv, bool pdl, cudaStream_t stream) {
     using C = PrefillCfg<D>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceFlag attr_set;
+    if (!attr_set.done()) {
         FT_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)C::SMEM));
         FT_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<D>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                            cudaSharedmemCarveoutMaxShared));
-        attr_set = true;
+        attr_set.mark();
     }
     const float scale_log2 = LOG2E / sqrtf((float)D);
     cudaLaunchConfig_t cfg;

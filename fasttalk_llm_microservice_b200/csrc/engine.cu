@@ -129,6 +129,25 @@ struct Engine {
 };
 constexpr size_t kStepTimes = 4096;
 
+// Every entry point that touches CUDA makes the engine's device current for its duration: the caller may be a
+// thread whose current device is another GPU (a fresh thread starts on device 0).
+struct DeviceGuard {
+    int prev = -1, dev;
+    explicit DeviceGuard(int d) : dev(d) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) cudaSetDevice(dev);
+    }
+    ~DeviceGuard() {
+        if (prev >= 0 && prev != dev) cudaSetDevice(prev);
+    }
+};
+// The split-K rendezvous and the tensor-parallel flag wait spin inside kernels and need every CTA of a launch
+// resident at once.  One engine alone on a GPU guarantees that (grids are sized to one wave); two engines in one
+// process on the SAME GPU (two models behind one server) could each hold part of the SMs and wait for CTAs that
+// can never be scheduled.  Steps are synchronous (they end with a stream synchronise), so serialising the steps
+// of engines that share a device removes the hazard without costing a lone engine anything.
+static std::mutex g_device_step_mu[kMaxDevices];
+
 constexpr int kTpFlags = 16384;        // >= CTAs of any exchanging GEMM launch; the last word is the step barrier
 
 // Step barrier between the two ranks before sampling: both halves of the logits are in place.
@@ -780,7 +799,10 @@ extern "C" ft_engine* ft_engine_create(const ft_engine_config* cfg, const ft_wei
 }
 
 extern "C" void ft_engine_destroy(ft_engine* h) {
-    if (h) engine_free(reinterpret_cast<Engine*>(h));
+    if (!h) return;
+    Engine* e = reinterpret_cast<Engine*>(h);
+    DeviceGuard dg(e->dev);
+    engine_free(e);
 }
 
 extern "C" long long ft_engine_submit(ft_engine* h, unsigned long long key, const int* tokens, int n,
@@ -838,6 +860,7 @@ extern "C" int ft_engine_tp_export(ft_engine* h, void** xchg, void** flags, void
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e && xchg && flags && logits, "ft_engine_tp_export: bad arguments");
     FT_REQUIRE(e->tp > 1, "ft_engine_tp_export: the engine was created without tensor parallelism");
+    DeviceGuard dg(e->dev);
     FT_CHECK_CUDA(cudaStreamSynchronize(e->stream));       // the arrival words are zeroed
     *xchg = e->tp_xchg;
     *flags = e->tp_flags;
@@ -884,6 +907,8 @@ extern "C" int ft_engine_step(ft_engine* h) {
     FT_REQUIRE(e, "ft_engine_step: null engine");
     FT_REQUIRE(e->tp == 1 || e->peer_xchg, "ft_engine_step: tensor-parallel engine has no peer attached");
     std::lock_guard<std::mutex> lk(e->mu);
+    std::lock_guard<std::mutex> dk(g_device_step_mu[e->dev % kMaxDevices]);
+    DeviceGuard dg(e->dev);
     return engine_step(e);
 }
 
@@ -964,6 +989,7 @@ extern "C" int ft_engine_timer(ft_engine* h, int stop, float* ms_out) {
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e, "ft_engine_timer: null engine");
     std::lock_guard<std::mutex> lk(e->mu);
+    DeviceGuard dg(e->dev);
     if (!stop) {
         FT_CHECK_CUDA(cudaEventRecord(e->t0, e->stream));
         return 0;
@@ -990,6 +1016,7 @@ extern "C" int ft_engine_get_logits(ft_engine* h, long long req, float* host_out
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e && host_out, "ft_engine_get_logits: bad arguments");
     std::lock_guard<std::mutex> lk(e->mu);
+    DeviceGuard dg(e->dev);
     auto it = e->requests.find(req);
     FT_REQUIRE(it != e->requests.end() && it->second->logits_row >= 0,
                "ft_engine_get_logits: request %lld has no logits from the last step", req);
@@ -1002,6 +1029,8 @@ extern "C" int ft_debug_prefill_logits(ft_engine* h, const int* tokens, int n, i
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e && tokens && host_out && n >= 1, "ft_debug_prefill_logits: bad arguments");
     std::lock_guard<std::mutex> lk(e->mu);
+    std::lock_guard<std::mutex> dk(g_device_step_mu[e->dev % kMaxDevices]);
+    DeviceGuard dg(e->dev);
     FT_REQUIRE(e->active.empty() && e->waiting.empty(), "ft_debug_prefill_logits: engine must be idle");
     FT_REQUIRE(chunk >= 1 && chunk <= e->logit_rows && chunk <= e->t_max,
                "ft_debug_prefill_logits: chunk %d exceeds debug_logit_rows %d / max_batched_tokens %d", chunk,

@@ -11,6 +11,25 @@ namespace ft {
 
 constexpr int GEMM_MAX_SPLITS = 16;
 
+// Per-device bookkeeping.  cudaFuncSetAttribute and the SM count belong to a DEVICE; a host may drive
+// several GPUs from one process (the C ABI allows it), so "done once" flags are kept per device ordinal.
+constexpr int kMaxDevices = 64;
+inline int current_device_slot() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0) d = 0;
+    return d % kMaxDevices;
+}
+// Usage: `if (!flag.done()) { ...set the attributes...; flag.mark(); }` — the flag is raised only AFTER the
+// set-up succeeded, so a second thread either sees it done or repeats the (idempotent) set-up itself.
+struct PerDeviceFlag {
+    volatile unsigned char flags[kMaxDevices] = {};
+    bool done() const { return flags[current_device_slot()] != 0; }
+    void mark() {
+        __sync_synchronize();
+        flags[current_device_slot()] = 1;
+    }
+};
+
 // ---- gemm.cu
 int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int box_rows);
 int gemm_pick_bn(int T, bool hilo);

@@ -945,15 +945,17 @@ int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int 
     return 0;
 }
 
-static int device_sms() {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
+static int device_sms() {          // of the CURRENT device
+    static int sms[kMaxDevices] = {};
+    const int slot = current_device_slot();
+    if (!sms[slot]) {
+        int dev = 0, n = 0;
         if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
-            sms = 148;
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+        sms[slot] = n;
     }
-    return sms;
+    return sms[slot];
 }
 
 // Token tile: with both activation planes a 256-token tile would leave only two pipeline
@@ -1020,8 +1022,8 @@ static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CU
     int stages = 0;
     size_t smem = 0;
     if (int r = stage_plan<BN, HILO>(n_out, T, K, splits, &stages, &smem)) return r;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceFlag attr_set;
+    if (!attr_set.done()) {
         FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, HILO>,
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         // without this the driver sizes the shared-memory carve-out for ONE CTA of a ~100 KB launch and
@@ -1029,7 +1031,7 @@ static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CU
         FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, HILO>,
                                            cudaFuncAttributePreferredSharedMemoryCarveout,
                                            cudaSharedmemCarveoutMaxShared));
-        attr_set = true;
+        attr_set.mark();
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(n_out / GEMM_BM, (T + BN - 1) / BN, splits);
@@ -1063,11 +1065,11 @@ static int launch_persistent_bn(const CUtensorMap& mw, const CUtensorMap& mx, co
     FT_REQUIRE(stages >= 2, "gemm (persistent): no room for a two-stage ring");
     const size_t smem = (size_t)stages * STAGE_BYTES + STAGING + 1024 + (2 * stages + 4) * 8 + 16 + BN * 4 + 16;
     FT_REQUIRE(smem <= 227 * 1024, "gemm (persistent): %zu bytes of shared memory needed", smem);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceFlag attr_set;
+    if (!attr_set.done()) {
         FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_persistent_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            227 * 1024));
-        attr_set = true;
+        attr_set.mark();
     }
     const int tiles = (n_out / GEMM_BM) * ((T + BN - 1) / BN);
     cudaLaunchConfig_t cfg = {};
@@ -1099,7 +1101,8 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
     if (stages > K / GEMM_BK && K / GEMM_BK >= 2) stages = K / GEMM_BK;
     const size_t smem = (size_t)stages * STAGE_BYTES + STAGING + 1024 + (2 * stages + 4) * 8 + 16 + BN * 4 + 16;
     FT_REQUIRE(smem <= 227 * 1024, "gemm (pair): %zu bytes of shared memory needed", smem);
-    static int max_clusters = 0;
+    static int max_clusters_dev[kMaxDevices] = {};
+    int& max_clusters = max_clusters_dev[current_device_slot()];
     if (!max_clusters) {
         FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         cudaLaunchConfig_t q = {};

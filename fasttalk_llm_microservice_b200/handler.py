@@ -114,6 +114,10 @@ class EngineRunner:
     # ---- engine thread
     def _run(self):
         try:
+            dev = getattr(self.engine, "device", None)
+            if dev is not None:                 # a fresh thread starts on device 0: make the engine's GPU current
+                import torch
+                torch.cuda.set_device(dev)
             while not self._stop:
                 with self._lock:
                     busy = bool(self._sinks)
@@ -223,7 +227,7 @@ def build_runner(model: str) -> EngineRunner:
                 w["lm_head"] = w["embed"]
         else:
             w = init_weights(spec, seed=_env_int("FASTTALK_SEED", 0), device=f"cuda:{dev}")
-    tok = load_tokenizer(spec.vocab, tok_path)
+    tok = load_tokenizer(spec.vocab, tok_path, require=bool(ckpt))
     lim = EngineLimits(max_batch=_env_int("FASTTALK_MAX_SESSIONS", 64),
                        max_batched_tokens=_env_int("FASTTALK_MAX_BATCHED_TOKENS", 8192),
                        max_context=_env_int("FASTTALK_MAX_CONTEXT", _env_int("DEFAULT_CONTEXT_WINDOW", 8192)))

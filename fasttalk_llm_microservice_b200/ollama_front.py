@@ -18,6 +18,7 @@ import json
 import time
 from typing import Any, AsyncGenerator, Dict, List
 
+from starlette.background import BackgroundTask
 from starlette.requests import Request
 from starlette.responses import JSONResponse, PlainTextResponse, StreamingResponse
 from starlette.routing import Route
@@ -34,6 +35,8 @@ def _now() -> str:
 
 
 def ollama_routes(handler, served: str, keys) -> List[Route]:
+    from .openai_server import _abandon      # close a generation + release its conversation key (idempotent)
+
     async def root(request: Request):
         ok = handler.check_connection()
         return PlainTextResponse("Ollama is running" if ok else "engine unavailable", status_code=200 if ok else 503)
@@ -90,6 +93,9 @@ def ollama_routes(handler, served: str, keys) -> List[Route]:
         except LLMServiceError as e:
             keys.release(key)
             return JSONResponse({"error": str(e)}, status_code=400)
+        except BaseException:               # client gone before the first token, or any other failure
+            await _abandon(agen, keys, key)
+            raise
         t_first = time.perf_counter_ns()
 
         def line(content: str, done: bool) -> bytes:
@@ -127,7 +133,8 @@ def ollama_routes(handler, served: str, keys) -> List[Route]:
             except LLMServiceError as e:
                 yield json.dumps({"error": str(e)}).encode() + b"\n"
 
-        return StreamingResponse(ndjson(), media_type="application/x-ndjson")
+        return StreamingResponse(ndjson(), media_type="application/x-ndjson",
+                                 background=BackgroundTask(_abandon, agen, keys, key))
 
     return [Route("/", root, methods=["GET", "HEAD"]), Route("/api/show", show, methods=["POST"]),
             Route("/api/tags", tags, methods=["GET"]), Route("/api/chat", chat, methods=["POST"])]

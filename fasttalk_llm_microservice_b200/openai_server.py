@@ -30,6 +30,7 @@ from typing import Any, AsyncGenerator, Dict, List, Optional
 
 from starlette.applications import Starlette
 from starlette.requests import Request
+from starlette.background import BackgroundTask
 from starlette.responses import JSONResponse, StreamingResponse
 from starlette.routing import Route
 
@@ -42,6 +43,15 @@ def _error(status: int, message: str, etype: str = "invalid_request_error", para
            code: Optional[str] = None) -> JSONResponse:
     return JSONResponse({"error": {"message": message, "type": etype, "param": param, "code": code}},
                         status_code=status)
+
+
+async def _abandon(agen, keys: "_SessionKeys", key: str) -> None:
+    """Close a generation and give its conversation key back (idempotent on both counts)."""
+    try:
+        await agen.aclose()
+    except BaseException:  # noqa: BLE001 - closing must not mask the error being propagated
+        pass
+    keys.release(key)
 
 
 class _SessionKeys:
@@ -160,6 +170,12 @@ def create_app(handler: NativeHandler, served_model: Optional[str] = None) -> St
             bad = e.category == ErrorCategory.VALIDATION
             return _error(400 if bad else 500, e.message if hasattr(e, "message") else str(e),
                           "invalid_request_error" if bad else "internal_error")
+        except BaseException:
+            # anything else — CancelledError when the client hangs up before the first token included —
+            # must not leave the conversation key marked busy (later turns would get base#1, base#2, ...
+            # and lose their KV prefix) nor the generation running
+            await _abandon(agen, keys, key)
+            raise
 
         async def events() -> AsyncGenerator[tuple, None]:
             """content / tool_call events of this completion, then ('end', finish_reason)."""
@@ -217,8 +233,11 @@ def create_app(handler: NativeHandler, served_model: Optional[str] = None) -> St
                 yield b"data: " + json.dumps({"error": {"message": str(e), "type": "internal_error"}}).encode() + b"\n\n"
             yield b"data: [DONE]\n\n"
 
+        # the background task runs after the response is over, also when the body was never iterated
+        # (client gone before the first byte): the generation is closed and the key released exactly once
         return StreamingResponse(sse(), media_type="text/event-stream",
-                                 headers={"Cache-Control": "no-cache", "X-Accel-Buffering": "no"})
+                                 headers={"Cache-Control": "no-cache", "X-Accel-Buffering": "no"},
+                                 background=BackgroundTask(_abandon, agen, keys, key))
 
     from .ollama_front import ollama_routes
     return Starlette(routes=[

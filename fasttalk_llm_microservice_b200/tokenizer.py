@@ -122,30 +122,49 @@ class HFTokenizer:
 
 
 class HFStreamDecoder:
-    """Decode the running id list and emit the new suffix once it no longer ends in an
-    incomplete UTF-8 sequence (U+FFFD)."""
+    """Incremental detokeniser: O(window) per token instead of re-decoding the whole reply.
+
+    Byte-level BPE pieces do not decode independently (a token may end inside a UTF-8 sequence, and
+    a leading-space rule may depend on the neighbour), so — as the vLLM / TGI detokenisers do — a
+    short window of already-emitted ids is decoded together with the new ones and only the text past
+    the window's own decoding is emitted: `prefix` = start of the window, `read` = ids already turned
+    into text.  Output is held back while the tail decodes to U+FFFD (an open UTF-8 sequence)."""
 
     def __init__(self, tok: HFTokenizer):
-        self.tok, self.ids, self.emitted = tok, [], 0
+        self.tok, self.ids, self.prefix, self.read = tok, [], 0, 0
+
+    def _emit(self, final: bool) -> str:
+        dec = self.tok.tk.decode
+        done = dec(self.ids[self.prefix:self.read], skip_special_tokens=True)
+        text = dec(self.ids[self.prefix:], skip_special_tokens=True)
+        if len(text) <= len(done) or (not final and text.endswith("\ufffd")):
+            return ""
+        self.prefix, self.read = self.read, len(self.ids)
+        if self.prefix > 64:                      # keep the id list short: drop what lies before the window
+            del self.ids[:self.prefix]
+            self.read -= self.prefix
+            self.prefix = 0
+        return text[len(done):]
 
     def push(self, t: int) -> str:
         if t in self.tok.specials:
             return ""
         self.ids.append(t)
-        text = self.tok.tk.decode(self.ids, skip_special_tokens=True)
-        if text.endswith("�"):
-            return ""
-        out, self.emitted = text[self.emitted:], len(text)
-        return out
+        return self._emit(False)
 
     def flush(self) -> str:
-        text = self.tok.tk.decode(self.ids, skip_special_tokens=True)
-        out, self.emitted = text[self.emitted:], len(text)
-        return out
+        return self._emit(True) if self.read < len(self.ids) else ""
 
 
-def load_tokenizer(vocab: int, path: Optional[str] = None):
+def load_tokenizer(vocab: int, path: Optional[str] = None, require: bool = False):
+    """`require`: a real checkpoint is being served — refuse to fall back to the byte tokenizer, whose ids
+    mean nothing to trained weights (set FASTTALK_ALLOW_BYTE_TOKENIZER=1 for random-init checkpoints)."""
     path = path or os.environ.get("FASTTALK_TOKENIZER_JSON")
     if path and os.path.exists(path):
         return HFTokenizer(path)
+    if require and os.environ.get("FASTTALK_ALLOW_BYTE_TOKENIZER", "0") != "1":
+        raise FileNotFoundError(
+            "a checkpoint was given but no tokenizer.json was found beside it (or in $FASTTALK_TOKENIZER_JSON); "
+            "serving it with the byte tokenizer would produce garbage text — set FASTTALK_ALLOW_BYTE_TOKENIZER=1 "
+            "to do that on purpose (random-init test checkpoints)")
     return ByteTokenizer(vocab)

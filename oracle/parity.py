@@ -111,7 +111,7 @@ def run(eng, jobs: Sequence[Job], max_steps: int = 100000, step=None, logits=Non
                 by_rid[j.rid] = j
 
 
-def finish(job: Job, min_exact_frac: float = 0.0) -> str:
+def finish(job: Job, min_exact_frac: float = 0.0, min_distinct: Optional[int] = None) -> str:
     """Assert the parity bar for one job and return (and record) its summary line."""
     n = job.n
     distinct = len(set(job.ref_tokens))
@@ -129,16 +129,16 @@ def finish(job: Job, min_exact_frac: float = 0.0) -> str:
         assert m <= limit, (f"{job.tag}: token {k} is {tok}, oracle {ref}, where the oracle's margin {m:.2e} of the "
                             f"logit scale is decisive (engine error measured {job.worst_err:.2e})")
     assert len(job.waived) <= WAIVERS_PER_64 * ((n + 63) // 64), f"{job.tag}: {len(job.waived)} near-ties in {n} tokens"
-    if n >= 8:
-        assert distinct >= n // 2, f"{job.tag}: oracle sequence degenerate ({distinct} distinct of {n})"
+    need = (n // 2 if n >= 8 else 0) if min_distinct is None else min_distinct
+    assert distinct >= need, f"{job.tag}: oracle sequence degenerate ({distinct} distinct of {n}, need {need})"
     assert job.exact >= min_exact_frac * n
     return line
 
 
 def check(eng, tag: str, session, prompt: Sequence[int], ref_tokens: Sequence[int], ref_logits: torch.Tensor,
-          **sampling) -> Job:
+          min_distinct: Optional[int] = None, **sampling) -> Job:
     """One sequence, alone in the engine: run, assert, report."""
     job = Job(tag, session, list(prompt), list(ref_tokens), ref_logits, sampling)
     run(eng, [job])
-    finish(job)
+    finish(job, min_distinct=min_distinct)
     return job

@@ -24,3 +24,16 @@ def pytest_collection_modifyitems(config, items):
     for it in items:
         if "gpu" in it.keywords:
             it.add_marker(skip)
+
+
+def pytest_terminal_summary(terminalreporter, exitstatus, config):
+    """One line per checked greedy sequence (oracle/parity.py) so the counts survive `-q`."""
+    try:
+        from oracle.parity import REPORT
+    except Exception:  # pragma: no cover
+        return
+    if REPORT:
+        terminalreporter.write_line("")
+        terminalreporter.write_line("greedy parity vs the fp32 oracle (teacher-forced, near-ties re-aligned):")
+        for line in REPORT:
+            terminalreporter.write_line("  " + line)

@@ -86,6 +86,16 @@ def test_real_tokenizer_json_streams_utf8(tmp_path):
     assert t[0] == tok.bos and t.count(tok.eot) == 2 and t.count(tok.start_header) == 3
     assert tok.decode(t) == "system\n\nbe briefuser\n\nhelloassistant\n\n"
     assert dec.push(tok.eot) == ""
+    # incremental: a long reply streams to exactly its full decoding, the decoder keeps only a short window of ids
+    # (re-decoding the whole reply per token was O(n^2) on the dispatch thread)
+    long_text = ("héllo wörld ✓ 你好 🙂 hello world, " * 60).strip()
+    ids = tok.encode(long_text)
+    dec = tok.stream_decoder()
+    out = "".join(dec.push(t) for t in ids) + dec.flush()
+    assert out == long_text and len(dec.ids) <= 80 and len(ids) > 600
+    # a checkpoint without a tokenizer.json is refused instead of silently served with the byte tokenizer
+    with pytest.raises(FileNotFoundError):
+        load_tokenizer(128256, None, require=True)
 
 
 def test_per_gpu_replica_commands_and_sticky_assignment():

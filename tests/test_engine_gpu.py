@@ -11,10 +11,11 @@ import pytest
 import torch
 
 from oracle import llama_oracle as O
+from oracle import parity as P
 
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
-LOGIT_TOL = 2e-2
+LOGIT_TOL = P.LOGIT_TOL
 
 
 def make_engine(spec, w, **kw):
@@ -38,25 +39,11 @@ def describe_err(tag, got, ref):
           f"L2-rel max {l2.max():.3e} mean {l2.mean():.3e}")
 
 
-def assert_greedy_parity(tag, out, ref_tokens, ref_logits):
-    """Greedy tokens must equal the fp32 oracle's.  Where they first differ, the oracle's own
-    top-1/top-2 margin must be inside the logit tolerance (a near-tie no bf16 path can
-    resolve) — anything else is a failure.  Tokens after a near-tie flip
-    follow a different history and are not compared."""
-    n = min(len(out), len(ref_tokens))
-    mism = [i for i in range(n) if out[i] != ref_tokens[i]]
-    print(f"\n[{tag}] greedy: {n} tokens, first mismatch {mism[0] if mism else None}, "
-          f"distinct oracle tokens {len(set(ref_tokens))}")
-    if not mism:
-        assert len(out) == len(ref_tokens)
-        return n
-    i = mism[0]
-    top2 = torch.topk(ref_logits[i], 2).values
-    margin = (top2[0] - top2[1]).item()
-    scale = ref_logits[i].abs().max().item()
-    print(f"[{tag}] step {i}: oracle margin {margin:.3e} = {margin / scale:.3e} of max|logit| (tol {LOGIT_TOL})")
-    assert margin < LOGIT_TOL * scale, f"{tag}: token {i} differs where the oracle's margin is decisive"
-    return i
+def greedy_parity(eng, tag, prompt, ref_tokens, ref_logits, session=None):
+    """Greedy tokens vs the fp32 oracle's over ALL positions (oracle/parity.py): teacher-forced logits at
+    every step, a mismatch only where the oracle's margin is within 3x the measured logit error (floor
+    5e-4 of the logit scale), the engine re-aligned on the oracle's token afterwards, counts asserted."""
+    return P.check(eng, tag, session or f"parity-{tag}", list(prompt), list(ref_tokens), ref_logits.cpu())
 
 
 @pytest.fixture(scope="module", params=["tiny-d64", "tiny-d128"])
@@ -84,11 +71,10 @@ def test_prefill_logits_match_golden(tiny):
 def test_greedy_matches_golden(tiny):
     spec, w, g, eng = tiny
     n = len(g["greedy"])
-    out = eng.generate([g["prompt"].tolist()], max_new_tokens=n, ignore_eos=True)[0]
     with torch.no_grad():
         ref_tokens, ref_logits = O.greedy_generate(w, spec, torch.from_numpy(g["prompt"]), n, return_logits=True)
     assert ref_tokens == g["greedy"].tolist()
-    assert_greedy_parity(spec.name, out, ref_tokens, ref_logits)
+    greedy_parity(eng, f"{spec.name} golden prompt", g["prompt"].tolist(), ref_tokens, ref_logits)
 
 
 def test_long_prompt_chunked_and_decode_logits(tiny):
@@ -99,20 +85,10 @@ def test_long_prompt_chunked_and_decode_logits(tiny):
     prompt = torch.randint(0, spec.vocab, (700,), generator=gen)
     with torch.no_grad():
         ref_tokens, ref_logits = O.greedy_generate(w, spec, prompt, 12, return_logits=True)
-    rid = eng.submit("long", prompt.tolist(), max_new_tokens=12, ignore_eos=True)
-    toks, logits = [], []
-    done = False
-    while not done:
-        if eng.step():
-            logits.append(eng.logits(rid))
-        for r, t, fin in eng.drain():
-            toks.append(t)
-            done = fin is not None
-    k = assert_greedy_parity(spec.name + " long", toks, ref_tokens, ref_logits)
-    got = torch.stack(logits[:k + 1]) if k < 12 else torch.stack(logits[:12])
-    describe_err(spec.name + " decode", got, ref_logits[:got.shape[0]])
-    assert per_pos_rel(got, ref_logits[:got.shape[0]]) < LOGIT_TOL
-    assert eng.stats()["prefill_tokens"] >= 700
+    pre0 = eng.stats()["prefill_tokens"]
+    job = greedy_parity(eng, spec.name + " 700-token prompt", prompt.tolist(), ref_tokens, ref_logits)
+    assert job.errs_checked >= 11 and job.worst_err < LOGIT_TOL
+    assert eng.stats()["prefill_tokens"] - pre0 >= 700
 
 
 def test_continuous_batching_equals_solo(tiny):
@@ -266,8 +242,9 @@ def test_llama1b_config1_greedy_and_logits(llama1b):
     """BASELINE config 1 shape: 128-token prompt, greedy decode, random-init Llama-3.2-1B.
     Teacher-forced logits over the prompt within 2e-2; the first 64 greedy tokens identical to
     the fp32 oracle's.  On random-init weights greedy argmax can hit near-ties:
-    a mismatch only counts as a failure if the oracle's top-1/top-2 margin at that step
-    exceeds the logit tolerance; the engine is then re-aligned to the oracle's token."""
+    a mismatch is waived only if the oracle's top-1/top-2 margin at that step is within 3x the logit error
+    measured in this very run; the engine is then re-aligned to the oracle's token and all 64 positions are
+    compared (oracle/parity.py)."""
     spec, w32, eng = llama1b
     gen = torch.Generator().manual_seed(1234)
     prompt = torch.randint(0, 128000, (128,), generator=gen)
@@ -278,8 +255,7 @@ def test_llama1b_config1_greedy_and_logits(llama1b):
     describe_err("1B cfg1 prefill", got_full, ref_full)
     err = per_pos_rel(got_full, ref_full)
     assert err < LOGIT_TOL, err
-    out = eng.generate([prompt.tolist()], max_new_tokens=64, ignore_eos=True)[0]
-    assert_greedy_parity("1B cfg1", out, ref_tokens, ref_logits)
+    greedy_parity(eng, "1B cfg1 (128-token prompt, 64 greedy)", prompt.tolist(), ref_tokens, ref_logits)
 
 
 def test_llama1b_batched_decode_matches_oracle_logits(llama1b):
@@ -315,50 +291,47 @@ def test_llama1b_batched_decode_matches_oracle_logits(llama1b):
 
 
 def test_llama1b_config2_full_size_64_sessions_2k_history(llama1b):
-    """BASELINE config 2 at its full size — the shape bench.py times: 64 sessions, each with a
-    2048-token history, decoding together.  Checked sessions: the first decode-step logits (at
-    context 2048) against the fp32 oracle, the greedy continuation against the oracle's, and the
-    size-independent property that a session's tokens do not depend on its 63 neighbours."""
+    """BASELINE config 2 at its full size — the shape bench.py times: 64 sessions, each with a 2048-token
+    history, decoding together for 64 steps.  The histories are prefilled first (turn 1), then all 64
+    sessions re-send them (conversation_manager.py:54-56): the prefix is served from the KV cache and the
+    64 rows decode in the same steps from the first token on.  Three of the sessions are checked against
+    the fp32 oracle at all 64 positions (teacher-forced logits at context 2048..2111, greedy tokens,
+    near-ties waived and re-aligned, oracle/parity.py); then each of them alone in the engine, which must
+    agree with its batched run wherever neither run met a near-tie."""
     spec, w32, eng = llama1b
     gen = torch.Generator().manual_seed(2048)
-    prompts = [torch.randint(0, 128000, (2048,), generator=gen) for _ in range(64)]
-    n_new = 80          # session 0 still decodes when session 63 joins: 64 rows decode together for 16 steps
-    rids = [eng.submit(f"full{i}", p.tolist(), max_new_tokens=n_new, ignore_eos=True) for i, p in enumerate(prompts)]
-    check = {rids[0]: 0, rids[31]: 31, rids[63]: 63}
-    toks = {r: [] for r in rids}
-    first_logits = {}
-    live = set(rids)
-    from fasttalk_llm_microservice_b200.native import NativeError
-    while live:
-        eng.step()
-        for r in check:
-            if r in live and len(toks[r]) == 1 and r not in first_logits:    # row of the first pure-decode step
-                try:
-                    first_logits[r] = eng.logits(r)
-                except NativeError:
-                    pass
-        for r, t, fin in eng.drain():
-            toks[r].append(t)
-            if fin:
-                live.discard(r)
-    assert all(len(v) == n_new for v in toks.values())
-    worst = 0.0
-    for r, i in check.items():
+    prompts = [torch.randint(0, 128000, (2048,), generator=gen).tolist() for _ in range(64)]
+    n_new = 64
+    eng.generate(prompts, max_new_tokens=1, sessions=[f"full{i}" for i in range(64)], ignore_eos=True)
+    checked = (0, 31, 63)
+    jobs = []
+    for i in checked:
         with torch.no_grad():
-            ref_tokens, ref_logits = O.greedy_generate(w32, spec, prompts[i], n_new, return_logits=True)
-        n_ok = assert_greedy_parity(f"1B cfg2 session {i}", toks[r], ref_tokens, ref_logits)
-        if n_ok >= 2 and r in first_logits:           # logits of decode step 1 (teacher-forced on an agreed token)
-            e = per_pos_rel(first_logits[r][None], ref_logits[1].cpu()[None])
-            worst = max(worst, e)
-            assert e < LOGIT_TOL, (i, e)
-        eng.close_session(f"full{i}")
-        solo = eng.generate([prompts[i].tolist()], max_new_tokens=n_new, ignore_eos=True)[0]
-        n_solo = assert_greedy_parity(f"1B cfg2 session {i} alone", solo, ref_tokens, ref_logits)
-        # alone or among 63 neighbours: the same tokens, up to the first near-tie of the oracle itself
-        assert solo[:min(n_ok, n_solo)] == toks[r][:min(n_ok, n_solo)]
-    print(f"\n[1B cfg2 full size] worst decode-step logit rel err at ctx 2049: {worst:.2e}")
+            ref_tokens, ref_logits = O.greedy_generate(w32, spec, torch.tensor(prompts[i]), n_new, return_logits=True)
+        jobs.append(P.Job(f"1B cfg2 session {i} among 64 at ctx 2048", f"full{i}", prompts[i], ref_tokens, ref_logits))
+    hits0, st0 = eng.stats()["prefix_hit_tokens"], eng.stats()
+    fillers = [eng.submit(f"full{i}", prompts[i], max_new_tokens=n_new + 8, ignore_eos=True)
+               for i in range(64) if i not in checked]
+    P.run(eng, jobs)
+    st1 = eng.stats()
+    assert st1["prefix_hit_tokens"] - hits0 >= 64 * 2047
+    # the 64 rows really decoded together: decode tokens per decode step over the checked span
+    rows_per_step = (st1["decode_tokens"] - st0["decode_tokens"]) / max(1, st1["decode_steps"] - st0["decode_steps"])
+    assert rows_per_step > 60, rows_per_step
+    for r in fillers:
+        eng.cancel(r)
+    eng.step(); eng.drain()
+    for j in jobs:
+        P.finish(j)
     for i in range(64):
         eng.close_session(f"full{i}")
+    for j, i in zip(jobs, checked):
+        solo = P.Job(f"1B cfg2 session {i} alone", f"solo{i}", prompts[i], j.ref_tokens, j.ref_logits)
+        P.run(eng, [solo])
+        P.finish(solo)
+        skip = {k for k, *_ in j.waived} | {k for k, *_ in solo.waived}
+        assert all(a == b for k, (a, b) in enumerate(zip(j.engine_tokens, solo.engine_tokens)) if k not in skip)
+        eng.close_session(f"solo{i}")
 
 
 def test_llama1b_long_context_8k_window():
@@ -374,21 +347,8 @@ def test_llama1b_long_context_8k_window():
         prompt = torch.randint(0, 128000, (8300,), generator=torch.Generator().manual_seed(8))
         with torch.no_grad():
             ref_tokens, ref_logits = O.greedy_generate(w32, spec, prompt, 8, return_logits=True)
-        rid = eng.submit("long", prompt.tolist(), max_new_tokens=8, ignore_eos=True)
-        out, first = [], None
-        while len(out) < 8:
-            eng.step()
-            if first is None and eng.stats()["last_prefill_tokens"] > 0:
-                try:
-                    first = eng.logits(rid)          # the step that finished the prompt: logits at position 8299
-                except Exception:
-                    pass
-            out += [t for r, t, f in eng.drain() if t >= 0]
-        assert first is not None
-        err = per_pos_rel(first[None], ref_logits[0].cpu()[None])
-        print(f"\n[1B ctx 8300] last-position logit rel err {err:.2e}")
-        assert err < LOGIT_TOL
-        assert_greedy_parity("1B ctx 8300", out, ref_tokens, ref_logits)
+        job = greedy_parity(eng, "1B ctx 8300 (8k window)", prompt.tolist(), ref_tokens, ref_logits)
+        assert job.errs_checked >= 7
     finally:
         eng.close()
         del w32, w
@@ -396,7 +356,7 @@ def test_llama1b_long_context_8k_window():
 
 
 # ------------------------------------------------------------------ the other named architectures
-@pytest.mark.parametrize("name,n_prompt,n_new", [("llama-3.2-3b", 96, 16), ("llama-3.1-8b", 70, 12)])
+@pytest.mark.parametrize("name,n_prompt,n_new", [("llama-3.2-3b", 96, 64), ("llama-3.1-8b", 70, 64)])
 def test_larger_configs_logits_and_greedy(name, n_prompt, n_new):
     """BASELINE configs 3-5 name Llama-3.2-3B (GQA group 3, head_dim 128) and Llama-3.1-8B (untied
     LM head, rope factor 8): same parity bar on random-init weights of those shapes."""
@@ -416,9 +376,73 @@ def test_larger_configs_logits_and_greedy(name, n_prompt, n_new):
         got = eng.debug_prefill_logits(prompt.tolist(), chunk=64)
         describe_err(f"{name} prefill", got, ref_full)
         assert per_pos_rel(got, ref_full) < LOGIT_TOL
-        out = eng.generate([prompt.tolist()], max_new_tokens=n_new, ignore_eos=True)[0]
-        assert_greedy_parity(name, out, ref_tokens, ref_logits)
+        greedy_parity(eng, f"{name} ({n_prompt}-token prompt, {n_new} greedy)", prompt.tolist(), ref_tokens, ref_logits)
     finally:
         eng.close()
         del w32, w
         torch.cuda.empty_cache()
+
+
+# ------------------------------------------------------------------ devices and threads
+def _tiny_setup():
+    from fasttalk_llm_microservice_b200.model_spec import SPECS
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    g = np.load(os.path.join(GOLD, "hf_tiny-d64.npz"))
+    spec = SPECS["tiny-d64"]
+    w = init_weights(spec, seed=int(g["seed"]), std=float(g["std"]), norm_jitter=float(g["norm_jitter"]))
+    return spec, w, g
+
+
+def test_two_engines_share_one_gpu_and_step_concurrently():
+    """Two models behind one process put two engines on the same GPU.  Their split-K rendezvous grids must never
+    interleave (each needs all its CTAs resident): steps of engines that share a device are serialised inside the
+    library.  Two threads hammer two engines at once; both must produce what they produce alone."""
+    import threading
+    spec, w, g = _tiny_setup()
+    prompts = [g["prompt"].tolist(), torch.randint(0, spec.vocab, (300,), generator=torch.Generator().manual_seed(3)).tolist()]
+    a, b = make_engine(spec, w), make_engine(spec, w)
+    try:
+        want = [a.generate([p], max_new_tokens=24, sessions=[f"w{i}"], ignore_eos=True)[0] for i, p in enumerate(prompts)]
+        got, errs = {}, []
+
+        def work(eng, name):
+            try:
+                for rep in range(6):
+                    got[(name, rep)] = [eng.generate([p], max_new_tokens=24, sessions=[f"{name}{rep}-{i}"], ignore_eos=True)[0]
+                                        for i, p in enumerate(prompts)]
+            except Exception as e:  # noqa: BLE001
+                errs.append(e)
+        ts = [threading.Thread(target=work, args=(a, "a")), threading.Thread(target=work, args=(b, "b"))]
+        [t.start() for t in ts]
+        [t.join(timeout=120) for t in ts]
+        assert not errs, errs
+        assert len(got) == 12 and all(v == want for v in got.values())
+    finally:
+        a.close()
+        b.close()
+
+
+def test_engine_stepped_from_a_fresh_thread():
+    """Every ft_engine_* entry makes the engine's device current itself: a thread that never called cudaSetDevice
+    (current device 0) can step an engine that lives on another GPU.  With one GPU the thread part still runs."""
+    import threading
+    from fasttalk_llm_microservice_b200.engine import Engine, EngineLimits
+    spec, w, g = _tiny_setup()
+    dev = torch.device("cuda", torch.cuda.device_count() - 1)        # the last GPU: != 0 whenever there are two
+    eng = Engine(spec, w, EngineLimits(max_batch=4, max_batched_tokens=128, max_context=512), eos_ids=(), device=dev)
+    torch.cuda.set_device(0)
+    try:
+        out = {}
+
+        def work():
+            out["tokens"] = eng.generate([g["prompt"].tolist()], max_new_tokens=12, ignore_eos=True)[0]
+        t = threading.Thread(target=work)
+        t.start()
+        t.join(timeout=60)
+        with torch.no_grad():
+            ref = O.greedy_generate(w, spec, torch.from_numpy(g["prompt"]), 12)
+        assert out.get("tokens") is not None
+        n_same = next((i for i, (x, y) in enumerate(zip(out["tokens"], ref)) if x != y), 12)
+        assert n_same >= 9, (out["tokens"], ref)      # the golden prompt's one near-tie sits at step 9
+    finally:
+        eng.close()

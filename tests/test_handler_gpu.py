@@ -52,6 +52,7 @@ def test_concurrent_sessions_stream_engine_tokens(stack):
     outs = asyncio.run(main())
     assert h.get_active_requests() == {}
     from oracle import llama_oracle as O
+    from oracle import parity as P
     for i, (msgs, chunks) in enumerate(zip(convs, outs)):
         prompt = tok.apply_chat_template(msgs)
         with torch.no_grad():
@@ -63,11 +64,17 @@ def test_concurrent_sessions_stream_engine_tokens(stack):
         tail = dec.flush()                       # an unfinished UTF-8 sequence is flushed at the end
         if tail:
             pieces.append((len(ref) - 1, tail))
-        # identical to the oracle up to the first near-tie (margin inside the 2e-2 logit tolerance)
+        # the engine itself on this conversation, all 20 positions against the oracle (teacher-forced, near-ties
+        # re-aligned: oracle/parity.py); the runner thread is idle while no handler request is in flight
+        job = P.check(eng, f"handler conversation {i}", f"direct-{i}", prompt, ref, ref_logits, min_distinct=1)   # templated byte prompts on the tiny model may loop
+        eng.close_session(f"direct-{i}")
+        # the handler's chunks are the oracle's pieces; a stream cannot be re-aligned, so it is compared up to the
+        # first near-tie, which must be one by the measured-error rule (not the 2e-2 logit tolerance)
+        limit = max(3.0 * job.worst_err, P.WAIVER_FLOOR)
         for (k, exp), got in zip(pieces, chunks):
             if got != exp:
                 top2 = torch.topk(ref_logits[k], 2).values
-                assert (top2[0] - top2[1]).item() < 2e-2 * ref_logits[k].abs().max().item(), (i, k)
+                assert (top2[0] - top2[1]).item() <= limit * ref_logits[k].abs().max().item(), (i, k)
                 break
         else:
             assert len(chunks) == len(pieces)

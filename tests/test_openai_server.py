@@ -281,6 +281,40 @@ def test_client_disconnect_frees_the_request(srv):
             break
         time.sleep(0.01)
     assert srv.handler.get_active_requests() == {} and srv.eng.stats()["active_requests"] == 0
+    # ... and the conversation key it held: the next turn of the same conversation gets slot #0 again
+    httpx.post(srv.base + "/chat/completions",
+               json={"model": "m", "messages": [{"role": "user", "content": "count"}]}).raise_for_status()
+    assert srv.eng.submitted[-1][0].endswith("#0")
+
+
+def test_session_key_is_released_when_the_first_token_never_comes():
+    """anything but LLMServiceError before the first token (a client that hangs up early raises
+    CancelledError there) used to leave the key busy for good; later turns then got base#1, base#2, ...
+    and lost their KV prefix.  Both wires."""
+    seen = []
+
+    class Broken:
+        model = "m"
+
+        def check_connection(self):
+            return True
+
+        async def generate_stream_async(self, messages, request_id=None, **kw):
+            seen.append(request_id)
+            raise RuntimeError("boom")
+            yield ""                                  # pragma: no cover
+
+    app = create_app(Broken(), "m")
+
+    async def go():
+        tr = httpx.ASGITransport(app=app, raise_app_exceptions=False)
+        async with httpx.AsyncClient(transport=tr, base_url="http://t") as c:
+            body = {"model": "m", "messages": [{"role": "user", "content": "hi"}]}
+            for path in ("/v1/chat/completions", "/v1/chat/completions", "/api/chat", "/api/chat"):
+                r = await c.post(path, json=body)
+                assert r.status_code == 500
+    asyncio.run(go())
+    assert len(seen) == 4 and all(k.endswith("#0") for k in seen), seen
 
 
 # ------------------------------------------------------------------ the unchanged reference client side

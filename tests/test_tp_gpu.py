@@ -25,3 +25,5 @@ def test_tp2_matches_the_oracle_and_tp1():
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "TP_OK" in r.stdout, r.stdout[-2000:]
     print(r.stdout[r.stdout.index("TP_OK"):].splitlines()[0])
+    from oracle.parity import REPORT
+    REPORT.extend(ln[len("TP_PARITY "):] for ln in r.stdout.splitlines() if ln.startswith("TP_PARITY "))
