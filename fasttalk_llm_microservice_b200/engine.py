@@ -38,6 +38,7 @@ class EngineLimits:
     num_pages: int = 0                  # 0 = enough for max_batch full contexts (+25 %)
     max_sessions: int = 0
     use_pdl: bool = True
+    decode_prefill_cap: int = 0         # prompt tokens per step while sequences decode: 0 = 1024, < 0 = uncapped
     debug_logit_rows: int = 0
 
 
@@ -88,6 +89,7 @@ class Engine:
         cfg.use_pdl = int(lim.use_pdl)
         cfg.debug_logit_rows = lim.debug_logit_rows
         cfg.tp_size, cfg.tp_rank = tp_size, tp_rank
+        cfg.decode_prefill_cap = lim.decode_prefill_cap
         wt = N.Weights()
         for name in ("embed", "lm_head", "final_norm", "attn_norm", "wqkv", "wo", "mlp_norm", "wgu", "wd"):
             setattr(wt, name, w[name].data_ptr())
@@ -170,6 +172,10 @@ class Engine:
         buf = np.empty(cap, dtype=np.float32)
         n = N.check(self.lib.ft_engine_step_times(self._h, buf.ctypes.data, cap), "ft_engine_step_times")
         return buf[:n].tolist()
+
+    def set_decode_prefill_cap(self, cap: int):
+        """Prompt tokens admitted per step while sequences decode (0 = default 1024, < 0 = uncapped)."""
+        N.check(self.lib.ft_engine_set_decode_prefill_cap(self._h, int(cap)), "ft_engine_set_decode_prefill_cap")
 
     def set_profile(self, on: bool):
         N.check(self.lib.ft_engine_set_profile(self._h, int(on)), "ft_engine_set_profile")

@@ -230,7 +230,8 @@ def build_runner(model: str) -> EngineRunner:
     tok = load_tokenizer(spec.vocab, tok_path, require=bool(ckpt))
     lim = EngineLimits(max_batch=_env_int("FASTTALK_MAX_SESSIONS", 64),
                        max_batched_tokens=_env_int("FASTTALK_MAX_BATCHED_TOKENS", 8192),
-                       max_context=_env_int("FASTTALK_MAX_CONTEXT", _env_int("DEFAULT_CONTEXT_WINDOW", 8192)))
+                       max_context=_env_int("FASTTALK_MAX_CONTEXT", _env_int("DEFAULT_CONTEXT_WINDOW", 8192)),
+                       decode_prefill_cap=_env_int("FASTTALK_DECODE_PREFILL_CAP", 0))
     eng = Engine(spec, w, lim, eos_ids=tok.eos_ids)
     return EngineRunner(eng, tok)
 

@@ -27,6 +27,7 @@ class EngineConfig(C.Structure):
         ("n_eos", C.c_int), ("eos_ids", C.c_int * 4),
         ("use_pdl", C.c_int), ("debug_logit_rows", C.c_int),
         ("tp_size", C.c_int), ("tp_rank", C.c_int),
+        ("decode_prefill_cap", C.c_int),
     ]
 
 
@@ -85,6 +86,7 @@ SIGNATURES = {
     "ft_engine_get_logits": (_I, [_VP, _LL, _VP]),
     "ft_engine_timer": (_I, [_VP, _I, _VP]),
     "ft_engine_set_profile": (_I, [_VP, _I]),
+    "ft_engine_set_decode_prefill_cap": (_I, [_VP, _I]),
     "ft_engine_step_times": (_I, [_VP, _VP, _I]),
     "ft_debug_prefill_logits": (_I, [_VP, _VP, _I, _I, _VP]),
     "ft_engine_tp_export": (_I, [_VP, _VP, _VP, _VP]),

@@ -52,6 +52,11 @@ typedef struct {
      * Both ranks must be fed the same requests in the same order and stepped together; call
      * ft_engine_tp_export / ft_engine_tp_attach after creation, before the first step. */
     int tp_size, tp_rank;
+    /* Prompt tokens a step may admit WHILE other sequences are decoding (they all wait for the step): the
+     * latency side of vLLM's --max-num-batched-tokens trade-off (docker-compose.vllm.yml:48).  0 = default
+     * (1024), < 0 = no cap (every step may fill max_batched_tokens).  An engine with no decoding sequence
+     * always uses the full max_batched_tokens budget. */
+    int decode_prefill_cap;
 } ft_engine_config;
 
 typedef struct {
@@ -123,6 +128,9 @@ int ft_engine_cancel(ft_engine* e, long long req);
 /* Forget a session and free its KV pages (session end / disconnect). */
 int ft_engine_session_close(ft_engine* e, unsigned long long session_key);
 int ft_engine_stats_get(ft_engine* e, ft_engine_stats* out);
+/* Change ft_engine_config.decode_prefill_cap of a live engine (same encoding: 0 default, < 0 uncapped);
+ * takes effect at the next step. */
+int ft_engine_set_decode_prefill_cap(ft_engine* e, int cap);
 /* Measurement hooks (bench.py): CUDA events on the engine's own stream.  ft_engine_timer(e, 0, 0)
  * records a start event; ft_engine_timer(e, 1, &ms) records a stop event, waits for it and returns
  * the device time between the two.  With profiling on, every decode-attention launch is bracketed
