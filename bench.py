@@ -10,11 +10,15 @@ Workload (BASELINE.json configs[1]): Llama-3.2-1B bf16, 64 concurrent sessions p
   value     K timed decode steps, CUDA events on the engine's stream, max over ranks;
             KV cache and weights resident in HBM (the engine still uploads its ~2 KB of
             per-step metadata and reads the 64 sampled token ids back every step).
-  e2e       one whole conversation turn per session through the public API
-            (Engine.submit / step / drain) with HOST token buffers: 64 sessions re-send a
-            ~2k-token history of which the last 224 tokens are new, prefill rides along with
-            decode (continuous batching), 32 tokens are generated per session; generated
-            tokens / wall time, with TTFT and inter-token latency percentiles.
+  e2e       the same metric through the reference-facing plugin: 64 concurrent
+            NativeHandler.generate_stream_async calls (the handler interface the reference's WebSocket
+            server calls, websocket_server_vllm.py:528-539) with HOST buffers — `messages` in, one `str`
+            chunk per token out.  Each session re-sends a ~2k-token history of which ~224 tokens are
+            new (the rest is served from the session's KV), prefill rides along with decode, 32 tokens
+            are generated; chunks / wall time, with TTFT and inter-token percentiles.
+  e2e_engine  the same turn one level down, at the C ABI (Engine.submit / step / drain, host token lists).
+  ws        the same turn one level up: the reference's UNCHANGED WebSocketLLMServer (baseline/_ref) in
+            front of NativeHandler, 64 `websockets` clients in their own process, timed at the client.
   roofline  the dominant kernel (paged decode attention): algorithmic KV bytes per launch /
             its CUDA-event time, measured in a second pass over K more steps with events
             around every launch (events break PDL overlap, so they stay out of `value`).
@@ -199,6 +203,9 @@ def run_reference(args, rank, world):
 # ----------------------------------------------------------------------------- our arm
 def run_native(args, rank, world, local_rank):
     import torch
+    # stdout carries exactly ONE line, the JSON record: everything else this process prints (the reference
+    # server's loggers write to sys.stdout at every level) goes to stderr
+    real_stdout, sys.stdout = sys.stdout, sys.stderr
     from fasttalk_llm_microservice_b200 import build
     from fasttalk_llm_microservice_b200.engine import Engine, EngineLimits
     from fasttalk_llm_microservice_b200.model_spec import get_spec
@@ -220,7 +227,8 @@ def run_native(args, rank, world, local_rank):
     w = init_weights(spec, seed=rank, device="cuda")
     max_new_long = 2 * K + W + 96       # prefill steps + warm-up + timed pass + profiled pass
     max_ctx = CTX + max_new_long + 128
-    eng = Engine(spec, w, EngineLimits(max_batch=SESSIONS, max_batched_tokens=8192, max_context=max_ctx),
+    eng = Engine(spec, w, EngineLimits(max_batch=SESSIONS, max_batched_tokens=8192, max_context=max_ctx,
+                                       decode_prefill_cap=-1),      # set-up prefill unthrottled; default cap before e2e
                  eos_ids=())
     gens = [torch.Generator().manual_seed(1234 + rank * 1000 + i) for i in range(SESSIONS)]
     rand_tokens = lambda i, n: torch.randint(0, 128000, (n,), generator=gens[i]).tolist()
@@ -326,6 +334,7 @@ def run_native(args, rank, world, local_rank):
     for r in rids:
         eng.cancel(r)
     eng.step(); eng.drain()
+    eng.set_decode_prefill_cap(args.prefill_cap)      # serving configuration from here on (0 = the engine default, 1024)
     # warm the sessions with a known history (prefix reuse needs the cached tokens == re-sent prefix)
     for i in range(SESSIONS):
         eng.close_session(f"s{i}")
@@ -338,6 +347,7 @@ def run_native(args, rank, world, local_rank):
             if fin:
                 live.discard(r)
     e0 = eng.stats()
+    eng.step_log()
     barrier()
     t_start = time.perf_counter()
     import numpy as np
@@ -368,6 +378,9 @@ def run_native(args, rank, world, local_rank):
     e2e_s = time.perf_counter() - t_start
     e2e_s = max_over_ranks(e2e_s)
     e1 = eng.stats()
+    e_log = eng.step_log()
+    # the steps streaming sessions waited longest for: [device ms, decode rows, prompt tokens, host ms]
+    e_mixed = sorted((r for r in e_log.tolist() if r[1] > 0), key=lambda r: -r[0])[:4]
     e_steps = e1["steps"] - e0["steps"]
     e2e_value = world * n_out / e2e_s
 
@@ -383,6 +396,113 @@ def run_native(args, rank, world, local_rank):
     gcold = torch.Generator().manual_seed(99 + rank)
     cold = sorted(ttft_once(f"cold{j}", torch.randint(0, 128000, (CTX,), generator=gcold).tolist()) for j in range(5))
     ttft_cold_ms = cold[len(cold) // 2]
+
+    for i in range(SESSIONS):
+        eng.close_session(f"t{i}")
+    for j in range(5):
+        eng.close_session(f"cold{j}")
+
+    # ---- e2e through the reference-facing plugin: 64 concurrent NativeHandler.generate_stream_async calls,
+    # `messages` (host strings) in, one `str` chunk per token out — the call websocket_server_vllm.py:528-539 makes.
+    # Inside the timed region: chat template + tokenisation, submit, the engine thread's steps (metadata H2D, sampled
+    # ids D2H), detokenisation, one call_soon_threadsafe per step, the asyncio queues.
+    import asyncio
+    import random
+    from fasttalk_llm_microservice_b200.handler import EngineRunner, NativeHandler
+    from fasttalk_llm_microservice_b200.tokenizer import ByteTokenizer
+    tok = ByteTokenizer(spec.vocab)
+    runner = EngineRunner(eng, tok)
+    handler = NativeHandler(model=MODEL, runner=runner)
+    rnd = random.Random(4321 + rank)
+    words = ["alpha", "bravo", "charlie", "delta", "echo", "foxtrot", "golf", "hotel", "india", "juliet", "kilo", "lima"]
+
+    def text_of(n_chars):
+        out = []
+        while sum(len(x) + 1 for x in out) < n_chars:
+            out.append(rnd.choice(words))
+        return " ".join(out)[:n_chars]
+
+    def conv_sized(target_tokens, tail):
+        """messages whose templated length is exactly target_tokens: system + user, then `tail` messages."""
+        sys_len = max(16, target_tokens - 64)
+        for _ in range(4):
+            m = [{"role": "system", "content": text_of(sys_len // 2)}, {"role": "user", "content": text_of(sys_len - sys_len // 2)}] + tail
+            sys_len += target_tokens - len(tok.apply_chat_template(m))
+        m[1]["content"] = m[1]["content"] + "x" * max(0, target_tokens - len(tok.apply_chat_template(m)))
+        return m
+
+    async def handler_turn(convs, max_tokens, tag):
+        t0 = time.perf_counter()
+        async def one(i, msgs):
+            stamps = []
+            async for chunk in handler.generate_stream_async(msgs, temperature=0.0, max_tokens=max_tokens, top_p=1.0,
+                                                             request_id=f"{tag}{i}"):
+                stamps.append(time.perf_counter() - t0)
+            return stamps
+        res = await asyncio.gather(*[one(i, m) for i, m in enumerate(convs)])
+        return res, time.perf_counter() - t0
+
+    conv1 = [conv_sized(CTX - TURN_NEW, []) for _ in range(SESSIONS)]
+    asyncio.run(handler_turn(conv1, 1, "h"))                                     # turn 1 (untimed): histories cached
+    conv2 = [m + [{"role": "assistant", "content": "ok"}, {"role": "user", "content": text_of(TURN_NEW - 16)}] for m in conv1]
+    h0 = eng.stats()
+    barrier()
+    h_res, h_wall = asyncio.run(handler_turn(conv2, TURN_GEN, "h"))
+    torch.cuda.synchronize()
+    h_wall = max_over_ranks(h_wall)
+    h1 = eng.stats()
+    h_steps = max(1, h1["steps"] - h0["steps"])
+    h_tokens = (h1["decode_tokens"] - h0["decode_tokens"]) + SESSIONS          # engine-side count: decode rows + first tokens
+    h_chunks = sum(len(r) for r in h_res)
+    h_first = [r[0] for r in h_res if r]
+    h_gaps = [b - a for r in h_res for a, b in zip(r, r[1:])]
+    e2e_handler = {"value": world * h_chunks / h_wall, "unit": "tok/s",
+                   "h2d_bytes_per_step": (h1["h2d_bytes"] - h0["h2d_bytes"]) / h_steps,
+                   "d2h_bytes_per_step": (h1["d2h_bytes"] - h0["d2h_bytes"]) / h_steps,
+                   "what": f"{SESSIONS} concurrent NativeHandler.generate_stream_async calls (the reference's handler "
+                           f"interface): messages in, one str chunk per token out; ~{CTX}-token templated history "
+                           f"(~{TURN_NEW} new, rest served from the session's KV), {TURN_GEN} generated; byte tokenizer",
+                   "chunks": h_chunks, "engine_tokens": h_tokens, "steps": h_steps, "wall_s": h_wall,
+                   "prompt_tokens_mean": sum(len(tok.apply_chat_template(m)) for m in conv2) / SESSIONS,
+                   "prefix_hit_tokens": h1["prefix_hit_tokens"] - h0["prefix_hit_tokens"],
+                   "ttft_ms_p50": 1e3 * pct(h_first, 0.5), "ttft_ms_p99": 1e3 * pct(h_first, 0.99),
+                   "itl_ms_p50": 1e3 * pct(h_gaps, 0.5), "itl_ms_p99": 1e3 * pct(h_gaps, 0.99),
+                   "decode_prefill_cap": args.prefill_cap or 1024}
+    for i in range(SESSIONS):
+        eng.close_session(f"h{i}")
+
+    # ---- WebSocket level (SURVEY.md §8d "two levels"): the reference's UNCHANGED WebSocketLLMServer from
+    # baseline/_ref, uvicorn on 127.0.0.1, 64 `websockets` clients in their own process, two turns; turn 2 timed
+    # client-side.  Rank 0 only, N = 1 only (one server per GPU in a deployment; the clients need host cores).
+    ws_level = None
+    if rank == 0 and world == 1 and not args.no_ws:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        try:
+            import ws_harness as WS
+            if WS.find_reference() is None:
+                ws_level = {"unavailable": "no reference checkout (baseline/_ref): run scripts/install_reference.sh"}
+            else:
+                srv = WS.ReferenceServer(runner, env={"DEFAULT_MAX_TOKENS": str(TURN_GEN), "VLLM_MODEL": MODEL})
+                try:
+                    n1 = CTX - TURN_NEW - TURN_GEN - 40
+                    specs = [{"system_prompt": text_of(n1 // 2), "turns": [text_of(n1 - n1 // 2), text_of(TURN_NEW - 16)]}
+                             for _ in range(SESSIONS)]
+                    w0 = eng.stats()
+                    res = WS.run_clients_subprocess(srv.port, specs)
+                    w1 = eng.stats()
+                    ws_level = WS.turn_metrics(res, 1)
+                    ws_level.update({"unit": "tok/s", "value": ws_level.pop("tok_s"),
+                                     "what": "unchanged reference WebSocketLLMServer (websocket_server_vllm.py) + NativeHandler, "
+                                             f"{SESSIONS} websockets clients in a separate process, turn 2 of 2 "
+                                             f"(~{CTX}-token history re-sent, {TURN_GEN} tokens generated), timed at the client",
+                                     "turn1": {k: v for k, v in WS.turn_metrics(res, 0).items() if k in ("tok_s", "ttft_ms_p50", "ttft_ms_p99")},
+                                     "prefix_hit_tokens": w1["prefix_hit_tokens"] - w0["prefix_hit_tokens"],
+                                     "reference_from": os.path.relpath(srv.ref, ROOT) if srv.ref.startswith(ROOT) else srv.ref})
+                finally:
+                    srv.stop()
+        except Exception as e:  # noqa: BLE001 - the WS level is reported, never allowed to lose the bench line
+            ws_level = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+    runner.shutdown()
 
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -415,15 +535,19 @@ def run_native(args, rank, world, local_rank):
                               "unit": "GB/s", "frac": step_achieved / peak,
                               "note": "whole decode step: weights + KV bytes (SURVEY.md §8d) / device time"},
             "cpu_baseline": cpu_base,
-            "e2e": {"value": e2e_value, "unit": "tok/s",
+            "e2e": e2e_handler,
+            "e2e_engine": {"value": e2e_value, "unit": "tok/s",
                     "h2d_bytes_per_step": (e1["h2d_bytes"] - e0["h2d_bytes"]) / max(e_steps, 1),
                     "d2h_bytes_per_step": (e1["d2h_bytes"] - e0["d2h_bytes"]) / max(e_steps, 1),
-                    "what": f"one turn/session via Engine.submit/step/drain with host token lists: "
+                    "what": f"one turn/session via the C ABI (Engine.submit/step/drain) with host token lists: "
                             f"{CTX}-token history ({TURN_NEW} new, rest prefix-cached), {TURN_GEN} generated",
                     "steps": e_steps, "wall_s": e2e_s, "tokens": n_out,
                     "ttft_ms_p50": 1e3 * pct(list(first.values()), 0.5), "ttft_ms_p99": 1e3 * pct(list(first.values()), 0.99),
                     "itl_ms_p50": 1e3 * pct(gaps, 0.5), "itl_ms_p99": 1e3 * pct(gaps, 0.99),
-                    "prefix_hit_tokens": e1["prefix_hit_tokens"] - e0["prefix_hit_tokens"]},
+                    "prefix_hit_tokens": e1["prefix_hit_tokens"] - e0["prefix_hit_tokens"],
+                    "slowest_steps_with_decode_rows": [[round(x, 3) for x in r] for r in e_mixed],
+                    "first_step": [round(x, 3) for x in e_log[0].tolist()] if len(e_log) else None},
+            "ws": ws_level,
             "latency": {"itl_ms_p50_decode": ms / K, "ttft_ms_cold_2048_single": ttft_cold_ms,
                         "ttft_ms_warm_p50_64_sessions": 1e3 * pct(list(first.values()), 0.5)},
             "gpu_launches": launches,
@@ -432,7 +556,7 @@ def run_native(args, rank, world, local_rank):
             "rank_ms_per_step": rank_ms,
             "settle_s": args.settle,
         }
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=real_stdout, flush=True)
     eng.close()
     if dist:
         dist.barrier()
@@ -446,6 +570,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ws", action="store_true", help="skip the WebSocket-level run")
+    ap.add_argument("--prefill-cap", type=int, default=0,
+                    help="engine decode_prefill_cap for the e2e runs (0 = engine default 1024, < 0 = uncapped)")
     ap.add_argument("--settle", type=float, default=2.0,
                     help="idle seconds between the set-up prefill and the warm-up (power-cap recovery; untimed)")
     args = ap.parse_args()

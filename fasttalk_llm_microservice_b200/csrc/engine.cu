@@ -24,6 +24,7 @@ struct Session {
     std::vector<int> pages;      // KV pages in position order
     std::vector<int> tokens;     // tokens whose K/V sit in the cache (positions 0..size-1)
     bool busy = false;
+    bool close_pending = false;  // session_close arrived while its request was inside a running step
     long long last_used = 0;
 };
 
@@ -40,6 +41,9 @@ struct Request {
     int state = REQ_WAITING;
     int last_token = -1;         // sampled but not yet fed back
     int logits_row = -1;         // row of the logits buffer in the latest step
+    bool in_flight = false;      // part of the step that is on the GPU right now (the engine lock is released
+                                 // while the step runs, so submit / cancel / close do not wait for the GPU)
+    bool cancel_pending = false; // cancelled while in flight: finished as "cancelled" when the step returns
 };
 
 struct OutTok { long long req; int token; int finish; };
@@ -70,7 +74,8 @@ struct Engine {
     ft_weights w;
     int dev = 0, sms = 148;
     cudaStream_t stream = nullptr;
-    std::mutex mu;
+    std::mutex mu;               // scheduler state; NOT held while a step's kernels run
+    std::mutex step_mu;          // one step (or debug / timer call that uses the stream's buffers) at a time
 
     int q_dim, kv_dim, qkv_dim, group, max_pages, t_max, r_max, logit_rows;
     int attn_ctas = 0;
@@ -126,7 +131,8 @@ struct Engine {
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     // device time of every step (events on the engine stream around upload .. sampled-token copy)
     cudaEvent_t s0 = nullptr, s1 = nullptr;
-    std::deque<float> step_gpu_ms;         // most recent kStepTimes steps, oldest first
+    struct StepRec { float gpu_ms, n_decode, n_prefill, host_ms; };
+    std::deque<StepRec> step_log;          // most recent kStepTimes steps, oldest first
 };
 constexpr size_t kStepTimes = 4096;
 
@@ -424,7 +430,7 @@ static unsigned long long mix64(unsigned long long x) {
 }
 
 // ------------------------------------------------------------------ one scheduler step
-static int engine_step(Engine* e) {
+static int engine_step(Engine* e, std::unique_lock<std::mutex>& lk) {
     const ft_engine_config& c = e->cfg;
     StepMeta& m = e->meta;
     const auto t_begin = std::chrono::steady_clock::now();
@@ -460,9 +466,14 @@ static int engine_step(Engine* e) {
         if (r->state == REQ_DECODE) dec.push_back(r);
     int budget = c.max_batched_tokens - (int)dec.size();
     // Sessions that are streaming wait for the whole step: beside decode rows a step admits at most
-    // `decode_prefill_cap` prompt tokens (a ~1k-token chunk adds ~3 ms to a 1B step instead of the ~25 ms a full
-    // 8192-token budget costs).  An engine with nothing decoding keeps the whole budget: first tokens come soonest.
-    if (!dec.empty() && e->decode_prefill_cap > 0) budget = std::min(budget, e->decode_prefill_cap);
+    // `decode_prefill_cap` prompt tokens (a ~1k-token chunk adds a few ms to a 1B step instead of the ~35 ms a full
+    // 8192-token budget costs).  The cap holds while at least as many sessions are streaming as are waiting for
+    // their first token; when more are waiting than streaming (a burst of arrivals behind one early bird, or an
+    // engine with nothing decoding) the step takes the whole budget: first tokens for the many come soonest.
+    int n_pending = 0;
+    for (Request* r : e->active) n_pending += r->state == REQ_PREFILL;
+    if (e->decode_prefill_cap > 0 && !dec.empty() && (int)dec.size() >= n_pending)
+        budget = std::min(budget, e->decode_prefill_cap);
     for (Request* r : e->active) {
         if (r->state != REQ_PREFILL || budget <= 0) continue;
         const int remaining = (int)r->prompt.size() - r->prefill_pos;
@@ -567,13 +578,26 @@ static int engine_step(Engine* e) {
                                       cudaMemcpyDeviceToHost, e->stream));
     }
     FT_CHECK_CUDA(cudaEventRecord(e->s1, e->stream));
-    FT_CHECK_CUDA(cudaStreamSynchronize(e->stream));
+    // The GPU works for milliseconds from here: give the scheduler lock back so that submit / cancel / close /
+    // drain / stats from other threads return at once (a submit used to wait for the whole step, which
+    // serialised 64 sessions arriving together into 64 steps).  What they may do meanwhile is limited to state
+    // this step does not use: requests in flight are only MARKED (cancel_pending / close_pending).
+    for (Request* r : dec) r->in_flight = true;
+    for (Request* r : pre) r->in_flight = true;
+    lk.unlock();
+    const cudaError_t sync_rc = cudaStreamSynchronize(e->stream);
+    lk.lock();
+    for (Request* r : dec) r->in_flight = false;
+    for (Request* r : pre) r->in_flight = false;
+    FT_CHECK_CUDA(sync_rc);
     e->st.d2h_bytes += (long long)b.n_logit_rows * sizeof(int);
     {
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, e->s0, e->s1) == cudaSuccess) {
-            if (e->step_gpu_ms.size() >= kStepTimes) e->step_gpu_ms.pop_front();
-            e->step_gpu_ms.push_back(ms);
+            if (e->step_log.size() >= kStepTimes) e->step_log.pop_front();
+            const float host_ms =
+                std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+            e->step_log.push_back({ms, (float)b.n_decode, (float)(b.T - b.n_decode), host_ms});
         }
     }
     for (int l = 0; l < e->prof_used; ++l) {
@@ -600,9 +624,17 @@ static int engine_step(Engine* e) {
         else if (r->n_generated >= r->max_new || ctx_after >= c.max_context) finish_request(e, r, 2, tok);
         else e->out.push_back({r->id, tok, 0});
     };
+    std::vector<Session*> to_close;
+    auto settle = [&](Request* r) -> bool {      // true: the request was cancelled / its session closed mid-step
+        if (r->sess && r->sess->close_pending) to_close.push_back(r->sess);
+        if (!r->cancel_pending) return false;
+        r->cancel_pending = false;
+        finish_request(e, r, 3, -1);
+        return true;
+    };
     for (Request* r : dec) {
         r->sess->tokens.push_back(r->last_token);
-        emit(r);
+        if (!settle(r)) emit(r);
     }
     for (int j = 0; j < b.n_prefill_req; ++j) {
         Request* r = pre[j];
@@ -611,10 +643,17 @@ static int engine_step(Engine* e) {
                          r->prompt.begin() + r->prefill_pos + pre_len[j]);
         r->prefill_pos += pre_len[j];
         e->st.prefill_tokens += pre_len[j];
+        if (settle(r)) continue;
         if (r->logits_row >= 0) {
             r->state = REQ_DECODE;
             emit(r);
         }
+    }
+    for (Session* sx : to_close) {
+        if (e->sessions.find(sx->key) == e->sessions.end() || e->sessions[sx->key] != sx) continue;   // listed twice
+        for (auto& kv : e->requests)
+            if (kv.second->sess == sx) kv.second->sess = nullptr;
+        drop_session(e, sx);
     }
     e->st.steps++;
     if (b.n_decode > 0) e->st.decode_steps++;
@@ -912,10 +951,11 @@ extern "C" int ft_engine_step(ft_engine* h) {
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e, "ft_engine_step: null engine");
     FT_REQUIRE(e->tp == 1 || e->peer_xchg, "ft_engine_step: tensor-parallel engine has no peer attached");
-    std::lock_guard<std::mutex> lk(e->mu);
+    std::lock_guard<std::mutex> sk(e->step_mu);
     std::lock_guard<std::mutex> dk(g_device_step_mu[e->dev % kMaxDevices]);
     DeviceGuard dg(e->dev);
-    return engine_step(e);
+    std::unique_lock<std::mutex> lk(e->mu);
+    return engine_step(e, lk);
 }
 
 extern "C" int ft_engine_drain(ft_engine* h, long long* req_ids, int* tokens, int* finish, int cap) {
@@ -948,6 +988,10 @@ extern "C" int ft_engine_cancel(ft_engine* h, long long req) {
     std::lock_guard<std::mutex> lk(e->mu);
     auto it = e->requests.find(req);
     if (it == e->requests.end() || it->second->state == REQ_DONE) return 1;    // nothing to cancel
+    if (it->second->in_flight) {         // inside the running step: finished as "cancelled" when it returns
+        it->second->cancel_pending = true;
+        return 0;
+    }
     finish_request(e, it->second, 3, -1);
     return 0;
 }
@@ -962,6 +1006,11 @@ extern "C" int ft_engine_session_close(ft_engine* h, unsigned long long key) {
     if (s->busy)
         for (auto& kv : e->requests)
             if (kv.second->sess == s && kv.second->state != REQ_DONE) {
+                if (kv.second->in_flight) {      // its pages are being read and written right now: close after the step
+                    kv.second->cancel_pending = true;
+                    s->close_pending = true;
+                    return 0;
+                }
                 finish_request(e, kv.second, 3, -1);
             }
     for (auto& kv : e->requests)
@@ -1002,6 +1051,7 @@ extern "C" int ft_engine_set_profile(ft_engine* h, int on) {
 extern "C" int ft_engine_timer(ft_engine* h, int stop, float* ms_out) {
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e, "ft_engine_timer: null engine");
+    std::lock_guard<std::mutex> sk(e->step_mu);
     std::lock_guard<std::mutex> lk(e->mu);
     DeviceGuard dg(e->dev);
     if (!stop) {
@@ -1015,20 +1065,24 @@ extern "C" int ft_engine_timer(ft_engine* h, int stop, float* ms_out) {
     return 0;
 }
 
-extern "C" int ft_engine_step_times(ft_engine* h, float* ms_out, int cap) {
+extern "C" int ft_engine_step_log(ft_engine* h, float* out, int cap_rows) {
     Engine* e = reinterpret_cast<Engine*>(h);
-    FT_REQUIRE(e && ms_out && cap >= 0, "ft_engine_step_times: bad arguments");
+    FT_REQUIRE(e && out && cap_rows >= 0, "ft_engine_step_log: bad arguments");
     std::lock_guard<std::mutex> lk(e->mu);
-    while ((int)e->step_gpu_ms.size() > cap) e->step_gpu_ms.pop_front();
+    while ((int)e->step_log.size() > cap_rows) e->step_log.pop_front();
     int n = 0;
-    for (float v : e->step_gpu_ms) ms_out[n++] = v;
-    e->step_gpu_ms.clear();
+    for (const auto& r : e->step_log) {
+        out[4 * n + 0] = r.gpu_ms; out[4 * n + 1] = r.n_decode; out[4 * n + 2] = r.n_prefill; out[4 * n + 3] = r.host_ms;
+        ++n;
+    }
+    e->step_log.clear();
     return n;
 }
 
 extern "C" int ft_engine_get_logits(ft_engine* h, long long req, float* host_out) {
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e && host_out, "ft_engine_get_logits: bad arguments");
+    std::lock_guard<std::mutex> sk(e->step_mu);       // the logits buffer belongs to the step while one runs
     std::lock_guard<std::mutex> lk(e->mu);
     DeviceGuard dg(e->dev);
     auto it = e->requests.find(req);
@@ -1042,8 +1096,9 @@ extern "C" int ft_engine_get_logits(ft_engine* h, long long req, float* host_out
 extern "C" int ft_debug_prefill_logits(ft_engine* h, const int* tokens, int n, int chunk, float* host_out) {
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e && tokens && host_out && n >= 1, "ft_debug_prefill_logits: bad arguments");
-    std::lock_guard<std::mutex> lk(e->mu);
+    std::lock_guard<std::mutex> sk(e->step_mu);
     std::lock_guard<std::mutex> dk(g_device_step_mu[e->dev % kMaxDevices]);
+    std::lock_guard<std::mutex> lk(e->mu);
     DeviceGuard dg(e->dev);
     FT_REQUIRE(e->active.empty() && e->waiting.empty(), "ft_debug_prefill_logits: engine must be idle");
     FT_REQUIRE(chunk >= 1 && chunk <= e->logit_rows && chunk <= e->t_max,

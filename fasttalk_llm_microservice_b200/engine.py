@@ -167,11 +167,16 @@ class Engine:
         N.check(self.lib.ft_engine_timer(self._h, 1, C.byref(ms)), "ft_engine_timer")
         return float(ms.value)
 
+    def step_log(self, cap: int = 4096) -> np.ndarray:
+        """float32 [steps, 4] since the last call, oldest first: device ms, decode rows, prompt tokens, host ms
+        (the engine keeps 4096)."""
+        buf = np.empty((cap, 4), dtype=np.float32)
+        n = N.check(self.lib.ft_engine_step_log(self._h, buf.ctypes.data, cap), "ft_engine_step_log")
+        return buf[:n].copy()
+
     def step_times_ms(self, cap: int = 4096) -> List[float]:
-        """Device time of each step since the last call (oldest first, the engine keeps 4096)."""
-        buf = np.empty(cap, dtype=np.float32)
-        n = N.check(self.lib.ft_engine_step_times(self._h, buf.ctypes.data, cap), "ft_engine_step_times")
-        return buf[:n].tolist()
+        """Device time of each step since the last call."""
+        return self.step_log(cap)[:, 0].tolist()
 
     def set_decode_prefill_cap(self, cap: int):
         """Prompt tokens admitted per step while sequences decode (0 = default 1024, < 0 = uncapped)."""

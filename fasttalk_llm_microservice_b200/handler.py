@@ -19,6 +19,7 @@ import asyncio
 import logging
 import os
 import queue
+import random
 import threading
 import time
 import uuid
@@ -34,12 +35,27 @@ except Exception:  # noqa: BLE001
     logger = logging.getLogger(__name__)
 
 _DONE = object()
+_TIMEOUT = object()
+
+
+def _arm_idle_watchdog(sink: "_Sink", loop, timeout: float) -> None:
+    """One timer per generation instead of one `asyncio.wait_for` per token (64 sessions x ~600 tokens/s each
+    made the per-chunk timeout handles a measurable share of the event loop): when it fires it either
+    finds that nothing arrived for `timeout` seconds and wakes the consumer with _TIMEOUT, or re-arms
+    itself for what is left of the current idle period."""
+    def check():
+        idle = time.monotonic() - sink.last
+        if idle >= timeout:
+            sink.aq.put_nowait(_TIMEOUT)
+        else:
+            sink.timer = loop.call_later(timeout - idle, check)
+    sink.timer = loop.call_later(timeout, check)
 
 
 class _Sink:
     """Where one request's text chunks go: an asyncio queue on its loop, or a thread queue."""
     __slots__ = ("loop", "aq", "tq", "decoder", "text", "stop", "finished", "error", "rid", "start_time",
-                 "cancelled", "n_tokens", "finish", "n_prompt")
+                 "cancelled", "n_tokens", "finish", "n_prompt", "last", "timer")
 
     def __init__(self, loop, decoder, stop):
         self.loop = loop
@@ -49,6 +65,7 @@ class _Sink:
         self.text, self.finished, self.error, self.rid = "", False, None, -1
         self.start_time, self.cancelled, self.n_tokens = time.time(), False, 0
         self.finish, self.n_prompt = None, 0      # engine finish reason ("stop" | "length" | ...), prompt tokens
+        self.last, self.timer = time.monotonic(), None     # async consumers: last item seen / idle watchdog handle
 
 
 class EngineRunner:
@@ -360,7 +377,7 @@ class NativeHandler:
                           temperature=1.0 if temperature is None else float(temperature),
                           top_k=int(top_k or 0), top_p=1.0 if top_p is None else float(top_p),
                           max_new_tokens=max_new,
-                          seed=(uuid.uuid4().int if seed is None else int(seed)) & 0xFFFFFFFF)
+                          seed=(random.getrandbits(32) if seed is None else int(seed)) & 0xFFFFFFFF)
         except Exception:
             with self._requests_lock:
                 self._active_requests.pop(req_id, None)
@@ -452,10 +469,15 @@ class NativeHandler:
         req_id = sink = None
         hit = False
         try:
-            req_id, sink = self._start(asyncio.get_running_loop(), messages, temperature, max_tokens, top_p,
+            loop = asyncio.get_running_loop()
+            req_id, sink = self._start(loop, messages, temperature, max_tokens, top_p,
                                        top_k, stop, request_id, "native-async", tools, seed)
+            _arm_idle_watchdog(sink, loop, self.timeout)
             while True:
-                item = await asyncio.wait_for(sink.aq.get(), timeout=self.timeout)
+                item = await sink.aq.get()
+                sink.last = time.monotonic()
+                if item is _TIMEOUT:
+                    raise TimeoutError(f"no token within {self.timeout}s")
                 if item is _DONE:
                     if sink.error:
                         raise sink.error
@@ -480,6 +502,8 @@ class NativeHandler:
         finally:
             # disconnects finalise the generator here: the batch slot is freed
             if sink is not None:
+                if sink.timer is not None:
+                    sink.timer.cancel()
                 self._finish(req_id, sink, _meta, hit)
 
 

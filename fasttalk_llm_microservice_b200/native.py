@@ -87,7 +87,7 @@ SIGNATURES = {
     "ft_engine_timer": (_I, [_VP, _I, _VP]),
     "ft_engine_set_profile": (_I, [_VP, _I]),
     "ft_engine_set_decode_prefill_cap": (_I, [_VP, _I]),
-    "ft_engine_step_times": (_I, [_VP, _VP, _I]),
+    "ft_engine_step_log": (_I, [_VP, _VP, _I]),
     "ft_debug_prefill_logits": (_I, [_VP, _VP, _I, _I, _VP]),
     "ft_engine_tp_export": (_I, [_VP, _VP, _VP, _VP]),
     "ft_engine_tp_attach": (_I, [_VP, _VP, _VP, _VP]),

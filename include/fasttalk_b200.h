@@ -54,8 +54,9 @@ typedef struct {
     int tp_size, tp_rank;
     /* Prompt tokens a step may admit WHILE other sequences are decoding (they all wait for the step): the
      * latency side of vLLM's --max-num-batched-tokens trade-off (docker-compose.vllm.yml:48).  0 = default
-     * (1024), < 0 = no cap (every step may fill max_batched_tokens).  An engine with no decoding sequence
-     * always uses the full max_batched_tokens budget. */
+     * (1024), < 0 = no cap (every step may fill max_batched_tokens).  The cap applies while at least as many
+     * sequences are decoding as are waiting for their first token; otherwise (nothing decoding, or a burst of
+     * arrivals that outnumbers the decoding sequences) the step uses the full max_batched_tokens budget. */
     int decode_prefill_cap;
 } ft_engine_config;
 
@@ -136,11 +137,12 @@ int ft_engine_set_decode_prefill_cap(ft_engine* e, int cap);
  * the device time between the two.  With profiling on, every decode-attention launch is bracketed
  * by events and accumulated into ft_engine_stats (this breaks PDL overlap around that kernel). */
 int ft_engine_timer(ft_engine* e, int stop, float* ms_out);
-/* Device time (ms, CUDA events on the engine's stream: metadata upload .. sampled-token copy) of each
- * of the most recent steps, oldest first, at most `cap` (the engine keeps 4096) -> HOST float array;
- * returns how many were written and forgets them.  The difference between ft_engine_timer's total and
- * their sum is the time the GPU waited for the host between steps. */
-int ft_engine_step_times(ft_engine* e, float* ms_out, int cap);
+/* One row of four floats per step for the most recent steps, oldest first, at most `cap_rows` (the engine
+ * keeps 4096) -> HOST float [rows][4]: device ms (CUDA events on the engine's stream: metadata upload ..
+ * sampled-token copy), decode rows, prompt tokens, host wall ms of the step.  Returns the rows written and
+ * forgets them.  ft_engine_timer's total minus the sum of the device times is what the GPU waited for the
+ * host between steps. */
+int ft_engine_step_log(ft_engine* e, float* out, int cap_rows);
 int ft_engine_set_profile(ft_engine* e, int on);
 /* fp32 logits [vocab] of `req` from the most recent step it took part in -> HOST buffer. */
 int ft_engine_get_logits(ft_engine* e, long long req, float* host_out);

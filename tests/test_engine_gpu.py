@@ -446,3 +446,74 @@ def test_engine_stepped_from_a_fresh_thread():
         assert n_same >= 9, (out["tokens"], ref)      # the golden prompt's one near-tie sits at step 9
     finally:
         eng.close()
+
+
+def test_submit_cancel_and_close_while_a_step_is_on_the_gpu():
+    """The scheduler lock is released while a step's kernels run, so submit / cancel / session_close from other
+    threads return without waiting for the GPU.  One thread steps continuously; the test thread submits requests,
+    cancels some and closes the sessions of others at arbitrary moments.  Every request must end with exactly one
+    finish event, untouched requests must produce what they produce alone, and every KV page must come back."""
+    import threading
+    import time
+    spec, w, g = _tiny_setup()
+    eng = make_engine(spec, w, max_batch=16, max_batched_tokens=512, max_context=1024)
+    try:
+        gen = torch.Generator().manual_seed(77)
+        prompts = [torch.randint(0, spec.vocab, (int(n),), generator=gen).tolist()
+                   for n in torch.randint(20, 400, (40,), generator=gen)]
+        want = {i: eng.generate([prompts[i]], max_new_tokens=20, sessions=[f"solo{i}"], ignore_eos=True)[0]
+                for i in range(0, 40, 4)}
+        for i in want:
+            eng.close_session(f"solo{i}")
+        total_free = eng.stats()["free_pages"]
+        stop, events, errs = threading.Event(), [], []
+
+        def stepper():
+            try:
+                while not stop.is_set():
+                    if eng.step() == 0:
+                        time.sleep(0.0002)
+                    events.extend(eng.drain())
+            except Exception as e:  # noqa: BLE001
+                errs.append(e)
+        t = threading.Thread(target=stepper)
+        t.start()
+        rids, slow = {}, 0.0
+        for i, p in enumerate(prompts):
+            t0 = time.perf_counter()
+            rids[i] = eng.submit(f"c{i}", p, max_new_tokens=20, ignore_eos=True)
+            slow = max(slow, time.perf_counter() - t0)
+            time.sleep(0.0007 * (i % 3))
+            if i % 4 == 1:
+                eng.cancel(rids[i])                       # often while its prefill or a decode step is in flight
+            if i % 4 == 2:
+                eng.close_session(f"c{i}")
+        deadline = time.time() + 60
+        while time.time() < deadline and not errs:
+            fins = {r for r, tok, fin in list(events) if fin is not None}
+            if all(r in fins for r in rids.values()):
+                break
+            time.sleep(0.01)
+        stop.set()
+        t.join(timeout=10)
+        assert not errs, errs
+        by = {}
+        for r, tok, fin in events:
+            by.setdefault(r, []).append((tok, fin))
+        for i, r in rids.items():
+            fins = [f for _, f in by.get(r, []) if f is not None]
+            assert len(fins) == 1, (i, fins)
+            toks = [tk for tk, _ in by[r] if tk >= 0]
+            if i % 4 == 0:
+                assert fins == ["length"] and toks == want[i], i          # untouched: same tokens as alone
+            elif i % 4 == 3:
+                assert fins == ["length"] and len(toks) == 20
+            else:
+                assert fins[0] in ("cancelled", "length")
+        for i in range(40):
+            eng.close_session(f"c{i}")
+        st = eng.stats()
+        assert st["free_pages"] == total_free and st["active_requests"] == 0, st
+        assert slow < 0.05, f"a submit waited {slow * 1e3:.1f} ms"
+    finally:
+        eng.close()

@@ -210,3 +210,45 @@ def test_unchanged_reference_server_drives_native_handler(monkeypatch):
     # turn 2 re-sends the history: turn 1's prompt (minus the generation header) is its prefix
     assert t2[:len(t1)] == t1
     assert eng.submitted[0][2]["temperature"] == 0.0 and eng.submitted[0][2]["max_new_tokens"] == 64
+
+
+def test_async_generation_times_out_when_the_engine_goes_quiet():
+    """One idle watchdog per generation (not a wait_for per token): a stream that gets no token for `timeout`
+    seconds fails with LLMServiceError like the reference's HTTP timeout does, and its batch slot is freed;
+    a stream that keeps receiving tokens is never cut, however long it runs."""
+    import time as _time
+    tok = ByteTokenizer()
+
+    class Stalling(FakeEngine):
+        def step(self):
+            _time.sleep(0.01)
+            return 0
+
+    eng = Stalling(tok)
+    runner = EngineRunner(eng, tok)
+    h = NativeHandler(model="m", runner=runner, timeout=0.3)
+
+    async def go():
+        t0 = _time.perf_counter()
+        with pytest.raises(LLMServiceError):
+            async for _ in h.generate_stream_async([{"role": "user", "content": "hi"}], request_id="quiet"):
+                pass
+        return _time.perf_counter() - t0
+    took = asyncio.run(go())
+    assert 0.25 <= took < 2.0, took
+    assert h.get_active_requests() == {} and eng.stats()["active_requests"] == 0
+    runner.shutdown()
+
+    class Slow(FakeEngine):                       # a token every 50 ms for ~1 s: longer than the timeout in total
+        def step(self):
+            _time.sleep(0.05)
+            return super().step()
+
+    eng2 = Slow(tok, reply="abcdefghijklmnopqrst")
+    runner2 = EngineRunner(eng2, tok)
+    h2 = NativeHandler(model="m", runner=runner2, timeout=0.3)
+
+    async def go2():
+        return [c async for c in h2.generate_stream_async([{"role": "user", "content": "hi"}], request_id="slow")]
+    assert "".join(asyncio.run(go2())) == "abcdefghijklmnopqrst"
+    runner2.shutdown()
