@@ -305,6 +305,13 @@ def run_native(args, rank, world, local_rank):
                       "what": "device ms of each timed step (events around upload..sampled-token copy), rank 0; "
                               "host_gap = (timed total - their sum) / K = GPU idle between steps"}
 
+    if args.tune:
+        if rank == 0:
+            print(json.dumps({"ms_per_step": ms / K, "step_frac": step_achieved / peak, "step_ms": step_stats,
+                              "clocks": clk}), file=real_stdout, flush=True)
+        eng.close()
+        return
+
     # ---- roofline of the dominant kernel: second pass, events around every launch
     eng.set_profile(True)
     p0 = eng.stats()
@@ -571,6 +578,7 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ws", action="store_true", help="skip the WebSocket-level run")
+    ap.add_argument("--tune", action="store_true", help="kernel tuning: print ms/step of the timed decode steps and exit")
     ap.add_argument("--prefill-cap", type=int, default=0,
                     help="engine decode_prefill_cap for the e2e runs (0 = engine default 1024, < 0 = uncapped)")
     ap.add_argument("--settle", type=float, default=2.0,

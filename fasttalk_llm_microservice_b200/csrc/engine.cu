@@ -11,6 +11,8 @@
 #include <deque>
 #include <mutex>
 #include <new>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <unordered_map>
 #include <vector>
@@ -80,6 +82,7 @@ struct Engine {
     int q_dim, kv_dim, qkv_dim, group, max_pages, t_max, r_max, logit_rows;
     int attn_ctas = 0;
     int decode_prefill_cap = 0;            // prompt tokens admitted per step while sequences are decoding (0 = no cap)
+    int prefill_planes = 2;                // activation planes of the multi-wave prefill GEMMs (1 = hi only)
     size_t kv_layer_bytes = 0;
 
     // device buffers
@@ -135,6 +138,7 @@ struct Engine {
     std::deque<StepRec> step_log;          // most recent kStepTimes steps, oldest first
 };
 constexpr size_t kStepTimes = 4096;
+constexpr int kDefaultPrefillPlanes = 2;
 
 // Every entry point that touches CUDA makes the engine's device current for its duration: the caller may be a
 // thread whose current device is another GPU (a fresh thread starts on device 0).
@@ -251,6 +255,7 @@ static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, 
     const int splits = staged ? gemm_pick_splits(n_out, T, K, e->sms, true) : 1;
     epi.scratch = e->gemm_scratch;
     epi.sync = e->gemm_sync;
+    epi.x_planes = e->prefill_planes;
     if (staged && splits > 1) {              // launches are stream-ordered and each epilogue waits for its predecessor
         epi.sync_mode = 1 + e->sync_parity;
         epi.sync_slots = e->sms;
@@ -692,6 +697,9 @@ static int engine_init(Engine* e) {
     e->r_max = c.max_batch;
     e->logit_rows = std::max(c.max_batch, c.debug_logit_rows);
     e->pdl = c.use_pdl != 0;
+    e->prefill_planes = c.prefill_planes == 1 ? 1 : c.prefill_planes == 2 ? 2 : kDefaultPrefillPlanes;
+    if (const char* ov = getenv("FT_PREFILL_PLANES"))       // A/B switch for experiments (scripts/)
+        if (atoi(ov) == 1 || atoi(ov) == 2) e->prefill_planes = atoi(ov);
     e->decode_prefill_cap = c.decode_prefill_cap == 0 ? 1024 : c.decode_prefill_cap < 0 ? 0 : c.decode_prefill_cap;
     e->tp = c.tp_size > 1 ? c.tp_size : 1;
     FT_REQUIRE(e->tp <= 2 && c.tp_rank >= 0 && c.tp_rank < e->tp, "engine: tensor parallelism is built for 2 ranks");

@@ -771,14 +771,14 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 // per CTA, per-mode epilogue on the CTA's own 128 rows.  Barriers: TMA of both CTAs counts on the LEADER's
 // full barrier; tcgen05.commit multicasts "stage free" / "accumulator ready" to both; both epilogues report
 // "accumulator drained" to the leader.
-template <int BN>
+template <int BN, bool HILO>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x_half,
                  const __grid_constant__ CUtensorMap map_x_lo_half, const __grid_constant__ ft_gemm_epilogue ep,
                  int n_out, int T, int k_chunks, int stages) {
     constexpr int HALF = BN / 2, CB = 64;      // BN = 128 or 256 tokens per tile, half of them in each CTA
     constexpr int B_PLANE = HALF * GEMM_BK * 2;
-    constexpr int STAGE_BYTES = GEMM_A_BYTES + 2 * B_PLANE;          // per CTA
+    constexpr int STAGE_BYTES = GEMM_A_BYTES + (HILO ? 2 : 1) * B_PLANE;          // per CTA
     constexpr uint32_t TMEM_COLS = 2 * BN;
 
     extern __shared__ uint8_t smem_raw[];
@@ -802,7 +802,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
         tma_prefetch_desc(&map_x_half);
-        tma_prefetch_desc(&map_x_lo_half);
+        if (HILO) tma_prefetch_desc(&map_x_lo_half);
         for (int s = 0; s < stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -841,8 +841,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
                     uint8_t* st = smem + (size_t)slot * STAGE_BYTES;
                     tma_tile_2d_pair(st, &map_w, i * GEMM_BK, row0, &full_bar[slot], pol_w);
                     tma_tile_2d_pair(st + GEMM_A_BYTES, &map_x_half, i * GEMM_BK, tok0, &full_bar[slot], pol_x);
-                    tma_tile_2d_pair(st + GEMM_A_BYTES + B_PLANE, &map_x_lo_half, i * GEMM_BK, tok0, &full_bar[slot],
-                                     pol_x);
+                    if (HILO)
+                        tma_tile_2d_pair(st + GEMM_A_BYTES + B_PLANE, &map_x_lo_half, i * GEMM_BK, tok0,
+                                         &full_bar[slot], pol_x);
                 }
             }
         }
@@ -865,13 +866,15 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
                     const uint32_t a_addr = smem_u32(smem + (size_t)slot * STAGE_BYTES);
                     const uint64_t a_desc = umma_desc_k128(a_addr);
                     const uint64_t b_desc = umma_desc_k128(a_addr + GEMM_A_BYTES);
-                    const uint64_t l_desc = umma_desc_k128(a_addr + GEMM_A_BYTES + B_PLANE);
 #pragma unroll
                     for (int k = 0; k < GEMM_BK / 16; ++k)
                         umma_bf16_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (i | k) != 0);
+                    if (HILO) {
+                        const uint64_t l_desc = umma_desc_k128(a_addr + GEMM_A_BYTES + B_PLANE);
 #pragma unroll
-                    for (int k = 0; k < GEMM_BK / 16; ++k)
-                        umma_bf16_pair(d_tmem, a_desc + 2 * k, l_desc + 2 * k, idesc, 1u);
+                        for (int k = 0; k < GEMM_BK / 16; ++k)
+                            umma_bf16_pair(d_tmem, a_desc + 2 * k, l_desc + 2 * k, idesc, 1u);
+                    }
                     umma_commit_pair(&empty_bar[slot]);
                 }
                 umma_commit_pair(&tmem_full_bar[acc]);
@@ -1090,10 +1093,10 @@ static int launch_persistent_bn(const CUtensorMap& mw, const CUtensorMap& mx, co
     return 0;
 }
 
-template <int BN>
+template <int BN, bool HILO>
 static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const CUtensorMap& mxl_half, int n_out, int T,
                        int K, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream) {
-    constexpr int STAGE_BYTES = GEMM_A_BYTES + 2 * (BN / 2) * GEMM_BK * 2;
+    constexpr int STAGE_BYTES = GEMM_A_BYTES + (HILO ? 2 : 1) * (BN / 2) * GEMM_BK * 2;
     constexpr int STAGING = 64 * GEMM_BM * 4;
     const size_t fixed = 1024 + 256 + BN * 4 + STAGING;
     int stages = (int)((227 * 1024 - fixed) / STAGE_BYTES);
@@ -1104,7 +1107,7 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
     static int max_clusters_dev[kMaxDevices] = {};
     int& max_clusters = max_clusters_dev[current_device_slot()];
     if (!max_clusters) {
-        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<BN, HILO>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         cudaLaunchConfig_t q = {};
         q.gridDim = dim3(device_sms() & ~1);
         q.blockDim = dim3(GEMM_THREADS);
@@ -1115,7 +1118,7 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
         q.attrs = qa;
         q.numAttrs = 1;
         int n = 0;
-        if (cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel<BN>, &q) != cudaSuccess || n <= 0) n = device_sms() / 2;
+        if (cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel<BN, HILO>, &q) != cudaSuccess || n <= 0) n = device_sms() / 2;
         max_clusters = n;
     }
     const int n_work = (n_out / (2 * GEMM_BM)) * ((T + BN - 1) / BN);
@@ -1134,7 +1137,7 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_pair_kernel<BN>, mw, mx_half, mxl_half, epi, n_out, T, K / GEMM_BK, stages));
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_pair_kernel<BN, HILO>, mw, mx_half, mxl_half, epi, n_out, T, K / GEMM_BK, stages));
     return 0;
 }
 
@@ -1195,9 +1198,14 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
         // number of work units: only when at least eight rounds of them remain per cluster (measured: with 3–5
         // rounds the down and QKV projections lose more to the last, partly empty round than the shape gains)
         const long long work256 = (long long)(n_out / (2 * GEMM_BM)) * ((T + 255) / 256);
+        // x_planes == 1: the multi-wave (prefill) tiles multiply the hi plane only — half the tensor work; the
+        // latency-bound decode tiles, where the second product is free, always use both
+        const bool one = epi.x_planes == 1;
         if (work256 >= 8LL * (device_sms() / 2))
-            return launch_pair<256>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
-        return launch_pair<128>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream);
+            return one ? launch_pair<256, false>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream)
+                       : launch_pair<256, true>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
+        return one ? launch_pair<128, false>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream)
+                   : launch_pair<128, true>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream);
     }
     if (multiwave && K <= 4096) {
         switch (bn) {

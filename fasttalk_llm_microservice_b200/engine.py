@@ -39,6 +39,7 @@ class EngineLimits:
     max_sessions: int = 0
     use_pdl: bool = True
     decode_prefill_cap: int = 0         # prompt tokens per step while sequences decode: 0 = 1024, < 0 = uncapped
+    prefill_planes: int = 0             # activation planes in the large prefill GEMMs: 0 = default, 1 = hi only, 2 = hi + lo
     debug_logit_rows: int = 0
 
 
@@ -90,6 +91,7 @@ class Engine:
         cfg.debug_logit_rows = lim.debug_logit_rows
         cfg.tp_size, cfg.tp_rank = tp_size, tp_rank
         cfg.decode_prefill_cap = lim.decode_prefill_cap
+        cfg.prefill_planes = lim.prefill_planes
         wt = N.Weights()
         for name in ("embed", "lm_head", "final_norm", "attn_norm", "wqkv", "wo", "mlp_norm", "wgu", "wd"):
             setattr(wt, name, w[name].data_ptr())

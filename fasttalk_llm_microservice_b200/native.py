@@ -27,7 +27,7 @@ class EngineConfig(C.Structure):
         ("n_eos", C.c_int), ("eos_ids", C.c_int * 4),
         ("use_pdl", C.c_int), ("debug_logit_rows", C.c_int),
         ("tp_size", C.c_int), ("tp_rank", C.c_int),
-        ("decode_prefill_cap", C.c_int),
+        ("decode_prefill_cap", C.c_int), ("prefill_planes", C.c_int),
     ]
 
 
@@ -66,6 +66,7 @@ class GemmEpilogue(C.Structure):
         ("tp_peer_xchg", C.c_void_p), ("tp_xchg", C.c_void_p), ("tp_peer_flags", C.c_void_p),
         ("tp_flags", C.c_void_p), ("tp_epoch", C.c_uint), ("tp_peer_out", C.c_void_p),
         ("out_stride", C.c_int), ("out_col0", C.c_int), ("sync_mode", C.c_int), ("sync_slots", C.c_int),
+        ("x_planes", C.c_int),
     ]
 
 
