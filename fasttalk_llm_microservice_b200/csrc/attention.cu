@@ -171,6 +171,16 @@ attn_decode_kernel(const __half* __restrict__ q, const uint8_t* __restrict__ kv_
         waited = true;
     }
 
+    // a sequence with no context has no tiles and so no CTA of its own: its output rows are defined as zero
+    if (blockIdx.x == 0 && !is_producer) {
+        for (int b = 0; b < B; ++b) {
+            if (tile_prefix[b + 1] != tile_prefix[b]) continue;
+            for (int e = threadIdx.x; e < nq * D; e += ATTN_COMPUTE_WARPS * 32) {
+                out[(size_t)b * nq * D + e] = __float2bfloat16(0.f);
+                if (out_lo) out_lo[(size_t)b * nq * D + e] = __float2bfloat16(0.f);
+            }
+        }
+    }
     const long long total = (long long)tile_prefix[B] * nkv;
     const long long per = (total + gridDim.x - 1) / gridDim.x;
     long long f = per * blockIdx.x;

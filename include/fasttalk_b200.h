@@ -275,7 +275,7 @@ int ft_silu_mul(const float* gu, int n_splits, long long split_stride, void* act
                 void* stream);
 
 /* K5: paged GQA decode attention, one query token per sequence.  q FP16 [B][nq][d], KV cache FP16,
- * out bf16 [B][nq*d] (+ residual plane out_lo, may be NULL).  `tile_prefix` (int32 [B+1]) and
+ * out bf16 [B][nq*d] (+ residual plane out_lo, may be NULL); a sequence with ctx_lens[b] == 0 gets zero rows.  `tile_prefix` (int32 [B+1]) and
  * `scratch` (ft_attn_decode_scratch_bytes) are device work buffers the call fills. */
 long long ft_attn_decode_scratch_bytes(int B, int nkv, int group, int d, int n_ctas);
 /* Tuning aid: per-CTA globaltimer (ns) timeline of the most recent ft_attn_decode launch ->

@@ -80,7 +80,7 @@ def cfg3():
     spec = get_spec("llama-3.2-3b")
     w = init_weights(spec, seed=0, device="cuda")
     out = {"config": "cfg3: llama-3.2-3b, 2k histories; 256 sessions on one GPU and the 32/GPU share of 8 GPUs"}
-    eng = Engine(spec, w, EngineLimits(max_batch=256, max_batched_tokens=8192, max_context=2048 + 256), eos_ids=())
+    eng = Engine(spec, w, EngineLimits(max_batch=256, max_batched_tokens=8192, max_context=2048 + 256, decode_prefill_cap=-1), eos_ids=())
     out["n1_256_sessions"] = decode_run(eng, spec, 256, 2048, 32, "a")
     out["n8_share_32_sessions"] = decode_run(eng, spec, 32, 2048, 64, "b")
     eng.close()
@@ -93,7 +93,7 @@ def cfg5():
     from fasttalk_llm_microservice_b200.openai_server import create_app
     from fasttalk_llm_microservice_b200.tokenizer import ByteTokenizer
     spec = get_spec("llama-3.1-8b")
-    eng = Engine(spec, init_weights(spec, seed=0, device="cuda"), EngineLimits(max_batch=16, max_batched_tokens=8192, max_context=4096), eos_ids=())
+    eng = Engine(spec, init_weights(spec, seed=0, device="cuda"), EngineLimits(max_batch=16, max_batched_tokens=8192, max_context=4096, decode_prefill_cap=-1), eos_ids=())
     tok = ByteTokenizer(spec.vocab)
     runner = EngineRunner(eng, tok)
     h = NativeHandler(model="llama3.1:8b", runner=runner)
@@ -191,7 +191,7 @@ def cfg2_http():
     from fasttalk_llm_microservice_b200.openai_server import create_app
     from fasttalk_llm_microservice_b200.tokenizer import ByteTokenizer
     spec = get_spec("llama-3.2-1b")
-    eng = Engine(spec, init_weights(spec, seed=0, device="cuda"), EngineLimits(max_batch=64, max_batched_tokens=8192, max_context=4096), eos_ids=())
+    eng = Engine(spec, init_weights(spec, seed=0, device="cuda"), EngineLimits(max_batch=64, max_batched_tokens=8192, max_context=4096, decode_prefill_cap=-1), eos_ids=())
     runner = EngineRunner(eng, ByteTokenizer(spec.vocab))
     h = NativeHandler(model="llama3.2:1b", runner=runner)
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()

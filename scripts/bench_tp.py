@@ -58,7 +58,7 @@ def main():
     chk = [None, None]
     dist.all_gather_object(chk, float(w["wd"][-1].float().sum()))
     assert chk[0] == chk[1], "ranks drew different weights"
-    lim = EngineLimits(max_batch=8, max_batched_tokens=8192, max_context=8192)
+    lim = EngineLimits(max_batch=8, max_batched_tokens=8192, max_context=8192, decode_prefill_cap=-1)
     res = {"model": spec.name, "ctx": a.ctx, "steps": a.steps, "tp2": [], "tp1": []}
     eng = Engine(spec, w, lim, eos_ids=(), tp_rank=rank, tp_size=2)
     tp.connect(eng)

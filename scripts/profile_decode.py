@@ -26,7 +26,7 @@ a = ap.parse_args()
 build.build()
 spec = get_spec(a.model)
 w = init_weights(spec, seed=0, device="cuda")
-eng = Engine(spec, w, EngineLimits(max_batch=a.sessions, max_batched_tokens=8192, max_context=a.ctx + 256,
+eng = Engine(spec, w, EngineLimits(max_batch=a.sessions, max_batched_tokens=8192, max_context=a.ctx + 256, decode_prefill_cap=-1,
                                    use_pdl=not a.no_pdl), eos_ids=())
 g = torch.Generator().manual_seed(1)
 for i in range(a.sessions):

@@ -517,3 +517,35 @@ def test_submit_cancel_and_close_while_a_step_is_on_the_gpu():
         assert slow < 0.05, f"a submit waited {slow * 1e3:.1f} ms"
     finally:
         eng.close()
+
+
+# ------------------------------------------------------------------ a real checkpoint directory (§8f-2)
+def test_engine_generates_from_a_transformers_checkpoint(tmp_path):
+    """transformers writes a Llama checkpoint (`save_pretrained`, sharded safetensors + config.json); checkpoint.py
+    loads it into the engine's stacked layout on the GPU; the engine's logits and greedy tokens are compared with
+    the fp32 oracle ON THE LOADED TENSORS and with transformers' own forward of the model that wrote the files."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+    from make_golden import hf_model
+    from fasttalk_llm_microservice_b200.checkpoint import load_hf_checkpoint
+    from fasttalk_llm_microservice_b200.model_spec import TINY_D128 as spec0
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    w0 = init_weights(spec0, seed=12, std=0.08, norm_jitter=0.1)
+    m = hf_model(spec0, w0)
+    m.to(torch.bfloat16).save_pretrained(tmp_path, safe_serialization=True, max_shard_size="300KB")
+    assert os.path.exists(tmp_path / "model.safetensors.index.json")
+    spec, w = load_hf_checkpoint(str(tmp_path), device="cuda", name=spec0.name)
+    assert spec == spec0
+    eng = make_engine(spec, w)
+    try:
+        prompt = torch.randint(0, spec.vocab, (150,), generator=torch.Generator().manual_seed(2))
+        with torch.no_grad():
+            ref_full = O.forward(w, spec, prompt).cpu()
+            hf_full = hf_model(spec0, w0)(prompt[None]).logits[0]                  # fresh fp32 transformers model
+            ref_tokens, ref_logits = O.greedy_generate(w, spec, prompt, 32, return_logits=True)
+        assert per_pos_rel(ref_full, hf_full) < 1e-4                               # oracle == transformers on these files
+        got = eng.debug_prefill_logits(prompt.tolist(), chunk=64)
+        assert per_pos_rel(got, hf_full) < LOGIT_TOL, per_pos_rel(got, hf_full)
+        greedy_parity(eng, "tiny-d128 from a save_pretrained checkpoint", prompt.tolist(), ref_tokens, ref_logits)
+    finally:
+        eng.close()

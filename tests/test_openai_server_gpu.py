@@ -70,3 +70,43 @@ def test_openai_stream_equals_handler_stream_and_reuses_kv(served):
     finally:
         c.close()
     assert h.get_active_requests() == {} and eng.stats()["active_requests"] == 0
+
+
+def test_ollama_ndjson_wire_over_the_real_engine(served):
+    """§8f-3 on the GPU: the Ollama wire (`POST /api/chat`, NDJSON; ollama_handler.py:142-177, 268-296) answered by
+    the same process over the real engine — raw NDJSON first, then, when the reference is on this box
+    (baseline/_ref), the reference's UNCHANGED OllamaHandler as the client.  Both must give what NativeHandler
+    yields for the conversation."""
+    import json
+    import sys
+    import httpx
+    import ws_harness as W
+    h, eng, base = served
+    root = base[:-3]
+    msgs = [{"role": "system", "content": "be brief"}, {"role": "user", "content": "say something about NVLink"}]
+    direct = list(h.generate_stream(msgs, temperature=0.0, max_tokens=20, top_p=0.9, top_k=40, request_id="ollama-direct"))
+    assert httpx.get(root + "/").status_code == 200
+    with httpx.stream("POST", root + "/api/chat", timeout=60.0, json={
+            "model": "tiny-d64", "messages": msgs, "stream": True,
+            "options": {"temperature": 0.0, "num_predict": 20, "top_p": 0.9, "top_k": 40}}) as r:
+        assert r.status_code == 200
+        lines = [json.loads(ln) for ln in r.iter_lines() if ln.strip()]
+    assert [ln["done"] for ln in lines[:-1]] == [False] * (len(lines) - 1) and lines[-1]["done"] is True
+    assert [ln["message"]["content"] for ln in lines[:-1]] == direct
+    assert lines[-1]["done_reason"] == "length" and lines[-1]["eval_count"] == 20 and lines[-1]["prompt_eval_count"] > 0
+    ref = W.find_reference()
+    if ref is None:
+        pytest.skip("raw NDJSON checked; no reference checkout for the unchanged OllamaHandler part")
+    for m in [k for k in sys.modules if k == "app" or k.startswith("app.")]:
+        del sys.modules[m]
+    sys.path.insert(0, ref)
+    try:
+        from app.core.ollama_handler import OllamaHandler
+        oh = OllamaHandler(base_url=root, model="tiny-d64")
+        assert oh.check_connection() is True
+        out = list(oh.generate_stream(msgs, temperature=0.0, max_tokens=20, top_p=0.9, top_k=40, request_id="oh-1"))
+        assert out == direct
+        oh.close()
+    finally:
+        sys.path.remove(ref)
+    assert h.get_active_requests() == {} and eng.stats()["active_requests"] == 0
