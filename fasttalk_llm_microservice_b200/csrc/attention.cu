@@ -714,10 +714,13 @@ static int launch_attn_prefill_d(const void* q, const void* kv_layer, const int*
 int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                         const int* req_q_start, const int* req_slot, const int* req_pos0,
                         const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq,
-                        int nkv, int d, bool pdl, cudaStream_t stream) {
+                        int nkv, int d, bool pdl, cudaStream_t stream, int q_rows) {
     FT_REQUIRE(d == 64 || d == 128, "attn_prefill: head_dim %d not supported (64 or 128)", d);
     FT_REQUIRE(nq % nkv == 0, "attn_prefill: nq %% nkv != 0");
     FT_REQUIRE(n_tiles >= 1, "attn_prefill: no tiles");
+    if (q_rows > 0 && attn_prefill_tc_supported(nq, nkv, d))        // tcgen05 / TMEM kernel (attention_tc.cu)
+        return launch_attn_prefill_tc(q, q_rows, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
+                                      tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, pdl, stream);
     if (d == 64)
         return launch_attn_prefill_d<64>(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
                                          tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, pdl, stream);
@@ -762,10 +765,10 @@ extern "C" int ft_attn_decode(const void* q, const void* kv_layer, const int* pa
 extern "C" int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                                const int* req_q_start, const int* req_slot, const int* req_pos0,
                                const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo,
-                               int nq, int nkv, int d, void* stream) {
+                               int nq, int nkv, int d, int q_rows, void* stream) {
     return ft::launch_attn_prefill(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
                                    tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, d, false,
-                                   static_cast<cudaStream_t>(stream));
+                                   static_cast<cudaStream_t>(stream), q_rows);
 }
 
 // ------------------------------------------------------------------ decode attention without allocations

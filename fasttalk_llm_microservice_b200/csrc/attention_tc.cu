@@ -1,0 +1,391 @@
+// K6 on tcgen05 / TMEM — causal chunked-prefill attention over the paged KV cache (head_dim 64, GQA group 4).
+//
+// One CTA = one (request, 64-query tile, KV head): the tile's 64 tokens x the 4 q heads of the group are 256
+// query rows, handled as two 128-row halves (32 tokens x 4 heads each, row = token * 4 + head) so that every
+// K/V tile that reaches shared memory feeds 256 rows of tensor-core work (the mma.sync kernel re-fetched each
+// tile per q head).  Per KV tile of 64 keys and per half:
+//
+//   S  = Q K^T   tcgen05.mma  M128 N64 K64   A = Q half (TMA 3-D box -> 128-byte-swizzled rows in smem),
+//                                           B = the K slab exactly as it lies in the cache: [64 keys][64 d] fp16
+//                                           with chunk ^ (row & 7) IS the K-major SWIZZLE_128B operand layout
+//   softmax      4 warps, one thread per row: tcgen05.ld of the row's 64 scores, running max / sum in fp32,
+//                exp2, P -> fp16 -> shared memory (K-major swizzled rows, the A operand of the next product)
+//   O += P V     tcgen05.mma  M128 N64 K64   B = the V slab as it lies in the cache: [64 keys][64 d] is the
+//                                           MN-major SWIZZLE_128B layout (d contiguous, 8-key groups 1 KB apart)
+//
+// S and O live in TMEM (4 x 64 columns).  O is rescaled lazily: the row maximum used for scaling only moves when
+// the running maximum exceeds it by more than 2^8 (P stays far inside fp16 range, the accumulation is fp32, the
+// final normalisation uses the same reference — exact arithmetic, not an approximation), so the TMEM round trip
+// of a rescale happens on the first tiles only.  The two halves ping-pong: while the softmax warps of one half
+// work on their scores, the tensor core runs the other half's products.
+//
+// Warp roles (320 threads): warp 0 = TMA producer (Q once, then a ring of 16 KB K|V tiles, one bulk copy each),
+// warp 1 = TMEM owner + MMA issuer (one elected thread), warps 2..5 = softmax / epilogue of half 0, warps 6..9 of
+// half 1 (warp w may touch TMEM lanes 32 * (w % 4) .. +31).
+//
+// What bounds it: 64 x 256 exponentials per KV tile on the SFU (16 / clk / SM on B200) take ~1024 clk, the four
+// products ~512 clk — the kernel is exp-bound at about half the tensor peak, like every d = 64 attention on
+// this chip.
+#include "common.cuh"
+#include "ft_internal.h"
+
+#include <mutex>
+
+namespace ft {
+
+constexpr int TC_THREADS = 320;
+constexpr int TC_ROWS = 128;                 // rows per half (UMMA M)
+constexpr int TC_D = 64;
+constexpr int TC_G = 4;                      // q heads per KV head
+constexpr int TC_TOK = 64;                   // query tokens per CTA
+constexpr int TC_STAGES = 6;
+constexpr int TC_TILE_BYTES = 2 * kKvTile * TC_D * 2;      // K slab + V slab = 16 KB
+constexpr int TC_HALF_BYTES = TC_ROWS * TC_D * 2;          // 16 KB: a Q half / a P half
+constexpr float TC_RESCALE_THRESHOLD = 8.f;                // log2 units
+constexpr size_t TC_SMEM = 1024 + 2 * TC_HALF_BYTES + 2 * TC_HALF_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES + 256;
+
+// instruction descriptor, kind::f16 with fp16 operands: C = f32 (bit 4), A/B format F16 (0), b_major at bit 16
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N, bool b_mn_major) {
+    return (1u << 4) | ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// 3-D tiled tensor-map copy (d, head, token) -> shared memory
+__device__ __forceinline__ void tma_tile_3d(void* dst_smem, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+// MN-major SWIZZLE_128B operand (V slab): 8-row groups (8 keys x 128 B) 1024 B apart along K; one 64-element MN block
+__device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3ffff) >> 4);
+    d |= (uint64_t)(1024 >> 4) << 16;       // LBO: stride between 64-element MN blocks (only one block here)
+    d |= (uint64_t)(1024 >> 4) << 32;       // SBO: stride between 8-row K groups
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;                 // SWIZZLE_128B
+    return d;
+}
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) __nanosleep(20);
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t* __restrict__ kv_layer,
+                       const int* __restrict__ page_table, int max_pages, const int* __restrict__ req_q_start,
+                       const int* __restrict__ req_slot, const int* __restrict__ req_pos0,
+                       const int* __restrict__ tile_req, const int* __restrict__ tile_q0,
+                       __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo, int nq, int nkv,
+                       float scale_log2) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* q_s = smem;                                     // [2][128 rows][128 B]
+    uint8_t* p_s = smem + 2 * TC_HALF_BYTES;                 // [2][128 rows][128 B]
+    uint8_t* kv_s = smem + 4 * TC_HALF_BYTES;                // [STAGES][K 8 KB | V 8 KB]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(kv_s + (size_t)TC_STAGES * TC_TILE_BYTES);
+    uint64_t* kv_full = bars;                                // [STAGES]
+    uint64_t* kv_empty = kv_full + TC_STAGES;                // [STAGES]
+    uint64_t* q_full = kv_empty + TC_STAGES;                 // [1]
+    uint64_t* s_full = q_full + 1;                           // [2] scores of half h are in TMEM
+    uint64_t* p_full = s_full + 2;                           // [2] probabilities of half h are in shared memory
+    uint64_t* pv_done = p_full + 2;                          // [2] O += P V of half h retired (P buffer / O are free)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&map_q);
+        for (int s = 0; s < TC_STAGES; ++s) {
+            mbar_init(&kv_full[s], 1);
+            mbar_init(&kv_empty[s], 1);
+        }
+        mbar_init(q_full, 1);
+        for (int h = 0; h < 2; ++h) {
+            mbar_init(&s_full[h], 1);
+            mbar_init(&p_full[h], TC_ROWS);
+            mbar_init(&pv_done[h], 1);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, 256);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
+
+    const int req = tile_req[blockIdx.x];
+    const int q0 = tile_q0[blockIdx.x];
+    const int q_row0 = req_q_start[req];
+    const int q_len = req_q_start[req + 1] - q_row0;
+    const int pos0 = req_pos0[req];
+    const int kvh = blockIdx.y;
+    const int rows_here = q_len - q0 < TC_TOK ? q_len - q0 : TC_TOK;
+    const int last_pos = pos0 + q0 + rows_here - 1;
+    const int n_tiles = last_pos / kKvTile + 1;
+    const int* pt = page_table + (size_t)req_slot[req] * max_pages;
+
+    if (warp == 0) {
+        // ---------------------------------------------------------------- TMA producer
+        if (lane == 0) {
+            mbar_expect_tx(q_full, 2 * TC_HALF_BYTES);
+            tma_tile_3d(q_s, &map_q, 0, kvh * TC_G, q_row0 + q0, q_full);
+            tma_tile_3d(q_s + TC_HALF_BYTES, &map_q, 0, kvh * TC_G, q_row0 + q0 + 32, q_full);
+        }
+        const uint64_t pol = policy_evict_last();            // re-read by the other KV heads' CTAs / later q tiles
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int t0 = 0; t0 < n_tiles; t0 += 32) {
+            const int mine = t0 + lane;
+            const int my_page = mine < n_tiles ? pt[mine] : 0;
+            const int n = n_tiles - t0 < 32 ? n_tiles - t0 : 32;
+            for (int i = 0; i < n; ++i) {
+                const int page = __shfl_sync(0xffffffffu, my_page, i);
+                if (lane == 0) {
+                    mbar_wait_sleep(&kv_empty[stage], phase ^ 1);
+                    mbar_expect_tx(&kv_full[stage], TC_TILE_BYTES);
+                    tma_bulk_g2s(kv_s + (size_t)stage * TC_TILE_BYTES,
+                                 kv_layer + ((size_t)page * nkv + kvh) * TC_TILE_BYTES, TC_TILE_BYTES, &kv_full[stage], pol);
+                }
+                if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ---------------------------------------------------------------- MMA issuer
+        if (elect_one()) {
+            constexpr uint32_t idesc_qk = umma_idesc_f16(TC_ROWS, kKvTile, false);
+            constexpr uint32_t idesc_pv = umma_idesc_f16(TC_ROWS, TC_D, true);
+            const uint32_t q_addr = smem_u32(q_s), p_addr = smem_u32(p_s);
+            auto issue_qk = [&](int h, uint32_t k_addr) {
+                const uint64_t a = umma_desc_k128(q_addr + h * TC_HALF_BYTES), b = umma_desc_k128(k_addr);
+#pragma unroll
+                for (int k = 0; k < TC_D / 16; ++k)
+                    umma_bf16(tmem_base + h * 64, a + 2 * k, b + 2 * k, idesc_qk, k != 0);
+                umma_commit(&s_full[h]);
+            };
+            mbar_wait(q_full, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            mbar_wait(&kv_full[0], 0);
+            tc_fence_after();
+            issue_qk(0, smem_u32(kv_s));
+            issue_qk(1, smem_u32(kv_s));
+            for (int j = 0; j < n_tiles; ++j) {
+                const uint32_t v_addr = smem_u32(kv_s + (size_t)stage * TC_TILE_BYTES) + kKvTile * TC_D * 2;
+                int nstage = stage + 1;
+                uint32_t nphase = phase;
+                if (nstage == TC_STAGES) { nstage = 0; nphase ^= 1; }
+                const bool more = j + 1 < n_tiles;
+                if (more) mbar_wait(&kv_full[nstage], nphase);
+                for (int h = 0; h < 2; ++h) {
+                    mbar_wait(&p_full[h], j & 1);                // P_h(j) written, S_h(j) consumed, O_h rescaled if needed
+                    tc_fence_after();
+                    const uint64_t a = umma_desc_k128(p_addr + h * TC_HALF_BYTES);
+#pragma unroll
+                    for (int k = 0; k < kKvTile / 16; ++k)
+                        umma_bf16(tmem_base + 128 + h * 64, a + 2 * k, umma_desc_mn128(v_addr + k * 2048), idesc_pv,
+                                  (j | k) != 0);
+                    umma_commit(&pv_done[h]);
+                    if (h == 1) umma_commit(&kv_empty[stage]);   // both halves' products on this tile have retired
+                    if (more) issue_qk(h, smem_u32(kv_s + (size_t)nstage * TC_TILE_BYTES));     // S_h is free again
+                }
+                stage = nstage;
+                phase = nphase;
+            }
+        }
+    } else {
+        // ---------------------------------------------------------------- softmax + epilogue (one thread per row)
+        const int h = (warp - 2) >> 2;
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;                     // TMEM lane == row of the half
+        const int tok = h * 32 + (row >> 2);                     // query token within the CTA's 64
+        const int head = kvh * TC_G + (row & 3);
+        const int pos = pos0 + q0 + tok;                         // absolute position of this row's query
+        const bool valid = q0 + tok < q_len;
+        const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        const uint32_t s_taddr = lane_base + h * 64, o_taddr = lane_base + 128 + h * 64;
+        const uint32_t p_row = smem_u32(p_s) + h * TC_HALF_BYTES + row * 128;
+        float m_ref = -INFINITY, l_run = 0.f;                    // m_ref in scaled (log2) units
+        for (int j = 0; j < n_tiles; ++j) {
+            mbar_wait(&s_full[h], j & 1);
+            tc_fence_after();
+            uint32_t sr[64];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) tmem_ld16_nowait(s_taddr + 16 * c, sr + 16 * c);
+            tmem_ld_wait();
+            float tmax = -INFINITY;
+            if (j * kKvTile + kKvTile - 1 > pos) {               // diagonal tile: causal mask
+#pragma unroll
+                for (int c = 0; c < 64; ++c) {
+                    float v = __uint_as_float(sr[c]);
+                    v = j * kKvTile + c <= pos ? v : -INFINITY;
+                    sr[c] = __float_as_uint(v);
+                    tmax = fmaxf(tmax, v);
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < 64; ++c) tmax = fmaxf(tmax, __uint_as_float(sr[c]));
+            }
+            const float m_new = fmaxf(m_ref, tmax * scale_log2);
+            if (j > 0) mbar_wait(&pv_done[h], (j - 1) & 1);      // P buffer free, O_h complete up to tile j - 1
+            const bool grow = m_new > m_ref + TC_RESCALE_THRESHOLD;
+            if (j == 0) {
+                m_ref = m_new;
+            } else if (__any_sync(0xffffffffu, grow)) {          // tcgen05.ld / st are warp-wide: rescale all 32 rows
+                tc_fence_after();
+                const float alpha = exp2f(m_ref - m_new);        // rows that did not grow: m_new >= m_ref, alpha <= 1
+                l_run *= alpha;
+                m_ref = m_new;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t orr[16];
+                    tmem_ld16_nowait(o_taddr + 16 * c, orr);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) orr[k] = __float_as_uint(__uint_as_float(orr[k]) * alpha);
+                    tmem_st16(o_taddr + 16 * c, orr);
+                }
+                tmem_st_wait();
+            }
+            const float mu = m_ref == -INFINITY ? 0.f : m_ref;
+            float psum = 0.f;
+#pragma unroll
+            for (int c8 = 0; c8 < 8; ++c8) {
+                uint32_t pk[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float p0 = exp2f(fmaf(__uint_as_float(sr[c8 * 8 + 2 * e]), scale_log2, -mu));
+                    const float p1 = exp2f(fmaf(__uint_as_float(sr[c8 * 8 + 2 * e + 1]), scale_log2, -mu));
+                    psum += p0 + p1;
+                    __half2 t = __floats2half2_rn(p0, p1);
+                    pk[e] = *reinterpret_cast<uint32_t*>(&t);
+                }
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(p_row + (((uint32_t)c8 ^ (row & 7)) << 4)),
+                             "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
+                             : "memory");
+            }
+            l_run += psum;
+            fence_proxy_async();                                 // generic-proxy stores -> visible to the tensor core
+            tc_fence_before();
+            mbar_arrive(&p_full[h]);
+        }
+        // ---- epilogue: O / l -> bf16 hi + lo planes
+        mbar_wait(&pv_done[h], (n_tiles - 1) & 1);
+        tc_fence_after();
+        const float inv = 1.f / l_run;
+        const size_t off = ((size_t)(q_row0 + q0 + tok) * nq + head) * TC_D;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            uint32_t orr[16];
+            tmem_ld16_nowait(o_taddr + 16 * c, orr);
+            tmem_ld_wait();
+            if (valid) {
+                uint32_t hi[8], lo[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float x = __uint_as_float(orr[2 * k]) * inv, y = __uint_as_float(orr[2 * k + 1]) * inv;
+                    hi[k] = pack_bf16(x, y);
+                    lo[k] = pack_bf16(x - bf16_lo(hi[k]), y - bf16_hi(hi[k]));
+                }
+                uint4* dst = reinterpret_cast<uint4*>(out + off + 16 * c);
+                dst[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                dst[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+                if (out_lo) {
+                    uint4* dl = reinterpret_cast<uint4*>(out_lo + off + 16 * c);
+                    dl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                    dl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+bool attn_prefill_tc_supported(int nq, int nkv, int d) {
+    static const bool off = getenv("FT_ATTN_PREFILL_MMA_SYNC") != nullptr;        // A/B switch (scripts/, tests)
+    return !off && d == TC_D && nkv >= 1 && nq == TC_G * nkv;
+}
+
+// q tensor maps are cached per (device, pointer, rows, heads): the engine's q buffer never moves
+struct QMapEntry { int dev; const void* q; int rows, nq; CUtensorMap map; };
+static std::mutex g_qmap_mu;
+static QMapEntry g_qmaps[16];
+static int g_qmap_n = 0, g_qmap_next = 0;
+
+int launch_attn_prefill_tc(const void* q, int q_rows, const void* kv_layer, const int* page_table, int max_pages,
+                           const int* req_q_start, const int* req_slot, const int* req_pos0, const int* tile_req,
+                           const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq, int nkv, bool pdl,
+                           cudaStream_t stream) {
+    FT_REQUIRE(q_rows >= 1, "attn_prefill (tcgen05): the q buffer's row count is needed for its tensor map");
+    CUtensorMap map;
+    {
+        std::lock_guard<std::mutex> lk(g_qmap_mu);
+        const int dev = current_device_slot();
+        const QMapEntry* hit = nullptr;
+        for (int i = 0; i < g_qmap_n; ++i)
+            if (g_qmaps[i].dev == dev && g_qmaps[i].q == q && g_qmaps[i].rows == q_rows && g_qmaps[i].nq == nq) hit = &g_qmaps[i];
+        if (!hit) {
+            QMapEntry e{dev, q, q_rows, nq, {}};
+            if (int r = make_tmap_f16_3d(&e.map, q, TC_D, nq, q_rows, TC_D, TC_G, 32)) return r;
+            g_qmaps[g_qmap_next] = e;
+            hit = &g_qmaps[g_qmap_next];
+            g_qmap_next = (g_qmap_next + 1) % 16;
+            if (g_qmap_n < 16) ++g_qmap_n;
+        }
+        map = hit->map;
+    }
+    static PerDeviceFlag attr_set;
+    if (!attr_set.done()) {
+        FT_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM));
+        attr_set.mark();
+    }
+    const float scale_log2 = 1.4426950408889634f / sqrtf((float)TC_D);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(n_tiles, nkv);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = TC_SMEM;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_tc_kernel, map, (const uint8_t*)kv_layer, page_table, max_pages,
+                                     req_q_start, req_slot, req_pos0, tile_req, tile_q0, (__nv_bfloat16*)out,
+                                     (__nv_bfloat16*)out_lo, nq, nkv, scale_log2));
+    return 0;
+}
+
+}  // namespace ft

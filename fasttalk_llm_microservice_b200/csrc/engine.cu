@@ -342,7 +342,7 @@ static int forward(Engine* e, const Batch& b) {
             FT_TRY(launch_attn_prefill(e->q, kv_l, d + m.o_pt, e->max_pages, d + m.o_qstart, d + m.o_rslot,
                                        d + m.o_rpos0, d + m.o_treq, d + m.o_tq0, b.n_tiles, e->attn_out,
                                        e->attn_out_lo, c.n_q_heads, c.n_kv_heads, c.head_dim, e->pdl,
-                                       e->stream));
+                                       e->stream, e->t_max));
             e->st.kernel_launches++;
         }
         {

@@ -32,6 +32,7 @@ struct PerDeviceFlag {
 
 // ---- gemm.cu
 int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int box_rows);
+int make_tmap_f16_3d(CUtensorMap* map, const void* base, int d0, int d1, int d2, int b0, int b1, int b2);
 int gemm_pick_bn(int T, bool hilo);
 int gemm_pick_splits(int n_out, int T, int K, int num_sms, bool hilo);
 size_t gemm_scratch_floats(int n_out, int T, int splits, bool hilo);   // split-K slabs of one launch
@@ -69,10 +70,19 @@ int launch_attn_decode(const void* q, const void* kv_layer, const int* page_tabl
                        const int* ctx_lens, const int* tile_prefix, void* out, void* out_lo, float* scratch,
                        int B, int nq, int nkv, int d, int n_ctas, bool pdl, cudaStream_t stream,
                        cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr, bool early = false);
+// q_rows: rows (tokens) the q / out buffers hold — the tcgen05 kernel builds a tensor map over q; <= 0 = unknown,
+// which selects the mma.sync kernel
 int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                         const int* req_q_start, const int* req_slot, const int* req_pos0,
                         const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq,
-                        int nkv, int d, bool pdl, cudaStream_t stream);
+                        int nkv, int d, bool pdl, cudaStream_t stream, int q_rows = 0);
+
+// ---- attention_tc.cu (tcgen05 / TMEM prefill attention: head_dim 64, GQA group 4)
+bool attn_prefill_tc_supported(int nq, int nkv, int d);
+int launch_attn_prefill_tc(const void* q, int q_rows, const void* kv_layer, const int* page_table, int max_pages,
+                           const int* req_q_start, const int* req_slot, const int* req_pos0, const int* tile_req,
+                           const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq, int nkv, bool pdl,
+                           cudaStream_t stream);
 
 // ---- sampling.cu
 int launch_sample(const float* logits, int B, int V, const float* temperature, const int* top_k,

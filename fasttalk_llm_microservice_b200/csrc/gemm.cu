@@ -948,6 +948,22 @@ int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int 
     return 0;
 }
 
+// fp16 tensor [d2][d1][d0] (d0 contiguous), box b0 x b1 x b2, 128-byte swizzle (b0 * 2 bytes must be 128).
+int make_tmap_f16_3d(CUtensorMap* map, const void* base, int d0, int d1, int d2, int b0, int b1, int b2) {
+    PFN_encodeTiled enc = get_encode_fn();
+    FT_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+    FT_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0 && b0 * 2 == 128, "3-D tensor map: bad base / box");
+    cuuint64_t dims[3] = {(cuuint64_t)d0, (cuuint64_t)d1, (cuuint64_t)d2};
+    cuuint64_t strides[2] = {(cuuint64_t)d0 * 2, (cuuint64_t)d0 * d1 * 2};
+    cuuint32_t box[3] = {(cuuint32_t)b0, (cuuint32_t)b1, (cuuint32_t)b2};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    FT_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (3-D) failed (%d) dims=%d,%d,%d", (int)r, d0, d1, d2);
+    return 0;
+}
+
 static int device_sms() {          // of the CURRENT device
     static int sms[kMaxDevices] = {};
     const int slot = current_device_slot();

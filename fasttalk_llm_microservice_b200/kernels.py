@@ -177,7 +177,7 @@ def attn_decode_noalloc(q: torch.Tensor, kv_layer: torch.Tensor, page_table: tor
 
 
 def attn_prefill(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tensor, req_q_start, req_slot,
-                 req_pos0):
+                 req_pos0, tensor_cores: bool = True):
     """q fp16 [T, nq, d]; request r owns rows req_q_start[r]:req_q_start[r+1].  Returns (hi, lo)."""
     assert q.dtype == torch.float16 and kv_layer.dtype == torch.float16
     T, nq, d = q.shape
@@ -193,7 +193,8 @@ def attn_prefill(q: torch.Tensor, kv_layer: torch.Tensor, page_table: torch.Tens
     out_lo = torch.zeros_like(out)
     N.check(N.load().ft_attn_prefill(N.ptr(q), N.ptr(kv_layer), N.ptr(page_table), page_table.shape[1],
                                      N.ptr(t_qs), N.ptr(t_slot), N.ptr(t_pos0), N.ptr(t_treq), N.ptr(t_tq0),
-                                     len(tile_req), N.ptr(out), N.ptr(out_lo), nq, nkv, d, N.cur_stream()),
+                                     len(tile_req), N.ptr(out), N.ptr(out_lo), nq, nkv, d, T if tensor_cores else 0,
+                                     N.cur_stream()),
             "ft_attn_prefill")
     return out, out_lo
 

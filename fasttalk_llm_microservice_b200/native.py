@@ -111,7 +111,7 @@ SIGNATURES = {
     "ft_debug_attn_trace": (_I, [_VP, _I]),
     "ft_attn_decode": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
     "ft_attn_decode_noalloc": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
-    "ft_attn_prefill": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP, _I, _VP, _VP, _I, _I, _I, _VP]),
+    "ft_attn_prefill": (_I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP, _I, _VP, _VP, _I, _I, _I, _I, _VP]),
     "ft_sample": (_I, [_VP, _I, _I, _VP, _VP, _VP, _VP, _VP, _VP]),
 }
 

@@ -306,11 +306,15 @@ int ft_attn_decode_noalloc(const void* q, const void* kv_layer, const int* page_
 
 /* K6: causal chunked-prefill attention over the paged cache.  Request r owns query rows
  * [req_q_start[r], req_q_start[r+1]) of q/out, page-table row req_slot[r], and its first query
- * sits at absolute position req_pos0[r].  Tiles (tile_req, tile_q0) enumerate 64-query blocks. */
+ * sits at absolute position req_pos0[r].  Tiles (tile_req, tile_q0) enumerate 64-query blocks.
+ * q_rows = number of rows (tokens) the q and out buffers hold.  With head_dim 64 and a GQA group of 4
+ * (Llama-3.2-1B) and q_rows > 0 this runs on tcgen05 / TMEM (one CTA per 64 queries x KV head, S and O in
+ * tensor memory, K/V slabs consumed as UMMA operands exactly as they lie in the cache); other shapes, or
+ * q_rows <= 0, run the mma.sync kernel. */
 int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                     const int* req_q_start, const int* req_slot, const int* req_pos0, const int* tile_req,
                     const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq, int nkv, int d,
-                    void* stream);
+                    int q_rows, void* stream);
 
 /* K7: per-row temperature / top-k / top-p sampling (argmax when temperature <= 0). */
 int ft_sample(const float* logits, int B, int V, const float* temperature, const int* top_k,

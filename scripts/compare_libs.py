@@ -138,12 +138,20 @@ def prefill_attention(rows):
         out = torch.zeros(T, nq * d, device=DEV, dtype=torch.bfloat16)
         out_lo = torch.zeros_like(out)
         lib = N.load()
-        ours = lambda: N.check(lib.ft_attn_prefill(N.ptr(q), N.ptr(kv), N.ptr(pt), maxp, N.ptr(t_qs), N.ptr(t_slot),
-                                                   N.ptr(t_pos0), N.ptr(t_treq), N.ptr(t_tq0), len(tile_req), N.ptr(out),
-                                                   N.ptr(out_lo), nq, nkv, d, N.cur_stream()), "ft_attn_prefill")
-        us = timed([ours], iters=20)
+        def ours(q_rows):
+            return lambda: N.check(lib.ft_attn_prefill(N.ptr(q), N.ptr(kv), N.ptr(pt), maxp, N.ptr(t_qs), N.ptr(t_slot),
+                                                       N.ptr(t_pos0), N.ptr(t_treq), N.ptr(t_tq0), len(tile_req), N.ptr(out),
+                                                       N.ptr(out_lo), nq, nkv, d, q_rows, N.cur_stream()), "ft_attn_prefill")
+        us = timed([ours(T)], iters=20)                  # tcgen05 / TMEM kernel
+        hi_tc = out.float() + out_lo.float()
+        us_sync = timed([ours(0)], iters=20)             # the round-1 mma.sync kernel (q_rows = 0 selects it)
+        hi_sync = out.float() + out_lo.float()
         row = {"section": "prefill attention (1B heads)", "shape": label, "GFLOP": flops / 1e9, "ours_us": us,
-               "ours_TFLOPs": flops / us / 1e6, "ours_frac_tensor": flops / us / 1e6 / PEAK_TF}
+               "ours": "attn_prefill_tc_kernel (tcgen05 / TMEM)", "ours_TFLOPs": flops / us / 1e6,
+               "ours_frac_tensor": flops / us / 1e6 / PEAK_TF, "ours_mma_sync_us": us_sync,
+               "ours_mma_sync_TFLOPs": flops / us_sync / 1e6, "tc_over_mma_sync_speedup": us_sync / us,
+               "tc_vs_mma_sync_max_abs_diff": float((hi_tc - hi_sync).abs().max()),
+               "tc_vs_mma_sync_rel": float((hi_tc - hi_sync).abs().max() / hi_sync.abs().max())}
         try:
             import flashinfer
             ws = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
