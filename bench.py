@@ -341,7 +341,7 @@ def run_native(args, rank, world, local_rank):
     for r in rids:
         eng.cancel(r)
     eng.step(); eng.drain()
-    eng.set_decode_prefill_cap(args.prefill_cap)      # serving configuration from here on (0 = the engine default, 1024)
+    eng.set_decode_prefill_cap(args.prefill_cap)      # serving configuration from here on (0 = the engine default, 768)
     # warm the sessions with a known history (prefix reuse needs the cached tokens == re-sent prefix)
     for i in range(SESSIONS):
         eng.close_session(f"s{i}")
@@ -474,7 +474,7 @@ def run_native(args, rank, world, local_rank):
                    "prefix_hit_tokens": h1["prefix_hit_tokens"] - h0["prefix_hit_tokens"],
                    "ttft_ms_p50": 1e3 * pct(h_first, 0.5), "ttft_ms_p99": 1e3 * pct(h_first, 0.99),
                    "itl_ms_p50": 1e3 * pct(h_gaps, 0.5), "itl_ms_p99": 1e3 * pct(h_gaps, 0.99),
-                   "decode_prefill_cap": args.prefill_cap or 1024}
+                   "decode_prefill_cap": args.prefill_cap or 768}
     for i in range(SESSIONS):
         eng.close_session(f"h{i}")
 
@@ -580,7 +580,7 @@ def main():
     ap.add_argument("--no-ws", action="store_true", help="skip the WebSocket-level run")
     ap.add_argument("--tune", action="store_true", help="kernel tuning: print ms/step of the timed decode steps and exit")
     ap.add_argument("--prefill-cap", type=int, default=0,
-                    help="engine decode_prefill_cap for the e2e runs (0 = engine default 1024, < 0 = uncapped)")
+                    help="engine decode_prefill_cap for the e2e runs (0 = engine default 768, < 0 = uncapped)")
     ap.add_argument("--settle", type=float, default=2.0,
                     help="idle seconds between the set-up prefill and the warm-up (power-cap recovery; untimed)")
     args = ap.parse_args()

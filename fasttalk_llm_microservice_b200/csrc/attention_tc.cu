@@ -9,11 +9,12 @@
 //                                           B = the K slab exactly as it lies in the cache: [64 keys][64 d] fp16
 //                                           with chunk ^ (row & 7) IS the K-major SWIZZLE_128B operand layout
 //   softmax      4 warps, one thread per row: tcgen05.ld of the row's 64 scores, running max / sum in fp32,
-//                exp2, P -> fp16 -> shared memory (K-major swizzled rows, the A operand of the next product)
+//                exp2, P -> fp16 -> TENSOR MEMORY (tcgen05.st, row = lane: the A operand of the next product)
 //   O += P V     tcgen05.mma  M128 N64 K64   B = the V slab as it lies in the cache: [64 keys][64 d] is the
 //                                           MN-major SWIZZLE_128B layout (d contiguous, 8-key groups 1 KB apart)
 //
-// S and O live in TMEM (4 x 64 columns).  O is rescaled lazily: the row maximum used for scaling only moves when
+// S (two buffers per half, so the scores of tile j + 1 are ready before the softmax of tile j ends) and O live in
+// TMEM together with two P buffers per half (all 512 columns: S 4 x 64, O 2 x 64, P 4 x 32).  O is rescaled lazily: the row maximum used for scaling only moves when
 // the running maximum exceeds it by more than 2^8 (P stays far inside fp16 range, the accumulation is fp32, the
 // final normalisation uses the same reference — exact arithmetic, not an approximation), so the TMEM round trip
 // of a rescale happens on the first tiles only.  The two halves ping-pong: while the softmax warps of one half
@@ -21,11 +22,14 @@
 //
 // Warp roles (320 threads): warp 0 = TMA producer (Q once, then a ring of 16 KB K|V tiles, one bulk copy each),
 // warp 1 = TMEM owner + MMA issuer (one elected thread), warps 2..5 = softmax / epilogue of half 0, warps 6..9 of
-// half 1 (warp w may touch TMEM lanes 32 * (w % 4) .. +31).
+// half 1 (warp w may touch TMEM lanes 32 * (w % 4) .. +31), one thread per query row.
 //
-// What bounds it: 64 x 256 exponentials per KV tile on the SFU (16 / clk / SM on B200) take ~1024 clk, the four
-// products ~512 clk — the kernel is exp-bound at about half the tensor peak, like every d = 64 attention on
-// this chip.
+// What bounds it (in-kernel clock64 timeline + ncu, profiles/r02_attn_prefill_tc.md): per 64-key tile the softmax
+// warps spend ~1200 clk in the exponentials — 64 x 256 of them at the SFU's 16 / clk / SM — and ~1300 clk in the
+// latency-bound rest (TMEM load ~450, row maximum, hand-over); both halves go through these phases in lock step, so
+// the SFU is busy half of the time and the tensor pipe 14 %.  Tried on top and not kept: two threads per row (16
+// softmax warps), prefetching the next tile's scores into a second register set, starting the halves half a tile
+// apart — each within 7 % either way.  The SFU bound itself is ~1024 clk per tile, i.e. about twice this speed.
 #include "common.cuh"
 #include "ft_internal.h"
 
@@ -42,7 +46,7 @@ constexpr int TC_STAGES = 6;
 constexpr int TC_TILE_BYTES = 2 * kKvTile * TC_D * 2;      // K slab + V slab = 16 KB
 constexpr int TC_HALF_BYTES = TC_ROWS * TC_D * 2;          // 16 KB: a Q half / a P half
 constexpr float TC_RESCALE_THRESHOLD = 8.f;                // log2 units
-constexpr size_t TC_SMEM = 1024 + 2 * TC_HALF_BYTES + 2 * TC_HALF_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES + 256;
+constexpr size_t TC_SMEM = 1024 + 2 * TC_HALF_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES + 512;
 
 // instruction descriptor, kind::f16 with fp16 operands: C = f32 (bit 4), A/B format F16 (0), b_major at bit 16
 __host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N, bool b_mn_major) {
@@ -87,6 +91,24 @@ __device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;                 // SWIZZLE_128B
     return d;
 }
+// D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (P, fp16 pairs packed into 32-bit columns, row = lane) is read
+// from tensor memory, so only V crosses the shared-memory port — with both operands in shared memory an
+// M128 N64 product asks for 192 B/clk, more than the port's 128 B/clk
+__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+        "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// 2^x on the SFU, one instruction: the arguments here are <= 2^8 by construction (lazy rescale) and anything below
+// -126 may flush to zero, so exp2f()'s range fix-up (a compare and two multiplies per element) buys nothing
+__device__ __forceinline__ float ex2_fast(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) __nanosleep(20);
 }
@@ -101,16 +123,15 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* q_s = smem;                                     // [2][128 rows][128 B]
-    uint8_t* p_s = smem + 2 * TC_HALF_BYTES;                 // [2][128 rows][128 B]
-    uint8_t* kv_s = smem + 4 * TC_HALF_BYTES;                // [STAGES][K 8 KB | V 8 KB]
+    uint8_t* kv_s = smem + 2 * TC_HALF_BYTES;                // [STAGES][K 8 KB | V 8 KB]
     uint64_t* bars = reinterpret_cast<uint64_t*>(kv_s + (size_t)TC_STAGES * TC_TILE_BYTES);
     uint64_t* kv_full = bars;                                // [STAGES]
     uint64_t* kv_empty = kv_full + TC_STAGES;                // [STAGES]
     uint64_t* q_full = kv_empty + TC_STAGES;                 // [1]
-    uint64_t* s_full = q_full + 1;                           // [2] scores of half h are in TMEM
-    uint64_t* p_full = s_full + 2;                           // [2] probabilities of half h are in shared memory
-    uint64_t* pv_done = p_full + 2;                          // [2] O += P V of half h retired (P buffer / O are free)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 2);
+    uint64_t* s_full = q_full + 1;                           // [2][2] scores of half h, buffer j & 1, are in TMEM
+    uint64_t* p_full = s_full + 4;                           // [2][2] probabilities of half h, tile parity j & 1, are in TMEM
+    uint64_t* pv_done = p_full + 4;                          // [2][2] O += P V of half h, tile parity j & 1, retired
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 4);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -123,14 +144,17 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
         }
         mbar_init(q_full, 1);
         for (int h = 0; h < 2; ++h) {
-            mbar_init(&s_full[h], 1);
-            mbar_init(&p_full[h], TC_ROWS);
-            mbar_init(&pv_done[h], 1);
+            mbar_init(&s_full[2 * h], 1);
+            mbar_init(&s_full[2 * h + 1], 1);
+            mbar_init(&p_full[2 * h], TC_ROWS / 32);         // one arrival per softmax warp
+            mbar_init(&p_full[2 * h + 1], TC_ROWS / 32);
+            mbar_init(&pv_done[2 * h], 1);
+            mbar_init(&pv_done[2 * h + 1], 1);
         }
         fence_mbar_init();
     }
     if (warp == 1) {
-        tmem_alloc(tmem_slot, 256);
+        tmem_alloc(tmem_slot, 512);
         tmem_relinquish();
     }
     tc_fence_before();
@@ -140,8 +164,11 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
     pdl_wait();
     pdl_launch_dependents();
 
-    const int req = tile_req[blockIdx.x];
-    const int q0 = tile_q0[blockIdx.x];
+    // the engine lists a request's q tiles in order, so the LAST tiles see the most keys: take the list back to
+    // front, otherwise the longest CTAs start last and the grid ends in a long tail
+    const int tile_idx = (int)gridDim.x - 1 - (int)blockIdx.x;
+    const int req = tile_req[tile_idx];
+    const int q0 = tile_q0[tile_idx];
     const int q_row0 = req_q_start[req];
     const int q_len = req_q_start[req + 1] - q_row0;
     const int pos0 = req_pos0[req];
@@ -181,42 +208,49 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
         if (elect_one()) {
             constexpr uint32_t idesc_qk = umma_idesc_f16(TC_ROWS, kKvTile, false);
             constexpr uint32_t idesc_pv = umma_idesc_f16(TC_ROWS, TC_D, true);
-            const uint32_t q_addr = smem_u32(q_s), p_addr = smem_u32(p_s);
-            auto issue_qk = [&](int h, uint32_t k_addr) {
+            const uint32_t q_addr = smem_u32(q_s);
+            auto issue_qk = [&](int h, int buf, uint32_t k_addr) {
                 const uint64_t a = umma_desc_k128(q_addr + h * TC_HALF_BYTES), b = umma_desc_k128(k_addr);
 #pragma unroll
                 for (int k = 0; k < TC_D / 16; ++k)
-                    umma_bf16(tmem_base + h * 64, a + 2 * k, b + 2 * k, idesc_qk, k != 0);
-                umma_commit(&s_full[h]);
+                    umma_bf16(tmem_base + (2 * h + buf) * 64, a + 2 * k, b + 2 * k, idesc_qk, k != 0);
+                umma_commit(&s_full[2 * h + buf]);
             };
+            auto stage_of = [&](int j) { return j % TC_STAGES; };
+            auto k_addr_of = [&](int j) { return smem_u32(kv_s + (size_t)stage_of(j) * TC_TILE_BYTES); };
             mbar_wait(q_full, 0);
-            int stage = 0;
-            uint32_t phase = 0;
-            mbar_wait(&kv_full[0], 0);
-            tc_fence_after();
-            issue_qk(0, smem_u32(kv_s));
-            issue_qk(1, smem_u32(kv_s));
+            // scores run two tiles ahead of the softmax (two S buffers per half): tile j + 2 is issued as soon as the
+            // softmax has read tile j out of the same buffer
+            for (int j = 0; j < 2 && j < n_tiles; ++j) {
+                mbar_wait(&kv_full[stage_of(j)], (j / TC_STAGES) & 1);
+                tc_fence_after();
+                issue_qk(0, j & 1, k_addr_of(j));
+                issue_qk(1, j & 1, k_addr_of(j));
+            }
             for (int j = 0; j < n_tiles; ++j) {
-                const uint32_t v_addr = smem_u32(kv_s + (size_t)stage * TC_TILE_BYTES) + kKvTile * TC_D * 2;
-                int nstage = stage + 1;
-                uint32_t nphase = phase;
-                if (nstage == TC_STAGES) { nstage = 0; nphase ^= 1; }
-                const bool more = j + 1 < n_tiles;
-                if (more) mbar_wait(&kv_full[nstage], nphase);
+                const uint32_t v_addr = k_addr_of(j) + kKvTile * TC_D * 2;
+                const bool more = j + 2 < n_tiles;
                 for (int h = 0; h < 2; ++h) {
-                    mbar_wait(&p_full[h], j & 1);                // P_h(j) written, S_h(j) consumed, O_h rescaled if needed
+                    // Every hand-over has one barrier PER BUFFER (tile parity): the softmax of one half may run up to two
+                    // tiles ahead of what this thread has observed (it is busy with the other half), and a single barrier
+                    // completing two phases unobserved would look "not yet complete" again — a deadlock.
+                    mbar_wait(&p_full[2 * h + (j & 1)], (j >> 1) & 1);   // P_h(j) written, S_h(j) consumed, O_h rescaled if needed
                     tc_fence_after();
-                    const uint64_t a = umma_desc_k128(p_addr + h * TC_HALF_BYTES);
+                    const uint32_t p_tmem = tmem_base + 384 + (2 * h + (j & 1)) * 32;     // 64 fp16 = 32 columns
 #pragma unroll
                     for (int k = 0; k < kKvTile / 16; ++k)
-                        umma_bf16(tmem_base + 128 + h * 64, a + 2 * k, umma_desc_mn128(v_addr + k * 2048), idesc_pv,
-                                  (j | k) != 0);
-                    umma_commit(&pv_done[h]);
-                    if (h == 1) umma_commit(&kv_empty[stage]);   // both halves' products on this tile have retired
-                    if (more) issue_qk(h, smem_u32(kv_s + (size_t)nstage * TC_TILE_BYTES));     // S_h is free again
+                        umma_f16_ts(tmem_base + 256 + h * 64, p_tmem + 8 * k, umma_desc_mn128(v_addr + k * 2048), idesc_pv,
+                                    (j | k) != 0);
+                    umma_commit(&pv_done[2 * h + (j & 1)]);
+                    if (h == 1) umma_commit(&kv_empty[stage_of(j)]);   // every product that reads this stage has been issued
+                    if (more) {
+                        if (h == 0) {
+                            mbar_wait(&kv_full[stage_of(j + 2)], ((j + 2) / TC_STAGES) & 1);
+                            tc_fence_after();
+                        }
+                        issue_qk(h, j & 1, k_addr_of(j + 2));    // S buffer j & 1 of this half is free again
+                    }
                 }
-                stage = nstage;
-                phase = nphase;
             }
         }
     } else {
@@ -229,35 +263,39 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
         const int pos = pos0 + q0 + tok;                         // absolute position of this row's query
         const bool valid = q0 + tok < q_len;
         const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
-        const uint32_t s_taddr = lane_base + h * 64, o_taddr = lane_base + 128 + h * 64;
-        const uint32_t p_row = smem_u32(p_s) + h * TC_HALF_BYTES + row * 128;
+        const uint32_t s_taddr0 = lane_base + 2 * h * 64, o_taddr = lane_base + 256 + h * 64;
+        const uint32_t p_taddr0 = lane_base + 384 + 2 * h * 32;
         float m_ref = -INFINITY, l_run = 0.f;                    // m_ref in scaled (log2) units
         for (int j = 0; j < n_tiles; ++j) {
-            mbar_wait(&s_full[h], j & 1);
+            mbar_wait(&s_full[2 * h + (j & 1)], (j >> 1) & 1);
             tc_fence_after();
+            const uint32_t s_taddr = s_taddr0 + (j & 1) * 64;
             uint32_t sr[64];
 #pragma unroll
             for (int c = 0; c < 4; ++c) tmem_ld16_nowait(s_taddr + 16 * c, sr + 16 * c);
             tmem_ld_wait();
-            float tmax = -INFINITY;
+            float t4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};      // four chains instead of one of 64
             if (j * kKvTile + kKvTile - 1 > pos) {               // diagonal tile: causal mask
 #pragma unroll
                 for (int c = 0; c < 64; ++c) {
                     float v = __uint_as_float(sr[c]);
                     v = j * kKvTile + c <= pos ? v : -INFINITY;
                     sr[c] = __float_as_uint(v);
-                    tmax = fmaxf(tmax, v);
+                    t4[c & 3] = fmaxf(t4[c & 3], v);
                 }
             } else {
 #pragma unroll
-                for (int c = 0; c < 64; ++c) tmax = fmaxf(tmax, __uint_as_float(sr[c]));
+                for (int c = 0; c < 64; ++c) t4[c & 3] = fmaxf(t4[c & 3], __uint_as_float(sr[c]));
             }
+            const float tmax = fmaxf(fmaxf(t4[0], t4[1]), fmaxf(t4[2], t4[3]));
             const float m_new = fmaxf(m_ref, tmax * scale_log2);
-            if (j > 0) mbar_wait(&pv_done[h], (j - 1) & 1);      // P buffer free, O_h complete up to tile j - 1
+            // P has two buffers per half: the one for tile j was last read by the product of tile j - 2
+            if (j > 1) mbar_wait(&pv_done[2 * h + (j & 1)], ((j - 2) >> 1) & 1);
             const bool grow = m_new > m_ref + TC_RESCALE_THRESHOLD;
             if (j == 0) {
                 m_ref = m_new;
             } else if (__any_sync(0xffffffffu, grow)) {          // tcgen05.ld / st are warp-wide: rescale all 32 rows
+                mbar_wait(&pv_done[2 * h + ((j - 1) & 1)], ((j - 1) >> 1) & 1);     // O_h complete up to tile j - 1
                 tc_fence_after();
                 const float alpha = exp2f(m_ref - m_new);        // rows that did not grow: m_new >= m_ref, alpha <= 1
                 l_run *= alpha;
@@ -273,30 +311,31 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                 }
                 tmem_st_wait();
             }
+            const uint32_t p_taddr = p_taddr0 + (j & 1) * 32;
             const float mu = m_ref == -INFINITY ? 0.f : m_ref;
-            float psum = 0.f;
+            float ps[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int c8 = 0; c8 < 8; ++c8) {
-                uint32_t pk[4];
+            for (int c16 = 0; c16 < 2; ++c16) {                  // 32 keys -> 16 packed columns per store
+                uint32_t pk[16];
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float p0 = exp2f(fmaf(__uint_as_float(sr[c8 * 8 + 2 * e]), scale_log2, -mu));
-                    const float p1 = exp2f(fmaf(__uint_as_float(sr[c8 * 8 + 2 * e + 1]), scale_log2, -mu));
-                    psum += p0 + p1;
+                for (int e = 0; e < 16; ++e) {
+                    const float p0 = ex2_fast(fmaf(__uint_as_float(sr[c16 * 32 + 2 * e]), scale_log2, -mu));
+                    const float p1 = ex2_fast(fmaf(__uint_as_float(sr[c16 * 32 + 2 * e + 1]), scale_log2, -mu));
+                    ps[(2 * e) & 3] += p0;
+                    ps[(2 * e + 1) & 3] += p1;
                     __half2 t = __floats2half2_rn(p0, p1);
                     pk[e] = *reinterpret_cast<uint32_t*>(&t);
                 }
-                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(p_row + (((uint32_t)c8 ^ (row & 7)) << 4)),
-                             "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3])
-                             : "memory");
+                tmem_st16(p_taddr + 16 * c16, pk);
             }
-            l_run += psum;
-            fence_proxy_async();                                 // generic-proxy stores -> visible to the tensor core
+            tmem_st_wait();
+            l_run += (ps[0] + ps[1]) + (ps[2] + ps[3]);
             tc_fence_before();
-            mbar_arrive(&p_full[h]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[2 * h + (j & 1)]);
         }
         // ---- epilogue: O / l -> bf16 hi + lo planes
-        mbar_wait(&pv_done[h], (n_tiles - 1) & 1);
+        mbar_wait(&pv_done[2 * h + ((n_tiles - 1) & 1)], ((n_tiles - 1) >> 1) & 1);
         tc_fence_after();
         const float inv = 1.f / l_run;
         const size_t off = ((size_t)(q_row0 + q0 + tok) * nq + head) * TC_D;
@@ -328,7 +367,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 256);
+        tmem_dealloc(tmem_base, 512);
     }
 }
 

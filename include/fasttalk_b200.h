@@ -54,7 +54,7 @@ typedef struct {
     int tp_size, tp_rank;
     /* Prompt tokens a step may admit WHILE other sequences are decoding (they all wait for the step): the
      * latency side of vLLM's --max-num-batched-tokens trade-off (docker-compose.vllm.yml:48).  0 = default
-     * (1024), < 0 = no cap (every step may fill max_batched_tokens).  The cap applies while at least as many
+     * (768), < 0 = no cap (every step may fill max_batched_tokens).  The cap applies while at least as many
      * sequences are decoding as are waiting for their first token; otherwise (nothing decoding, or a burst of
      * arrivals that outnumbers the decoding sequences) the step uses the full max_batched_tokens budget. */
     int decode_prefill_cap;

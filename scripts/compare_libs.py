@@ -235,12 +235,17 @@ def projections(rows):
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "compare_libs.json"))
+    ap.add_argument("--only", default="", help="comma list of: decode, prefill, gemm")
     a = ap.parse_args()
     build.build()
     rows = []
-    guarded("decode attention", decode_attention, rows)
-    guarded("prefill attention", prefill_attention, rows)
-    guarded("projections", projections, rows)
+    only = set(x for x in a.only.split(",") if x)
+    if not only or "decode" in only:
+        guarded("decode attention", decode_attention, rows)
+    if not only or "prefill" in only:
+        guarded("prefill attention", prefill_attention, rows)
+    if not only or "gemm" in only:
+        guarded("projections", projections, rows)
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     with open(a.out, "w") as fh:
         json.dump({"peak_hbm_GBs": PEAK, "peak_bf16_TFLOPs_sustained": PEAK_TF, "rows": rows}, fh, indent=1)
