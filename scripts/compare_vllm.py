@@ -1,0 +1,164 @@
+"""Engine-level comparator against what the reference actually delegates to (round-1 verdict, next #7 ii):
+vLLM (docker-compose.vllm.yml:12,38-53: `--dtype float16 --max-num-seqs .. --max-num-batched-tokens 8192`), the
+version this image ships, on the SAME random-init Llama-3.2-1B weights (exported with checkpoint.save_hf_checkpoint),
+the cfg-2 workload: 64 sessions x 2048-token histories (token ids), greedy, EOS ignored.
+
+  * decode throughput: (time of prompts + N tokens) - (time of prompts + 1 token), both engines the same way
+  * the first 64 greedy tokens of three sessions, vLLM's vs ours — the one pin to the reference's real arithmetic
+    this box can give (vLLM runs fp16 weights; ours bf16 weights with fp16 attention: near-ties may flip)
+
+Each engine runs in its own subprocess with a time limit; a failure is recorded as "unavailable: <why>".
+
+    python scripts/compare_vllm.py [--out gpurun_out/compare_vllm.json] [--limit-s 420]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+MODEL, SESSIONS, CTX, N_NEW = "llama-3.2-1b", 64, 2048, 256
+
+
+def prompts():
+    import torch
+    g = torch.Generator().manual_seed(2048)
+    return [torch.randint(0, 128000, (CTX,), generator=g).tolist() for _ in range(SESSIONS)]
+
+
+def run_ours(out_path):
+    import torch
+    from fasttalk_llm_microservice_b200 import build
+    from fasttalk_llm_microservice_b200.engine import Engine, EngineLimits
+    from fasttalk_llm_microservice_b200.model_spec import get_spec
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    build.build()
+    spec = get_spec(MODEL)
+    w = init_weights(spec, seed=0)                 # CPU generator: the same tensors the checkpoint for vLLM is written from
+    eng = Engine(spec, w, EngineLimits(max_batch=SESSIONS, max_batched_tokens=8192, max_context=CTX + N_NEW + 64,
+                                       decode_prefill_cap=-1), eos_ids=())
+    ps = prompts()
+
+    def timed(n_new, tag):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = eng.generate(ps, max_new_tokens=n_new, sessions=[f"{tag}{i}" for i in range(SESSIONS)], ignore_eos=True)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        for i in range(SESSIONS):
+            eng.close_session(f"{tag}{i}")
+        return dt, out
+    timed(2, "w")                                  # warm-up
+    t1 = min(timed(1, f"a{k}")[0] for k in range(3))
+    tn, toks = min((timed(N_NEW + 1, f"b{k}") for k in range(3)), key=lambda r: r[0])
+    res = {"engine": "fasttalk_b200 (this repository), bf16 weights, fp16 attention, hi+lo activation planes",
+           "prefill_s": t1, "total_s": tn, "decode_tok_s": SESSIONS * N_NEW / (tn - t1),
+           "prefill_tok_s": SESSIONS * CTX / t1, "tokens": {str(i): toks[i][:64] for i in (0, 31, 63)}}
+    with open(out_path, "w") as fh:
+        json.dump(res, fh)
+    eng.close()
+
+
+def run_vllm(out_path, ckpt):
+    import torch
+    from fasttalk_llm_microservice_b200.checkpoint import save_hf_checkpoint
+    from fasttalk_llm_microservice_b200.model_spec import get_spec
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    spec = get_spec(MODEL)
+    if not os.path.exists(os.path.join(ckpt, "model.safetensors")):
+        save_hf_checkpoint(spec, init_weights(spec, seed=0), ckpt)
+    import vllm
+    from vllm import LLM, SamplingParams
+    llm = LLM(model=ckpt, dtype="float16", skip_tokenizer_init=True, max_num_seqs=SESSIONS, max_num_batched_tokens=8192,
+              max_model_len=CTX + N_NEW + 64, gpu_memory_utilization=0.45, enable_prefix_caching=False, seed=0)
+    ps = [{"prompt_token_ids": p} for p in prompts()]
+
+    def timed(n_new):
+        sp = SamplingParams(temperature=0.0, max_tokens=n_new, ignore_eos=True, detokenize=False)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        outs = llm.generate(ps, sp, use_tqdm=False)
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0, [list(o.outputs[0].token_ids) for o in outs]
+    timed(2)
+    t1 = min(timed(1)[0] for _ in range(3))
+    tn, toks = min((timed(N_NEW + 1) for _ in range(3)), key=lambda r: r[0])
+    res = {"engine": f"vLLM {vllm.__version__}, --dtype float16, max_num_seqs {SESSIONS}, max_num_batched_tokens 8192, "
+                     "prefix caching off, CUDA graphs on (defaults)",
+           "prefill_s": t1, "total_s": tn, "decode_tok_s": SESSIONS * N_NEW / (tn - t1),
+           "prefill_tok_s": SESSIONS * CTX / t1, "tokens": {str(i): toks[i][:64] for i in (0, 31, 63)}}
+    with open(out_path, "w") as fh:
+        json.dump(res, fh)
+
+
+def run_hf(out_path, ckpt):
+    """transformers' own LlamaForCausalLM on the same checkpoint files, fp32 on the GPU: the arbiter when the two
+    engines disagree (greedy, sessions 0 / 31 / 63, 16 tokens)."""
+    import torch
+    from transformers import AutoModelForCausalLM
+    m = AutoModelForCausalLM.from_pretrained(ckpt, torch_dtype=torch.float32).cuda().eval()
+    ps = prompts()
+    toks = {}
+    with torch.no_grad():
+        for i in (0, 31, 63):
+            ids = torch.tensor([ps[i]], device="cuda")
+            out = m.generate(ids, max_new_tokens=16, do_sample=False, pad_token_id=0)
+            toks[str(i)] = out[0, len(ps[i]):].tolist()
+    with open(out_path, "w") as fh:
+        json.dump({"engine": "transformers LlamaForCausalLM fp32 (GPU), same checkpoint files", "tokens": toks}, fh)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "compare_vllm.json"))
+    ap.add_argument("--limit-s", type=int, default=420)
+    ap.add_argument("--role", default="")
+    ap.add_argument("--tmp", default="/tmp/ft_vllm_cmp")
+    a = ap.parse_args()
+    os.makedirs(a.tmp, exist_ok=True)
+    if a.role == "ours":
+        run_ours(os.path.join(a.tmp, "ours.json")); sys.exit(0)
+    if a.role == "vllm":
+        run_vllm(os.path.join(a.tmp, "vllm.json"), os.path.join(a.tmp, "ckpt")); sys.exit(0)
+    if a.role == "hf":
+        run_hf(os.path.join(a.tmp, "hf.json"), os.path.join(a.tmp, "ckpt")); sys.exit(0)
+    result = {"workload": f"{MODEL} random-init seed 0, {SESSIONS} sessions x {CTX}-token prompts, greedy, {N_NEW} tokens"}
+    for role in ("ours", "vllm", "hf"):
+        t0 = time.time()
+        try:
+            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--role", role, "--tmp", a.tmp],
+                               capture_output=True, text=True, timeout=a.limit_s, cwd=ROOT)
+            if r.returncode != 0:
+                tail = (r.stderr or r.stdout).strip().splitlines()[-12:]
+                result[role] = {"unavailable": f"exit {r.returncode}: " + " | ".join(tail)[-900:]}
+            else:
+                with open(os.path.join(a.tmp, role + ".json")) as fh:
+                    result[role] = json.load(fh)
+        except subprocess.TimeoutExpired:
+            result[role] = {"unavailable": f"did not finish within the {a.limit_s} s time box"}
+        result[role]["wall_s"] = time.time() - t0
+    o, v = result.get("ours", {}), result.get("vllm", {})
+    if "tokens" in o and "tokens" in v:
+        agree = {}
+        for k in o["tokens"]:
+            x, y = o["tokens"][k], v["tokens"][k]
+            n = next((i for i, (p, q) in enumerate(zip(x, y)) if p != q), min(len(x), len(y)))
+            agree[k] = {"first_mismatch": n, "equal_of_64": sum(int(p == q) for p, q in zip(x, y))}
+        result["greedy_agreement_first_64"] = agree
+        hf = result.get("hf", {})
+        if "tokens" in hf:
+            def first_diff(x, y):
+                return next((i for i, (p, q) in enumerate(zip(x, y)) if p != q), min(len(x), len(y)))
+            result["vs_transformers_fp32_first_16"] = {
+                k: {"ours_first_mismatch": first_diff(o["tokens"][k], hf["tokens"][k]),
+                    "vllm_first_mismatch": first_diff(v["tokens"][k], hf["tokens"][k])} for k in hf["tokens"]}
+        result["decode_speedup_over_vllm"] = o["decode_tok_s"] / v["decode_tok_s"]
+        result["prefill_speedup_over_vllm"] = o["prefill_tok_s"] / v["prefill_tok_s"]
+    os.makedirs(os.path.dirname(a.out), exist_ok=True)
+    with open(a.out, "w") as fh:
+        json.dump(result, fh, indent=1)
+    print(json.dumps({k: (val if k not in ("ours", "vllm") else {kk: vv for kk, vv in val.items() if kk != "tokens"})
+                      for k, val in result.items() if k != "hf"}, indent=1))
