@@ -328,10 +328,13 @@ def run_native(args, rank, world, local_rank):
     layer_kv_bytes = spec.kv_bytes_per_token() // spec.layers
     attn_bytes_per_launch = kv_tok / max(n_l, 1) * layer_kv_bytes
     attn_achieved = attn_bytes_per_launch / (attn_ms / max(n_l, 1) * 1e-3) / 1e9 if attn_ms > 0 else 0.0
-    # DRAM traffic of that kernel from the committed `ncu --set full` capture of the same workload
-    # (profiles/r01_ncu_final.md); null when the capture is for another shape
+    # DRAM traffic of that kernel from the newest committed `ncu --set full` capture of the same workload
+    # (profiles/rNN_attn_traffic.json, written from profiles/rNN_ncu_decode.md); null when there is none for this
+    # shape.  It is a per-round capture, not a live counter: the kernel's source hash is recorded beside it.
     traffic, traffic_src = None, None
-    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_attn_traffic.json")
+    import glob
+    cands = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r*_attn_traffic.json")))
+    tpath = cands[-1] if cands else ""
     if MODEL == "llama-3.2-1b" and SESSIONS == 64 and CTX == 2048 and os.path.exists(tpath):
         with open(tpath) as f:
             tj = json.load(f)
