@@ -48,11 +48,6 @@ constexpr int TC_HALF_BYTES = TC_ROWS * TC_D * 2;          // 16 KB: a Q half / 
 constexpr float TC_RESCALE_THRESHOLD = 8.f;                // log2 units
 constexpr size_t TC_SMEM = 1024 + 2 * TC_HALF_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES + 512;
 
-// instruction descriptor, kind::f16 with fp16 operands: C = f32 (bit 4), A/B format F16 (0), b_major at bit 16
-__host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N, bool b_mn_major) {
-    return (1u << 4) | ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
-
 __device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 "

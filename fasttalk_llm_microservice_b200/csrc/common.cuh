@@ -266,6 +266,11 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
            ((uint32_t)(M >> 4) << 24);
 }
 
+// the same with fp16 operands (A / B format F16 = 0); b_mn_major: B is an MN-major tile (bit 16)
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N, bool b_mn_major = false) {
+    return (1u << 4) | ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
 // ------------------------------------------------------------------ mma.sync path (attention)
 __device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& r0, uint32_t& r1,
                                             uint32_t& r2, uint32_t& r3) {

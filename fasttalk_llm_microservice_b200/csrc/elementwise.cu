@@ -358,6 +358,45 @@ int launch_silu_mul(const float* gu, int n_splits, size_t split_stride, void* ac
     return 0;
 }
 
+// fp16(hi + lo) of two bf16 planes (lo may be null: plain bf16 -> fp16, used once for the weights).  Large prefill
+// projections multiply ONE fp16 activation plane against fp16 copies of the weights (engine, prefill_planes = 3):
+// 11 mantissa bits in one tensor-core pass instead of 16 in two.  Saturating, eight elements per thread.
+__global__ void __launch_bounds__(256)
+planes_to_f16_kernel(const uint4* __restrict__ hi, const uint4* __restrict__ lo, uint4* __restrict__ out, size_t n8) {
+    pdl_wait();
+    pdl_launch_dependents();
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 a = hi[i];
+        uint4 b = make_uint4(0u, 0u, 0u, 0u);
+        if (lo) b = lo[i];
+        uint4 o;
+        o.x = pack_f16_sat(bf16_lo(a.x) + bf16_lo(b.x), bf16_hi(a.x) + bf16_hi(b.x));
+        o.y = pack_f16_sat(bf16_lo(a.y) + bf16_lo(b.y), bf16_hi(a.y) + bf16_hi(b.y));
+        o.z = pack_f16_sat(bf16_lo(a.z) + bf16_lo(b.z), bf16_hi(a.z) + bf16_hi(b.z));
+        o.w = pack_f16_sat(bf16_lo(a.w) + bf16_lo(b.w), bf16_hi(a.w) + bf16_hi(b.w));
+        out[i] = o;
+    }
+}
+
+int launch_planes_to_f16(const void* hi, const void* lo, void* out, size_t n_elems, bool pdl, cudaStream_t stream) {
+    FT_REQUIRE(n_elems % 8 == 0, "planes_to_f16: element count must be a multiple of 8");
+    const size_t n8 = n_elems / 8;
+    size_t blocks = (n8 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks == 0) return 0;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3(256);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, planes_to_f16_kernel, (const uint4*)hi, (const uint4*)lo, (uint4*)out, n8));
+    return 0;
+}
+
 }  // namespace ft
 
 // ------------------------------------------------------------------ C ABI (kernel level)

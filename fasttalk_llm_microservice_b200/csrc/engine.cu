@@ -82,7 +82,12 @@ struct Engine {
     int q_dim, kv_dim, qkv_dim, group, max_pages, t_max, r_max, logit_rows;
     int attn_ctas = 0;
     int decode_prefill_cap = 0;            // prompt tokens admitted per step while sequences are decoding (0 = no cap)
-    int prefill_planes = 2;                // activation planes of the multi-wave prefill GEMMs (1 = hi only)
+    int prefill_planes = 2;                // activation planes of the multi-wave prefill GEMMs (1 = hi only, 3 = one fp16 plane)
+    // prefill_planes == 3: fp16 copies of the four projections' weights and fp16 staging planes of their inputs
+    void *w16_qkv = nullptr, *w16_o = nullptr, *w16_gu = nullptr, *w16_d = nullptr;
+    void *x16_xn = nullptr, *x16_attn = nullptr, *x16_act = nullptr;
+    std::vector<CUtensorMap> m16_wqkv, m16_wo, m16_wgu, m16_wd;
+    CUtensorMap m16_xn[2], m16_attn[2], m16_act[2];      // token boxes of 128 and 64 rows
     size_t kv_layer_bytes = 0;
 
     // device buffers
@@ -138,7 +143,7 @@ struct Engine {
     std::deque<StepRec> step_log;          // most recent kStepTimes steps, oldest first
 };
 constexpr size_t kStepTimes = 4096;
-constexpr int kDefaultPrefillPlanes = 2;
+constexpr int kDefaultPrefillPlanes = 3;      // one fp16 plane x fp16 weight copies in the large prefill GEMMs (measured: DESIGN.md §2)
 constexpr int kDefaultDecodePrefillCap = 768;    // a 64-row 1B step with 768 prompt tokens beside it takes ~5.5 ms (1024: ~7)
 
 // Every entry point that touches CUDA makes the engine's device current for its duration: the caller may be a
@@ -249,14 +254,21 @@ struct Batch {
 
 // One projection with a fused epilogue.  `staged` epilogues (RESID / QKV_ROPE) split K across
 // one wave of CTAs that rendezvous in the epilogue; the others run unsplit.
+struct F16Path {                 // the fp16 single-plane form of one projection (prefill_planes == 3); null maps = not available
+    const CUtensorMap* mw = nullptr;
+    const CUtensorMap* mx = nullptr;         // [2]: 128- and 64-row boxes
+    const void *hi = nullptr, *lo = nullptr;
+    void* x16 = nullptr;
+};
+
 static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, const CUtensorMap* xmaps_lo,
-                    int T, int n_out, int K, ft_gemm_epilogue epi) {
+                    int T, int n_out, int K, ft_gemm_epilogue epi, const F16Path* f16 = nullptr) {
     const int bn = gemm_pick_bn(T, true);
     const bool staged = epi.mode == FT_EPI_RESID || epi.mode == FT_EPI_QKV_ROPE;
     const int splits = staged ? gemm_pick_splits(n_out, T, K, e->sms, true) : 1;
     epi.scratch = e->gemm_scratch;
     epi.sync = e->gemm_sync;
-    epi.x_planes = e->prefill_planes;
+    epi.x_planes = e->prefill_planes == 3 ? 2 : e->prefill_planes;
     if (staged && splits > 1) {              // launches are stream-ordered and each epilogue waits for its predecessor
         epi.sync_mode = 1 + e->sync_parity;
         epi.sync_slots = e->sms;
@@ -275,6 +287,14 @@ static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, 
         FT_REQUIRE(ctas < kTpFlags, "engine: %d CTAs exceed the tensor-parallel arrival words", ctas);
     }
     e->st.kernel_launches++;
+    if (f16 && f16->mw && e->prefill_planes == 3 && splits == 1 && gemm_pair_eligible(n_out, T)) {
+        // large prefill projection: ONE fp16 plane (= fp16(hi + lo), staged by a small kernel) against fp16 weights
+        FT_TRY(launch_planes_to_f16(f16->hi, f16->lo, f16->x16, (size_t)T * K, e->pdl, e->stream));
+        e->st.kernel_launches++;
+        epi.x_planes = 3;
+        return launch_gemm(*f16->mw, f16->mx[0], &f16->mx[0], bn, n_out, T, K, 1, epi, e->pdl, e->stream, &f16->mx[1],
+                           &f16->mx[1]);
+    }
     return launch_gemm(mw, xmaps[bn_index(bn)], &xmaps_lo[bn_index(bn)], bn, n_out, T, K, splits, epi, e->pdl,
                        e->stream, &xmaps[bn_index(64)], &xmaps_lo[bn_index(64)]);
 }
@@ -302,6 +322,7 @@ static int forward(Engine* e, const Batch& b) {
     }
     // L2 prefetch of the next projection's weights only pays when the GEMMs are latency-bound
     const bool decode_only = b.n_tiles == 0 && T <= 128;
+    const bool use16 = e->prefill_planes == 3 && e->w16_qkv != nullptr && T > 128;
     ft_gemm_epilogue rstd = {};            // fields shared by every epilogue that applies 1/rms
     rstd.ssq_in = e->ssq;
     rstd.ssq_parts = e->ssq_parts;
@@ -324,7 +345,8 @@ static int forward(Engine* e, const Batch& b) {
             ep.nq = c.n_q_heads;
             ep.nkv = c.n_kv_heads;
             ep.head_dim = c.head_dim;
-            FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, e->m_xn_lo, T, e->qkv_dim, c.hidden, ep));
+            const F16Path f = {use16 ? &e->m16_wqkv[l] : nullptr, e->m16_xn, e->xn, e->xn_lo, e->x16_xn};
+            FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, e->m_xn_lo, T, e->qkv_dim, c.hidden, ep, &f));
         }
         if (b.n_decode > 0) {
             cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -359,7 +381,8 @@ static int forward(Engine* e, const Batch& b) {
                 ep.prefetch = bf16_off(e->w.wgu, (size_t)l * 2 * c.ffn * H);
                 ep.prefetch_bytes = (long long)2 * c.ffn * H * 2;
             }
-            FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, e->m_attn_lo, T, c.hidden, e->q_dim, ep));
+            const F16Path f = {use16 ? &e->m16_wo[l] : nullptr, e->m16_attn, e->attn_out, e->attn_out_lo, e->x16_attn};
+            FT_TRY(run_gemm(e, e->m_wo[l], e->m_attn, e->m_attn_lo, T, c.hidden, e->q_dim, ep, &f));
         }
         {   // gate/up projection: 1/rms and SwiGLU in the epilogue, act = silu(g) * u
             ft_gemm_epilogue ep = rstd;
@@ -370,7 +393,8 @@ static int forward(Engine* e, const Batch& b) {
                 ep.prefetch = bf16_off(e->w.wd, (size_t)l * c.ffn * H);
                 ep.prefetch_bytes = (long long)c.ffn * H * 2;
             }
-            FT_TRY(run_gemm(e, e->m_wgu[l], e->m_xn, e->m_xn_lo, T, 2 * c.ffn, c.hidden, ep));
+            const F16Path f = {use16 ? &e->m16_wgu[l] : nullptr, e->m16_xn, e->xn, e->xn_lo, e->x16_xn};
+            FT_TRY(run_gemm(e, e->m_wgu[l], e->m_xn, e->m_xn_lo, T, 2 * c.ffn, c.hidden, ep, &f));
         }
         {
             ft_gemm_epilogue ep = {};
@@ -385,7 +409,8 @@ static int forward(Engine* e, const Batch& b) {
                 ep.prefetch = bf16_off(e->w.wqkv, (size_t)(l + 1) * e->qkv_dim * H);
                 ep.prefetch_bytes = (long long)e->qkv_dim * H * 2;
             }
-            FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, e->m_act_lo, T, c.hidden, c.ffn, ep));
+            const F16Path f = {use16 ? &e->m16_wd[l] : nullptr, e->m16_act, e->act, e->act_lo, e->x16_act};
+            FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, e->m_act_lo, T, c.hidden, c.ffn, ep, &f));
         }
     }
     if (b.n_logit_rows > 0) {
@@ -698,9 +723,10 @@ static int engine_init(Engine* e) {
     e->r_max = c.max_batch;
     e->logit_rows = std::max(c.max_batch, c.debug_logit_rows);
     e->pdl = c.use_pdl != 0;
-    e->prefill_planes = c.prefill_planes == 1 ? 1 : c.prefill_planes == 2 ? 2 : kDefaultPrefillPlanes;
+    e->prefill_planes = c.prefill_planes >= 1 && c.prefill_planes <= 3 ? c.prefill_planes : kDefaultPrefillPlanes;
     if (const char* ov = getenv("FT_PREFILL_PLANES"))       // A/B switch for experiments (scripts/)
-        if (atoi(ov) == 1 || atoi(ov) == 2) e->prefill_planes = atoi(ov);
+        if (atoi(ov) >= 1 && atoi(ov) <= 3) e->prefill_planes = atoi(ov);
+    if (e->tp > 1 && e->prefill_planes == 3) e->prefill_planes = 2;      // the fp16 form is built for single-GPU engines
     e->decode_prefill_cap = c.decode_prefill_cap == 0 ? kDefaultDecodePrefillCap : c.decode_prefill_cap < 0 ? 0 : c.decode_prefill_cap;
     e->tp = c.tp_size > 1 ? c.tp_size : 1;
     FT_REQUIRE(e->tp <= 2 && c.tp_rank >= 0 && c.tp_rank < e->tp, "engine: tensor parallelism is built for 2 ranks");
@@ -804,6 +830,34 @@ static int engine_init(Engine* e) {
         FT_TRY(make_tmap_bf16_k64(&e->m_last[i], e->xn_last, (int)rows_last, c.hidden, kBns[i]));
         FT_TRY(make_tmap_bf16_k64(&e->m_last_lo[i], e->xn_last_lo, (int)rows_last, c.hidden, kBns[i]));
     }
+    if (e->prefill_planes == 3) {
+        // fp16 copies of the projection weights (bf16 -> fp16 is exact for every weight above fp16's subnormal range) and
+        // fp16 staging planes of their inputs
+        auto to16 = [&](void** dst, const void* src, size_t elems) -> int {
+            FT_CHECK_CUDA(cudaMalloc(dst, elems * 2));
+            return launch_planes_to_f16(src, nullptr, *dst, elems, false, e->stream);
+        };
+        FT_TRY(to16(&e->w16_qkv, e->w.wqkv, L * e->qkv_dim * c.hidden));
+        FT_TRY(to16(&e->w16_o, e->w.wo, L * (size_t)c.hidden * e->q_dim));
+        FT_TRY(to16(&e->w16_gu, e->w.wgu, L * 2 * (size_t)c.ffn * c.hidden));
+        FT_TRY(to16(&e->w16_d, e->w.wd, L * (size_t)c.hidden * c.ffn));
+        FT_TRY(alloc_zero(&e->x16_xn, T * c.hidden * 2));
+        FT_TRY(alloc_zero(&e->x16_attn, T * e->q_dim * 2));
+        FT_TRY(alloc_zero(&e->x16_act, T * c.ffn * 2));
+        e->m16_wqkv.resize(L); e->m16_wo.resize(L); e->m16_wgu.resize(L); e->m16_wd.resize(L);
+        for (size_t l = 0; l < L; ++l) {
+            FT_TRY(make_tmap_bf16_k64(&e->m16_wqkv[l], at(e->w16_qkv, l * e->qkv_dim * c.hidden), e->qkv_dim, c.hidden, 128));
+            FT_TRY(make_tmap_bf16_k64(&e->m16_wo[l], at(e->w16_o, l * (size_t)c.hidden * e->q_dim), c.hidden, e->q_dim, 128));
+            FT_TRY(make_tmap_bf16_k64(&e->m16_wgu[l], at(e->w16_gu, l * 2 * (size_t)c.ffn * c.hidden), 2 * c.ffn, c.hidden, 128));
+            FT_TRY(make_tmap_bf16_k64(&e->m16_wd[l], at(e->w16_d, l * (size_t)c.hidden * c.ffn), c.hidden, c.ffn, 128));
+        }
+        const int boxes[2] = {128, 64};
+        for (int i = 0; i < 2; ++i) {         // 16-bit tiles: the tensor map only moves bits, the MMA descriptor names the type
+            FT_TRY(make_tmap_bf16_k64(&e->m16_xn[i], e->x16_xn, (int)T, c.hidden, boxes[i]));
+            FT_TRY(make_tmap_bf16_k64(&e->m16_attn[i], e->x16_attn, (int)T, e->q_dim, boxes[i]));
+            FT_TRY(make_tmap_bf16_k64(&e->m16_act[i], e->x16_act, (int)T, c.ffn, boxes[i]));
+        }
+    }
     e->prof_ev.resize(2 * L);
     for (auto& ev : e->prof_ev) FT_CHECK_CUDA(cudaEventCreate(&ev));
     FT_CHECK_CUDA(cudaEventCreate(&e->t0));
@@ -826,6 +880,8 @@ static void engine_free(Engine* e) {
     cudaFree(e->tp_xchg); cudaFree(e->tp_flags);
     cudaFree(e->xn_lo); cudaFree(e->attn_out_lo); cudaFree(e->act_lo); cudaFree(e->xn_last_lo);
     cudaFree(e->attn_scratch); cudaFree(e->meta.d);
+    cudaFree(e->w16_qkv); cudaFree(e->w16_o); cudaFree(e->w16_gu); cudaFree(e->w16_d);
+    cudaFree(e->x16_xn); cudaFree(e->x16_attn); cudaFree(e->x16_act);
     if (e->meta.h) cudaFreeHost(e->meta.h);
     for (auto ev : e->prof_ev) if (ev) cudaEventDestroy(ev);
     if (e->t0) cudaEventDestroy(e->t0);

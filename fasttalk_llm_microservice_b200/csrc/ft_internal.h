@@ -34,6 +34,7 @@ struct PerDeviceFlag {
 int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int box_rows);
 int make_tmap_f16_3d(CUtensorMap* map, const void* base, int d0, int d1, int d2, int b0, int b1, int b2);
 int gemm_pick_bn(int T, bool hilo);
+bool gemm_pair_eligible(int n_out, int T);      // would launch_gemm run this (hi/lo, unsplit) projection on the CTA-pair kernel?
 int gemm_pick_splits(int n_out, int T, int K, int num_sms, bool hilo);
 size_t gemm_scratch_floats(int n_out, int T, int splits, bool hilo);   // split-K slabs of one launch
 // Modes and fields: ft_gemm_epilogue in include/fasttalk_b200.h.
@@ -57,6 +58,7 @@ int launch_embed_planes(const int* tokens, const void* embed, const void* gamma,
 int launch_gather_planes(const void* x, const void* x_lo, const float* ssq, int ssq_parts, int ssq_stride,
                          const int* row_idx, int n_rows, int h, void* out, void* out_lo, float* ssq_out,
                          int ssq_out_stride, bool pdl, cudaStream_t stream);
+int launch_planes_to_f16(const void* hi, const void* lo, void* out, size_t n_elems, bool pdl, cudaStream_t stream);
 int launch_silu_mul(const float* gu, int n_splits, size_t split_stride, void* act, void* act_lo, int T,
                     int f, bool pdl, cudaStream_t stream);
 

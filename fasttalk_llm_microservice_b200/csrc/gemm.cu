@@ -771,7 +771,7 @@ gemm_persistent_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_c
 // per CTA, per-mode epilogue on the CTA's own 128 rows.  Barriers: TMA of both CTAs counts on the LEADER's
 // full barrier; tcgen05.commit multicasts "stage free" / "accumulator ready" to both; both epilogues report
 // "accumulator drained" to the leader.
-template <int BN, bool HILO>
+template <int BN, bool HILO, bool F16 = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x_half,
                  const __grid_constant__ CUtensorMap map_x_lo_half, const __grid_constant__ ft_gemm_epilogue ep,
@@ -849,7 +849,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
     } else if (warp == 1 && rank == 0) {
         if (elect_one()) {
-            constexpr uint32_t idesc = umma_idesc_bf16(2 * GEMM_BM, BN);
+            constexpr uint32_t idesc = F16 ? umma_idesc_f16(2 * GEMM_BM, BN) : umma_idesc_bf16(2 * GEMM_BM, BN);
             int ct = 0;
             uint32_t use = 0;
             for (int w = cl; w < n_work; w += n_cl, ++use) {
@@ -975,6 +975,12 @@ static int device_sms() {          // of the CURRENT device
         sms[slot] = n;
     }
     return sms[slot];
+}
+
+bool gemm_pair_eligible(int n_out, int T) {
+    static const bool off = getenv("FT_GEMM_NO_PAIR") != nullptr || getenv("FT_GEMM_NO_PERSISTENT") != nullptr;
+    const int bn = gemm_pick_bn(T, true);
+    return !off && bn == 128 && n_out % (2 * GEMM_BM) == 0 && (n_out / GEMM_BM) * ((T + bn - 1) / bn) > device_sms();
 }
 
 // Token tile: with both activation planes a 256-token tile would leave only two pipeline
@@ -1109,7 +1115,7 @@ static int launch_persistent_bn(const CUtensorMap& mw, const CUtensorMap& mx, co
     return 0;
 }
 
-template <int BN, bool HILO>
+template <int BN, bool HILO, bool F16 = false>
 static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const CUtensorMap& mxl_half, int n_out, int T,
                        int K, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream) {
     constexpr int STAGE_BYTES = GEMM_A_BYTES + (HILO ? 2 : 1) * (BN / 2) * GEMM_BK * 2;
@@ -1123,7 +1129,7 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
     static int max_clusters_dev[kMaxDevices] = {};
     int& max_clusters = max_clusters_dev[current_device_slot()];
     if (!max_clusters) {
-        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<BN, HILO>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<BN, HILO, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         cudaLaunchConfig_t q = {};
         q.gridDim = dim3(device_sms() & ~1);
         q.blockDim = dim3(GEMM_THREADS);
@@ -1134,7 +1140,7 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
         q.attrs = qa;
         q.numAttrs = 1;
         int n = 0;
-        if (cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel<BN, HILO>, &q) != cudaSuccess || n <= 0) n = device_sms() / 2;
+        if (cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel<BN, HILO, F16>, &q) != cudaSuccess || n <= 0) n = device_sms() / 2;
         max_clusters = n;
     }
     const int n_work = (n_out / (2 * GEMM_BM)) * ((T + BN - 1) / BN);
@@ -1153,7 +1159,7 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_pair_kernel<BN, HILO>, mw, mx_half, mxl_half, epi, n_out, T, K / GEMM_BK, stages));
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_pair_kernel<BN, HILO, F16>, mw, mx_half, mxl_half, epi, n_out, T, K / GEMM_BK, stages));
     return 0;
 }
 
@@ -1217,12 +1223,18 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
         // x_planes == 1: the multi-wave (prefill) tiles multiply the hi plane only — half the tensor work; the
         // latency-bound decode tiles, where the second product is free, always use both
         const bool one = epi.x_planes == 1;
+        if (epi.x_planes == 3) {      // ONE fp16 activation plane against fp16 weights (the caller passed those maps)
+            if (work256 >= 8LL * (device_sms() / 2))
+                return launch_pair<256, false, true>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
+            return launch_pair<128, false, true>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream);
+        }
         if (work256 >= 8LL * (device_sms() / 2))
             return one ? launch_pair<256, false>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream)
                        : launch_pair<256, true>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
         return one ? launch_pair<128, false>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream)
                    : launch_pair<128, true>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream);
     }
+    FT_REQUIRE(epi.x_planes != 3, "gemm: the fp16 single-plane path exists for the CTA-pair kernel only (check gemm_pair_eligible)");
     if (multiwave && K <= 4096) {
         switch (bn) {
             case 16: return launch_persistent_bn<16>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);

@@ -39,7 +39,7 @@ class EngineLimits:
     max_sessions: int = 0
     use_pdl: bool = True
     decode_prefill_cap: int = 0         # prompt tokens per step while sequences decode: 0 = 768, < 0 = uncapped
-    prefill_planes: int = 0             # activation planes in the large prefill GEMMs: 0 = default, 1 = hi only, 2 = hi + lo
+    prefill_planes: int = 0             # large prefill GEMMs: 0 = default, 1 = bf16 hi only, 2 = bf16 hi + lo, 3 = one fp16 plane x fp16 weight copies
     debug_logit_rows: int = 0
 
 

@@ -58,8 +58,10 @@ typedef struct {
      * sequences are decoding as are waiting for their first token; otherwise (nothing decoding, or a burst of
      * arrivals that outnumbers the decoding sequences) the step uses the full max_batched_tokens budget. */
     int decode_prefill_cap;
-    /* Activation planes the large prefill projections multiply (ft_gemm_epilogue.x_planes): 0 = default, 1 = hi
-     * plane only, 2 = hi + lo.  Decode-sized steps always use both. */
+    /* How the large prefill projections (more tiles than SMs, 128-token tiles) multiply their activations:
+     * 0 = default, 1 = bf16 hi plane only, 2 = bf16 hi + lo planes (two MMAs per tile), 3 = ONE fp16 plane
+     * (fp16(hi + lo), staged by a small kernel) against fp16 copies of the weights the engine makes at creation
+     * (+ 2 bytes per projection weight).  Decode-sized steps always use hi + lo.  Single-GPU engines only for 3. */
     int prefill_planes;
 } ft_engine_config;
 
@@ -237,7 +239,8 @@ typedef struct {
                                   the next one's epilogue starts (stream order + the epilogue's dependency wait) */
     int sync_slots;            /* sync_mode 1 / 2: counter pairs in `sync` */
     int x_planes;              /* 0 / 2: multiply both activation planes everywhere; 1: grids of more tiles than SMs with
-                                  128-token tiles (prefill) multiply the hi plane only — half the tensor work there */
+                                  128-token tiles (prefill) multiply the hi plane only — half the tensor work there;
+                                  3 (engine): x and w are FP16 tensors, one plane, CTA-pair kernel only */
 } ft_gemm_epilogue;
 long long ft_gemm_scratch_bytes(int n_out, int T, int K, int n_splits);
 int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int n_out, int T, int K, int n_splits,

@@ -42,7 +42,7 @@ for name in a.models.split(","):
         ref_tokens, ref_logits = O.greedy_generate(w32, spec, prompt, 16, return_logits=True)
     del w32
     torch.cuda.empty_cache()
-    for planes in (2, 1):
+    for planes in (2, 3, 1):
         eng = Engine(spec, w, EngineLimits(max_batch=4, max_batched_tokens=8192, max_context=a.n + 256,
                                            debug_logit_rows=a.n, prefill_planes=planes, decode_prefill_cap=-1), eos_ids=())
         got = eng.debug_prefill_logits(prompt.tolist(), chunk=a.n)[-256:]
