@@ -287,7 +287,7 @@ static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, 
         FT_REQUIRE(ctas < kTpFlags, "engine: %d CTAs exceed the tensor-parallel arrival words", ctas);
     }
     e->st.kernel_launches++;
-    if (f16 && f16->mw && e->prefill_planes == 3 && splits == 1 && gemm_pair_eligible(n_out, T)) {
+    if (f16 && f16->mw && e->prefill_planes == 3 && gemm_f16_path_ok(n_out, T, K, splits)) {
         // large prefill projection: ONE fp16 plane (= fp16(hi + lo), staged by a small kernel) against fp16 weights
         FT_TRY(launch_planes_to_f16(f16->hi, f16->lo, f16->x16, (size_t)T * K, e->pdl, e->stream));
         e->st.kernel_launches++;

@@ -34,7 +34,8 @@ struct PerDeviceFlag {
 int make_tmap_bf16_k64(CUtensorMap* map, const void* base, int rows, int K, int box_rows);
 int make_tmap_f16_3d(CUtensorMap* map, const void* base, int d0, int d1, int d2, int b0, int b1, int b2);
 int gemm_pick_bn(int T, bool hilo);
-bool gemm_pair_eligible(int n_out, int T);      // would launch_gemm run this (hi/lo, unsplit) projection on the CTA-pair kernel?
+bool gemm_pair_eligible(int n_out, int T);
+bool gemm_f16_path_ok(int n_out, int T, int K, int splits);      // is there a one-fp16-plane form (x_planes = 3) of this launch?      // would launch_gemm run this (hi/lo, unsplit) projection on the CTA-pair kernel?
 int gemm_pick_splits(int n_out, int T, int K, int num_sms, bool hilo);
 size_t gemm_scratch_floats(int n_out, int T, int splits, bool hilo);   // split-K slabs of one launch
 // Modes and fields: ft_gemm_epilogue in include/fasttalk_b200.h.

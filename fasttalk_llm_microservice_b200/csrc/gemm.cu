@@ -431,7 +431,7 @@ __device__ __forceinline__ void gemm_epilogue(const ft_gemm_epilogue& ep, const 
     }
 }
 
-template <int BN, bool HILO>
+template <int BN, bool HILO, bool F16 = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
                          const __grid_constant__ CUtensorMap map_x,
@@ -547,7 +547,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_w,
         }
     } else if (warp == 1) {
         if (elect_one()) {
-            constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN);
+            constexpr uint32_t idesc = F16 ? umma_idesc_f16(GEMM_BM, BN) : umma_idesc_bf16(GEMM_BM, BN);
             int s = 0;
             uint32_t ph = 0;
             for (int i = 0; i < n_iter; ++i) {
@@ -983,6 +983,17 @@ bool gemm_pair_eligible(int n_out, int T) {
     return !off && bn == 128 && n_out % (2 * GEMM_BM) == 0 && (n_out / GEMM_BM) * ((T + bn - 1) / bn) > device_sms();
 }
 
+// Does launch_gemm have a one-fp16-plane form (x_planes = 3) of this launch?  128-token tiles, K unsplit, and either the
+// CTA-pair kernel or the tile-per-CTA kernel would run it (the persistent tile walk is hi + lo only).
+bool gemm_f16_path_ok(int n_out, int T, int K, int splits) {
+    static const bool no_persistent = getenv("FT_GEMM_NO_PERSISTENT") != nullptr;
+    const int bn = gemm_pick_bn(T, true);
+    if (bn != 128 || splits != 1) return false;
+    if (gemm_pair_eligible(n_out, T)) return true;
+    const bool multiwave = !no_persistent && (n_out / GEMM_BM) * ((T + bn - 1) / bn) > device_sms();
+    return !(multiwave && K <= 4096);
+}
+
 // Token tile: with both activation planes a 256-token tile would leave only two pipeline
 // stages in 227 KB of shared memory, so the hi/lo path tops out at 128.
 int gemm_pick_bn(int T, bool hilo) {
@@ -1041,7 +1052,7 @@ static int stage_plan(int n_out, int T, int K, int splits, int* stages_out, size
     return 0;
 }
 
-template <int BN, bool HILO>
+template <int BN, bool HILO, bool F16 = false>
 static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap& mxl, int n_out,
                           int T, int K, int splits, const ft_gemm_epilogue& epi, bool pdl, cudaStream_t stream) {
     int stages = 0;
@@ -1049,11 +1060,11 @@ static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CU
     if (int r = stage_plan<BN, HILO>(n_out, T, K, splits, &stages, &smem)) return r;
     static PerDeviceFlag attr_set;
     if (!attr_set.done()) {
-        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, HILO>,
+        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, HILO, F16>,
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         // without this the driver sizes the shared-memory carve-out for ONE CTA of a ~100 KB launch and
         // the second CTA the multi-wave plan counts on never becomes resident (ncu: occupancy limit 1)
-        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, HILO>,
+        FT_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, HILO, F16>,
                                            cudaFuncAttributePreferredSharedMemoryCarveout,
                                            cudaSharedmemCarveoutMaxShared));
         attr_set.mark();
@@ -1072,7 +1083,7 @@ static int launch_gemm_bn(const CUtensorMap& mw, const CUtensorMap& mx, const CU
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<BN, HILO>, mw, mx, mxl, epi, n_out, T,
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<BN, HILO, F16>, mw, mx, mxl, epi, n_out, T,
                                      K / GEMM_BK, stages));
     return 0;
 }
@@ -1234,7 +1245,11 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
         return one ? launch_pair<128, false>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream)
                    : launch_pair<128, true>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream);
     }
-    FT_REQUIRE(epi.x_planes != 3, "gemm: the fp16 single-plane path exists for the CTA-pair kernel only (check gemm_pair_eligible)");
+    if (epi.x_planes == 3) {          // one fp16 plane x fp16 weights on the tile-per-CTA kernel (grids of at most one wave)
+        FT_REQUIRE(bn == 128 && splits == 1 && !(multiwave && K <= 4096),
+                   "gemm: no fp16 single-plane form of this launch (check gemm_f16_path_ok)");
+        return launch_gemm_bn<128, false, true>(mw, mx, mx, n_out, T, K, 1, epi, pdl, stream);
+    }
     if (multiwave && K <= 4096) {
         switch (bn) {
             case 16: return launch_persistent_bn<16>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
