@@ -726,7 +726,6 @@ static int engine_init(Engine* e) {
     e->prefill_planes = c.prefill_planes >= 1 && c.prefill_planes <= 3 ? c.prefill_planes : kDefaultPrefillPlanes;
     if (const char* ov = getenv("FT_PREFILL_PLANES"))       // A/B switch for experiments (scripts/)
         if (atoi(ov) >= 1 && atoi(ov) <= 3) e->prefill_planes = atoi(ov);
-    if (e->tp > 1 && e->prefill_planes == 3) e->prefill_planes = 2;      // the fp16 form is built for single-GPU engines
     e->decode_prefill_cap = c.decode_prefill_cap == 0 ? kDefaultDecodePrefillCap : c.decode_prefill_cap < 0 ? 0 : c.decode_prefill_cap;
     e->tp = c.tp_size > 1 ? c.tp_size : 1;
     FT_REQUIRE(e->tp <= 2 && c.tp_rank >= 0 && c.tp_rank < e->tp, "engine: tensor parallelism is built for 2 ranks");

@@ -61,7 +61,7 @@ typedef struct {
     /* How the large prefill projections (more tiles than SMs, 128-token tiles) multiply their activations:
      * 0 = default, 1 = bf16 hi plane only, 2 = bf16 hi + lo planes (two MMAs per tile), 3 = ONE fp16 plane
      * (fp16(hi + lo), staged by a small kernel) against fp16 copies of the weights the engine makes at creation
-     * (+ 2 bytes per projection weight).  Decode-sized steps always use hi + lo.  Single-GPU engines only for 3. */
+     * (+ 2 bytes per projection weight).  Decode-sized steps always use hi + lo. */
     int prefill_planes;
 } ft_engine_config;
 
