@@ -573,6 +573,55 @@ def run_native(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_tp(args, rank, world, local_rank):
+    """`--tp 2` (BASELINE configs[3]): Llama-3.1-8B at a 7936-token history, one engine over two GPUs with the all-reduce
+    fused into the row-parallel GEMMs (csrc/gemm.cu), against the same engine on one GPU.  Launch under torchrun with
+    2 ranks.  One JSON line from rank 0; `value` = streamed tok/s at 8 sessions with TP=2."""
+    import torch
+    import torch.distributed as dist
+    assert world == 2, "--tp 2 needs exactly two ranks (torchrun --nproc-per-node 2)"
+    real_stdout, sys.stdout = sys.stdout, sys.stderr
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("gloo")
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import bench_tp
+    from fasttalk_llm_microservice_b200 import build, tp
+    from fasttalk_llm_microservice_b200.engine import Engine, EngineLimits
+    from fasttalk_llm_microservice_b200.model_spec import get_spec
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    if rank == 0:
+        build.build()
+    dist.barrier()
+    spec = get_spec("llama-3.1-8b")
+    w = init_weights(spec, seed=0, device="cuda")
+    lim = EngineLimits(max_batch=8, max_batched_tokens=8192, max_context=8192, decode_prefill_cap=-1)
+    ctx, steps = 7936, max(args.steps, 8)
+    eng = Engine(spec, w, lim, eos_ids=(), tp_rank=rank, tp_size=2)
+    tp.connect(eng)
+    tp2 = []
+    for sessions in (1, 8):
+        dist.barrier()
+        tp2.append(bench_tp.run(eng, sessions, ctx, steps, spec, f"a{sessions}_", 0.5))
+    dist.barrier()
+    eng.close()
+    if rank == 0:
+        one = Engine(spec, w, lim, eos_ids=())
+        tp1 = [bench_tp.run(one, sessions, ctx, steps, spec, f"b{sessions}_", 1.0) for sessions in (1, 8)]
+        one.close()
+        line = {"metric": "Llama-3.1-8B streamed tok/s, 8192-token window, TP=2 over NVLink (BASELINE configs[3])",
+                "value": tp2[1]["tok_s"], "unit": "tok/s", "n_gpus": 2, "steps": steps, "warmup": 8,
+                "ms_per_step": tp2[1]["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": "llama-3.1-8b bf16, 8 sessions at a 7936-token history, one engine over 2 GPUs",
+                           "parallelism": "tp2, all-reduce fused into the row-parallel GEMM epilogues (no collective call)"},
+                "tp2": tp2, "tp1_same_box": tp1,
+                "tp2_over_tp1": [a["tok_s"] / b["tok_s"] for a, b in zip(tp2, tp1)],
+                "exchange_ab": "profiles/r02_tp2.md (fused GEMM + exchange vs GEMM + ncclAllReduce)"}
+        print(json.dumps(line), file=real_stdout, flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -581,6 +630,7 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ws", action="store_true", help="skip the WebSocket-level run")
+    ap.add_argument("--tp", type=int, default=1, help="2 = the Llama-3.1-8B tensor-parallel configuration (torchrun, 2 ranks)")
     ap.add_argument("--tune", action="store_true", help="kernel tuning: print ms/step of the timed decode steps and exit")
     ap.add_argument("--prefill-cap", type=int, default=0,
                     help="engine decode_prefill_cap for the e2e runs (0 = engine default 768, < 0 = uncapped)")
@@ -593,6 +643,9 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.tp == 2:
+        run_tp(args, rank, world, local_rank)
         return
     if world == 1 and args.gpus > 1:
         # launched without torchrun: re-exec under it so `python bench.py --gpus N` works too

@@ -313,11 +313,14 @@ __device__ __forceinline__ uint32_t pack_f16_sat(float lo, float hi) {
     return *reinterpret_cast<uint32_t*>(&t);
 }
 
-// Byte offset of 16-byte chunk `c` of row `r` inside a [rows][D] bf16 KV slab whose chunks
-// are XOR-swizzled in HBM (so a plain bulk copy lands bank-conflict-free for ldmatrix).
+// Byte offset of 16-byte chunk `c` of token row `r` inside the K (or V) slab of one (page, head).  A slab is stored
+// as D / 64 sub-slabs of [64 tokens][64 dims] (128-byte rows), dims 0..63 first, and inside every sub-slab the eight
+// chunks of a row are XOR-swizzled with the row index.  That is (a) conflict-free for ldmatrix after a plain bulk copy
+// and (b) exactly the 128-byte-swizzled UMMA operand layout — K-major for K, MN-major for V — so the tcgen05 attention
+// consumes the cache in place (attention_tc.cu).  For D = 64 there is one sub-slab and this is the round-1 layout.
 template <int D>
 __host__ __device__ __forceinline__ int kv_swizzled_chunk(int r, int c) {
-    return r * (D * 2) + ((c ^ (r & 7)) << 4);
+    return (c >> 3) * (kKvTile * 128) + r * 128 + (((c & 7) ^ (r & 7)) << 4);
 }
 
 }  // namespace ft

@@ -376,7 +376,8 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                     uint8_t* slab = reinterpret_cast<uint8_t*>(ep.kv_layer) +
                                     (((size_t)page * ep.nkv + kvh) * 2 + (region == 2 ? 1 : 0)) *
                                         (size_t)(kKvTile * d * 2);
-                    const int off = r * (d * 2) + ((((i >> 3) ^ (r & 7))) << 4) + (i & 7) * 2;
+                    // sub-slab of 64 dims, 128-byte rows, chunks swizzled with the row (kv_swizzled_chunk in common.cuh)
+                    const int off = (i >> 6) * (kKvTile * 128) + r * 128 + (((((i >> 3) & 7) ^ (r & 7))) << 4) + (i & 7) * 2;
                     *reinterpret_cast<uint2*>(slab + off) = h4;
                 }
             } else if (mode == FT_EPI_SWIGLU) {

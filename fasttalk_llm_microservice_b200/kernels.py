@@ -209,16 +209,25 @@ def sample(logits: torch.Tensor, temperature=None, top_k=None, top_p=None, seeds
 
 
 # ---- KV cache (un)swizzle helpers for tests: logical [tokens, d] <-> stored slab
+# A stored slab is d / 64 sub-slabs of [64 tokens][64 dims]; inside a sub-slab the eight 16-byte chunks of a row are
+# XOR-swizzled with the row index (csrc/common.cuh: kv_swizzled_chunk).  The XOR is an involution.
+def _kv_perm(x: torch.Tensor) -> torch.Tensor:
+    h, rows = x.shape[0], x.shape[1]
+    r = torch.arange(rows, device=x.device)[None, :, None]
+    c = torch.arange(8, device=x.device)[None, None, :]
+    src = (c ^ (r & 7)).expand(h, rows, 8)
+    return torch.gather(x, 2, src[..., None].expand(h, rows, 8, 8))
+
+
 def kv_slab_logical(slab: torch.Tensor) -> torch.Tensor:
-    """slab [64, d] as stored -> logical [64, d] (undo the 16-byte chunk XOR swizzle)."""
+    """slab [64, d] as stored (memory order [d/64][64][64]) -> logical [64, d]."""
     rows, d = slab.shape
-    chunks = slab.reshape(rows, d // 8, 8)
-    r = torch.arange(rows, device=slab.device)[:, None]
-    c = torch.arange(d // 8, device=slab.device)[None, :]
-    src = c ^ (r & 7)
-    return torch.gather(chunks, 1, src[..., None].expand(-1, -1, 8)).reshape(rows, d)
+    x = slab.reshape(d // 64, rows, 8, 8)
+    return _kv_perm(x).permute(1, 0, 2, 3).reshape(rows, d)
 
 
 def kv_slab_store(logical: torch.Tensor) -> torch.Tensor:
-    """inverse of kv_slab_logical (the XOR is an involution)."""
-    return kv_slab_logical(logical)
+    """inverse of kv_slab_logical: logical [64, d] -> the [64, d]-shaped view of the stored bytes."""
+    rows, d = logical.shape
+    x = logical.reshape(rows, d // 64, 8, 8).permute(1, 0, 2, 3).contiguous()
+    return _kv_perm(x).reshape(rows, d)
