@@ -720,7 +720,7 @@ int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_tab
     FT_REQUIRE(n_tiles >= 1, "attn_prefill: no tiles");
     if (q_rows > 0 && attn_prefill_tc_supported(nq, nkv, d))        // tcgen05 / TMEM kernel (attention_tc.cu)
         return launch_attn_prefill_tc(q, q_rows, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
-                                      tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, pdl, stream);
+                                      tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, d, pdl, stream);
     if (d == 64)
         return launch_attn_prefill_d<64>(q, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0,
                                          tile_req, tile_q0, n_tiles, out, out_lo, nq, nkv, pdl, stream);

@@ -38,15 +38,24 @@
 namespace ft {
 
 constexpr int TC_THREADS = 320;
-constexpr int TC_ROWS = 128;                 // rows per half (UMMA M)
-constexpr int TC_D = 64;
-constexpr int TC_G = 4;                      // q heads per KV head
+constexpr int TC_ROWS = 128;                 // rows per half (UMMA M); 32 tokens x G heads of them are real
 constexpr int TC_TOK = 64;                   // query tokens per CTA
-constexpr int TC_STAGES = 6;
-constexpr int TC_TILE_BYTES = 2 * kKvTile * TC_D * 2;      // K slab + V slab = 16 KB
-constexpr int TC_HALF_BYTES = TC_ROWS * TC_D * 2;          // 16 KB: a Q half / a P half
-constexpr float TC_RESCALE_THRESHOLD = 8.f;                // log2 units
-constexpr size_t TC_SMEM = 1024 + 2 * TC_HALF_BYTES + (size_t)TC_STAGES * TC_TILE_BYTES + 512;
+constexpr int TC_SUB_BYTES = kKvTile * 128;  // one [64 tokens][64 dims] fp16 sub-slab = 8 KB; also 64 rows of a Q block
+constexpr int TC_QBLK_BYTES = TC_ROWS * 128; // one 128-row x 64-dim block of Q = 16 KB
+constexpr float TC_RESCALE_THRESHOLD = 8.f;  // log2 units
+
+template <int D>
+struct TcCfg {
+    static constexpr int KH = D / 64;                                   // 64-dim blocks of the head
+    static constexpr int TILE_BYTES = 2 * KH * TC_SUB_BYTES;             // K slab + V slab: 16 KB (d 64) / 32 KB (d 128)
+    static constexpr int STAGES = D == 64 ? 6 : 4;
+    static constexpr int Q_BYTES = 2 * KH * TC_QBLK_BYTES;               // both halves
+    static constexpr size_t SMEM = 1024 + Q_BYTES + (size_t)STAGES * TILE_BYTES + 512;
+    // TMEM columns: S, two buffers per half, 64 fp32 columns each; P (fp16, 32 columns) is written over the first half
+    // of the S buffer it was computed from; O of the two halves behind them
+    static constexpr int COL_S = 0, COL_O = 256, COLS = 512;
+    static_assert(256 + 2 * D <= 512, "tensor memory");
+};
 
 __device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
     asm volatile(
@@ -80,7 +89,7 @@ __device__ __forceinline__ void tma_tile_3d(void* dst_smem, const CUtensorMap* m
 __device__ __forceinline__ uint64_t umma_desc_mn128(uint32_t smem_addr) {
     uint64_t d = 0;
     d |= (uint64_t)((smem_addr & 0x3ffff) >> 4);
-    d |= (uint64_t)(1024 >> 4) << 16;       // LBO: stride between 64-element MN blocks (only one block here)
+    d |= (uint64_t)(TC_SUB_BYTES >> 4) << 16;   // LBO: stride between 64-element MN blocks = one sub-slab (d = 128: two blocks)
     d |= (uint64_t)(1024 >> 4) << 32;       // SBO: stride between 8-row K groups
     d |= (uint64_t)1 << 46;
     d |= (uint64_t)2 << 61;                 // SWIZZLE_128B
@@ -108,6 +117,7 @@ __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) 
     while (!mbar_try_wait(bar, parity)) __nanosleep(20);
 }
 
+template <int D, int G>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t* __restrict__ kv_layer,
                        const int* __restrict__ page_table, int max_pages, const int* __restrict__ req_q_start,
@@ -115,14 +125,17 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                        const int* __restrict__ tile_req, const int* __restrict__ tile_q0,
                        __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo, int nq, int nkv,
                        float scale_log2) {
+    using C = TcCfg<D>;
+    constexpr int KH = C::KH;
+    constexpr int R = 32 * G;                                 // real rows of a half (row = token * G + head)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* q_s = smem;                                     // [2][128 rows][128 B]
-    uint8_t* kv_s = smem + 2 * TC_HALF_BYTES;                // [STAGES][K 8 KB | V 8 KB]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(kv_s + (size_t)TC_STAGES * TC_TILE_BYTES);
+    uint8_t* q_s = smem;                                     // [2 halves][KH dim blocks][128 rows][128 B]
+    uint8_t* kv_s = smem + C::Q_BYTES;                       // [STAGES][K: KH sub-slabs | V: KH sub-slabs]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(kv_s + (size_t)C::STAGES * C::TILE_BYTES);
     uint64_t* kv_full = bars;                                // [STAGES]
-    uint64_t* kv_empty = kv_full + TC_STAGES;                // [STAGES]
-    uint64_t* q_full = kv_empty + TC_STAGES;                 // [1]
+    uint64_t* kv_empty = kv_full + C::STAGES;                // [STAGES]
+    uint64_t* q_full = kv_empty + C::STAGES;                 // [1]
     uint64_t* s_full = q_full + 1;                           // [2][2] scores of half h, buffer j & 1, are in TMEM
     uint64_t* p_full = s_full + 4;                           // [2][2] probabilities of half h, tile parity j & 1, are in TMEM
     uint64_t* pv_done = p_full + 4;                          // [2][2] O += P V of half h, tile parity j & 1, retired
@@ -133,7 +146,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_q);
-        for (int s = 0; s < TC_STAGES; ++s) {
+        for (int s = 0; s < C::STAGES; ++s) {
             mbar_init(&kv_full[s], 1);
             mbar_init(&kv_empty[s], 1);
         }
@@ -149,8 +162,17 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
         fence_mbar_init();
     }
     if (warp == 1) {
-        tmem_alloc(tmem_slot, 512);
+        tmem_alloc(tmem_slot, C::COLS);
         tmem_relinquish();
+    }
+    if (R < TC_ROWS && warp >= 2) {
+        // a GQA group of 3 fills 96 of a half's 128 rows: the other 32 rows of every Q block are zeroed so that their
+        // (never stored) scores are finite.  Generic-proxy stores, made visible to the tensor core before the barrier.
+        for (int i = threadIdx.x - 64; i < 2 * KH * (TC_ROWS - R) * 8; i += TC_THREADS - 64) {
+            const int blk = i / ((TC_ROWS - R) * 8), rem = i % ((TC_ROWS - R) * 8);
+            *reinterpret_cast<uint4*>(q_s + (size_t)blk * TC_QBLK_BYTES + (R + rem / 8) * 128 + (rem % 8) * 16) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        fence_proxy_async();
     }
     tc_fence_before();
     __syncthreads();
@@ -176,9 +198,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
     if (warp == 0) {
         // ---------------------------------------------------------------- TMA producer
         if (lane == 0) {
-            mbar_expect_tx(q_full, 2 * TC_HALF_BYTES);
-            tma_tile_3d(q_s, &map_q, 0, kvh * TC_G, q_row0 + q0, q_full);
-            tma_tile_3d(q_s + TC_HALF_BYTES, &map_q, 0, kvh * TC_G, q_row0 + q0 + 32, q_full);
+            mbar_expect_tx(q_full, 2 * KH * R * 128);
+            for (int h = 0; h < 2; ++h)
+                for (int kh = 0; kh < KH; ++kh)
+                    tma_tile_3d(q_s + (size_t)(h * KH + kh) * TC_QBLK_BYTES, &map_q, kh * 64, kvh * G, q_row0 + q0 + 32 * h, q_full);
         }
         const uint64_t pol = policy_evict_last();            // re-read by the other KV heads' CTAs / later q tiles
         int stage = 0;
@@ -191,39 +214,43 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                 const int page = __shfl_sync(0xffffffffu, my_page, i);
                 if (lane == 0) {
                     mbar_wait_sleep(&kv_empty[stage], phase ^ 1);
-                    mbar_expect_tx(&kv_full[stage], TC_TILE_BYTES);
-                    tma_bulk_g2s(kv_s + (size_t)stage * TC_TILE_BYTES,
-                                 kv_layer + ((size_t)page * nkv + kvh) * TC_TILE_BYTES, TC_TILE_BYTES, &kv_full[stage], pol);
+                    mbar_expect_tx(&kv_full[stage], C::TILE_BYTES);
+                    tma_bulk_g2s(kv_s + (size_t)stage * C::TILE_BYTES,
+                                 kv_layer + ((size_t)page * nkv + kvh) * C::TILE_BYTES, C::TILE_BYTES, &kv_full[stage], pol);
                 }
-                if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
         // ---------------------------------------------------------------- MMA issuer
         if (elect_one()) {
             constexpr uint32_t idesc_qk = umma_idesc_f16(TC_ROWS, kKvTile, false);
-            constexpr uint32_t idesc_pv = umma_idesc_f16(TC_ROWS, TC_D, true);
+            constexpr uint32_t idesc_pv = umma_idesc_f16(TC_ROWS, D, true);
             const uint32_t q_addr = smem_u32(q_s);
             auto issue_qk = [&](int h, int buf, uint32_t k_addr) {
-                const uint64_t a = umma_desc_k128(q_addr + h * TC_HALF_BYTES), b = umma_desc_k128(k_addr);
 #pragma unroll
-                for (int k = 0; k < TC_D / 16; ++k)
-                    umma_bf16(tmem_base + (2 * h + buf) * 64, a + 2 * k, b + 2 * k, idesc_qk, k != 0);
+                for (int kh = 0; kh < KH; ++kh) {
+                    const uint64_t a = umma_desc_k128(q_addr + (h * KH + kh) * TC_QBLK_BYTES);
+                    const uint64_t b = umma_desc_k128(k_addr + kh * TC_SUB_BYTES);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16(tmem_base + C::COL_S + (2 * h + buf) * 64, a + 2 * k, b + 2 * k, idesc_qk, (kh | k) != 0);
+                }
                 umma_commit(&s_full[2 * h + buf]);
             };
-            auto stage_of = [&](int j) { return j % TC_STAGES; };
-            auto k_addr_of = [&](int j) { return smem_u32(kv_s + (size_t)stage_of(j) * TC_TILE_BYTES); };
+            auto stage_of = [&](int j) { return j % C::STAGES; };
+            auto k_addr_of = [&](int j) { return smem_u32(kv_s + (size_t)stage_of(j) * C::TILE_BYTES); };
             mbar_wait(q_full, 0);
             // scores run two tiles ahead of the softmax (two S buffers per half): tile j + 2 is issued as soon as the
-            // softmax has read tile j out of the same buffer
+            // product of tile j — which reads its P out of the same buffer — has been issued in front of it
             for (int j = 0; j < 2 && j < n_tiles; ++j) {
-                mbar_wait(&kv_full[stage_of(j)], (j / TC_STAGES) & 1);
+                mbar_wait(&kv_full[stage_of(j)], (j / C::STAGES) & 1);
                 tc_fence_after();
                 issue_qk(0, j & 1, k_addr_of(j));
                 issue_qk(1, j & 1, k_addr_of(j));
             }
             for (int j = 0; j < n_tiles; ++j) {
-                const uint32_t v_addr = k_addr_of(j) + kKvTile * TC_D * 2;
+                const uint32_t v_addr = k_addr_of(j) + KH * TC_SUB_BYTES;
                 const bool more = j + 2 < n_tiles;
                 for (int h = 0; h < 2; ++h) {
                     // Every hand-over has one barrier PER BUFFER (tile parity): the softmax of one half may run up to two
@@ -231,19 +258,19 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                     // completing two phases unobserved would look "not yet complete" again — a deadlock.
                     mbar_wait(&p_full[2 * h + (j & 1)], (j >> 1) & 1);   // P_h(j) written, S_h(j) consumed, O_h rescaled if needed
                     tc_fence_after();
-                    const uint32_t p_tmem = tmem_base + 384 + (2 * h + (j & 1)) * 32;     // 64 fp16 = 32 columns
+                    const uint32_t p_tmem = tmem_base + C::COL_S + (2 * h + (j & 1)) * 64;    // 64 fp16 = 32 columns, over S
 #pragma unroll
                     for (int k = 0; k < kKvTile / 16; ++k)
-                        umma_f16_ts(tmem_base + 256 + h * 64, p_tmem + 8 * k, umma_desc_mn128(v_addr + k * 2048), idesc_pv,
+                        umma_f16_ts(tmem_base + C::COL_O + h * D, p_tmem + 8 * k, umma_desc_mn128(v_addr + k * 2048), idesc_pv,
                                     (j | k) != 0);
                     umma_commit(&pv_done[2 * h + (j & 1)]);
                     if (h == 1) umma_commit(&kv_empty[stage_of(j)]);   // every product that reads this stage has been issued
                     if (more) {
                         if (h == 0) {
-                            mbar_wait(&kv_full[stage_of(j + 2)], ((j + 2) / TC_STAGES) & 1);
+                            mbar_wait(&kv_full[stage_of(j + 2)], ((j + 2) / C::STAGES) & 1);
                             tc_fence_after();
                         }
-                        issue_qk(h, j & 1, k_addr_of(j + 2));    // S buffer j & 1 of this half is free again
+                        issue_qk(h, j & 1, k_addr_of(j + 2));    // in order behind the product that read P out of this buffer
                     }
                 }
             }
@@ -253,13 +280,12 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
         const int h = (warp - 2) >> 2;
         const int quarter = warp & 3;
         const int row = quarter * 32 + lane;                     // TMEM lane == row of the half
-        const int tok = h * 32 + (row >> 2);                     // query token within the CTA's 64
-        const int head = kvh * TC_G + (row & 3);
+        const int tok = h * 32 + row / G;                        // query token within the CTA's 64
+        const int head = kvh * G + row % G;
         const int pos = pos0 + q0 + tok;                         // absolute position of this row's query
-        const bool valid = q0 + tok < q_len;
+        const bool valid = row < R && q0 + tok < q_len;
         const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
-        const uint32_t s_taddr0 = lane_base + 2 * h * 64, o_taddr = lane_base + 256 + h * 64;
-        const uint32_t p_taddr0 = lane_base + 384 + 2 * h * 32;
+        const uint32_t s_taddr0 = lane_base + C::COL_S + 2 * h * 64, o_taddr = lane_base + C::COL_O + h * D;
         float m_ref = -INFINITY, l_run = 0.f;                    // m_ref in scaled (log2) units
         for (int j = 0; j < n_tiles; ++j) {
             mbar_wait(&s_full[2 * h + (j & 1)], (j >> 1) & 1);
@@ -284,8 +310,6 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
             }
             const float tmax = fmaxf(fmaxf(t4[0], t4[1]), fmaxf(t4[2], t4[3]));
             const float m_new = fmaxf(m_ref, tmax * scale_log2);
-            // P has two buffers per half: the one for tile j was last read by the product of tile j - 2
-            if (j > 1) mbar_wait(&pv_done[2 * h + (j & 1)], ((j - 2) >> 1) & 1);
             const bool grow = m_new > m_ref + TC_RESCALE_THRESHOLD;
             if (j == 0) {
                 m_ref = m_new;
@@ -296,7 +320,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                 l_run *= alpha;
                 m_ref = m_new;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
+                for (int c = 0; c < D / 16; ++c) {
                     uint32_t orr[16];
                     tmem_ld16_nowait(o_taddr + 16 * c, orr);
                     tmem_ld_wait();
@@ -306,7 +330,6 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                 }
                 tmem_st_wait();
             }
-            const uint32_t p_taddr = p_taddr0 + (j & 1) * 32;
             const float mu = m_ref == -INFINITY ? 0.f : m_ref;
             float ps[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -321,7 +344,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                     __half2 t = __floats2half2_rn(p0, p1);
                     pk[e] = *reinterpret_cast<uint32_t*>(&t);
                 }
-                tmem_st16(p_taddr + 16 * c16, pk);
+                tmem_st16(s_taddr + 16 * c16, pk);               // P over the scores it came from (this row has read them)
             }
             tmem_st_wait();
             l_run += (ps[0] + ps[1]) + (ps[2] + ps[3]);
@@ -333,9 +356,9 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
         mbar_wait(&pv_done[2 * h + ((n_tiles - 1) & 1)], ((n_tiles - 1) >> 1) & 1);
         tc_fence_after();
         const float inv = 1.f / l_run;
-        const size_t off = ((size_t)(q_row0 + q0 + tok) * nq + head) * TC_D;
+        const size_t off = ((size_t)(q_row0 + q0 + tok) * nq + head) * D;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < D / 16; ++c) {
             uint32_t orr[16];
             tmem_ld16_nowait(o_taddr + 16 * c, orr);
             tmem_ld_wait();
@@ -362,37 +385,67 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 512);
+        tmem_dealloc(tmem_base, C::COLS);
     }
 }
 
 // ------------------------------------------------------------------ host side
 bool attn_prefill_tc_supported(int nq, int nkv, int d) {
     static const bool off = getenv("FT_ATTN_PREFILL_MMA_SYNC") != nullptr;        // A/B switch (scripts/, tests)
-    return !off && d == TC_D && nkv >= 1 && nq == TC_G * nkv;
+    return !off && (d == 64 || d == 128) && nkv >= 1 && (nq == 4 * nkv || nq == 3 * nkv);
 }
 
-// q tensor maps are cached per (device, pointer, rows, heads): the engine's q buffer never moves
-struct QMapEntry { int dev; const void* q; int rows, nq; CUtensorMap map; };
+// q tensor maps are cached per (device, pointer, rows, heads, head_dim, group): the engine's q buffer never moves
+struct QMapEntry { int dev; const void* q; int rows, nq, d, g; CUtensorMap map; };
 static std::mutex g_qmap_mu;
 static QMapEntry g_qmaps[16];
 static int g_qmap_n = 0, g_qmap_next = 0;
 
+template <int D, int G>
+static int launch_tc(const CUtensorMap& map, const void* kv_layer, const int* page_table, int max_pages,
+                     const int* req_q_start, const int* req_slot, const int* req_pos0, const int* tile_req,
+                     const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq, int nkv, bool pdl, cudaStream_t stream) {
+    using C = TcCfg<D>;
+    static PerDeviceFlag attr_set;
+    if (!attr_set.done()) {
+        FT_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_tc_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        attr_set.mark();
+    }
+    const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(n_tiles, nkv);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = C::SMEM;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_tc_kernel<D, G>, map, (const uint8_t*)kv_layer, page_table, max_pages,
+                                     req_q_start, req_slot, req_pos0, tile_req, tile_q0, (__nv_bfloat16*)out,
+                                     (__nv_bfloat16*)out_lo, nq, nkv, scale_log2));
+    return 0;
+}
+
 int launch_attn_prefill_tc(const void* q, int q_rows, const void* kv_layer, const int* page_table, int max_pages,
                            const int* req_q_start, const int* req_slot, const int* req_pos0, const int* tile_req,
-                           const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq, int nkv, bool pdl,
+                           const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq, int nkv, int d, bool pdl,
                            cudaStream_t stream) {
     FT_REQUIRE(q_rows >= 1, "attn_prefill (tcgen05): the q buffer's row count is needed for its tensor map");
+    const int g = nq / nkv;
     CUtensorMap map;
     {
         std::lock_guard<std::mutex> lk(g_qmap_mu);
         const int dev = current_device_slot();
         const QMapEntry* hit = nullptr;
         for (int i = 0; i < g_qmap_n; ++i)
-            if (g_qmaps[i].dev == dev && g_qmaps[i].q == q && g_qmaps[i].rows == q_rows && g_qmaps[i].nq == nq) hit = &g_qmaps[i];
+            if (g_qmaps[i].dev == dev && g_qmaps[i].q == q && g_qmaps[i].rows == q_rows && g_qmaps[i].nq == nq &&
+                g_qmaps[i].d == d && g_qmaps[i].g == g)
+                hit = &g_qmaps[i];
         if (!hit) {
-            QMapEntry e{dev, q, q_rows, nq, {}};
-            if (int r = make_tmap_f16_3d(&e.map, q, TC_D, nq, q_rows, TC_D, TC_G, 32)) return r;
+            QMapEntry e{dev, q, q_rows, nq, d, g, {}};
+            if (int r = make_tmap_f16_3d(&e.map, q, d, nq, q_rows, 64, g, 32)) return r;
             g_qmaps[g_qmap_next] = e;
             hit = &g_qmaps[g_qmap_next];
             g_qmap_next = (g_qmap_next + 1) % 16;
@@ -400,26 +453,16 @@ int launch_attn_prefill_tc(const void* q, int q_rows, const void* kv_layer, cons
         }
         map = hit->map;
     }
-    static PerDeviceFlag attr_set;
-    if (!attr_set.done()) {
-        FT_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM));
-        attr_set.mark();
-    }
-    const float scale_log2 = 1.4426950408889634f / sqrtf((float)TC_D);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(n_tiles, nkv);
-    cfg.blockDim = dim3(TC_THREADS);
-    cfg.dynamicSmemBytes = TC_SMEM;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
-    FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_tc_kernel, map, (const uint8_t*)kv_layer, page_table, max_pages,
-                                     req_q_start, req_slot, req_pos0, tile_req, tile_q0, (__nv_bfloat16*)out,
-                                     (__nv_bfloat16*)out_lo, nq, nkv, scale_log2));
-    return 0;
+#define FT_TC_CASE(D_, G_)                                                                                        \
+    if (d == D_ && g == G_)                                                                                       \
+        return launch_tc<D_, G_>(map, kv_layer, page_table, max_pages, req_q_start, req_slot, req_pos0, tile_req,  \
+                                 tile_q0, n_tiles, out, out_lo, nq, nkv, pdl, stream);
+    FT_TC_CASE(64, 4)
+    FT_TC_CASE(64, 3)
+    FT_TC_CASE(128, 4)
+    FT_TC_CASE(128, 3)
+#undef FT_TC_CASE
+    FT_REQUIRE(false, "attn_prefill (tcgen05): head_dim %d with a GQA group of %d is not built", d, g);
 }
 
 }  // namespace ft

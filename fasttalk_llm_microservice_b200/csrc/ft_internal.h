@@ -80,11 +80,11 @@ int launch_attn_prefill(const void* q, const void* kv_layer, const int* page_tab
                         const int* tile_req, const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq,
                         int nkv, int d, bool pdl, cudaStream_t stream, int q_rows = 0);
 
-// ---- attention_tc.cu (tcgen05 / TMEM prefill attention: head_dim 64, GQA group 4)
+// ---- attention_tc.cu (tcgen05 / TMEM prefill attention: head_dim 64 / 128, GQA group 3 / 4)
 bool attn_prefill_tc_supported(int nq, int nkv, int d);
 int launch_attn_prefill_tc(const void* q, int q_rows, const void* kv_layer, const int* page_table, int max_pages,
                            const int* req_q_start, const int* req_slot, const int* req_pos0, const int* tile_req,
-                           const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq, int nkv, bool pdl,
+                           const int* tile_q0, int n_tiles, void* out, void* out_lo, int nq, int nkv, int d, bool pdl,
                            cudaStream_t stream);
 
 // ---- sampling.cu

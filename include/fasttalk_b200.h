@@ -264,7 +264,9 @@ int ft_add_rmsnorm(float* resid, const float* partials, int n_splits, long long 
 
 /* K4: split-K reduce of the fused QKV projection, RoPE on q and k (cos/sin tables fp32
  * [pos][d/2]), q -> FP16 [T][nq][d], k/v -> paged cache layer
- * [page][kv_head][K|V][64][d] FP16 (saturating) with XOR-swizzled 16-byte chunks.  Attention
+ * [page][kv_head][K|V][d/64][64 tokens][64 dims] FP16 (saturating): every K (V) slab is d/64 sub-slabs with
+ * 128-byte token rows whose eight 16-byte chunks are XOR-swizzled with (row & 7) — conflict-free for ldmatrix and
+ * exactly the 128-byte-swizzled UMMA operand layout (tests: kernels.kv_slab_logical / kv_slab_store).  Attention
  * runs in fp16 with fp32 accumulation: same bytes as bf16, three more mantissa bits, and the
  * dtype the reference deploys its engine with (docker-compose.vllm.yml:45 --dtype float16). */
 int ft_rope_kv_append(const float* qkv, int n_splits, long long split_stride, const float* cos_t,
@@ -310,9 +312,9 @@ int ft_attn_decode_noalloc(const void* q, const void* kv_layer, const int* page_
 /* K6: causal chunked-prefill attention over the paged cache.  Request r owns query rows
  * [req_q_start[r], req_q_start[r+1]) of q/out, page-table row req_slot[r], and its first query
  * sits at absolute position req_pos0[r].  Tiles (tile_req, tile_q0) enumerate 64-query blocks.
- * q_rows = number of rows (tokens) the q and out buffers hold.  With head_dim 64 and a GQA group of 4
- * (Llama-3.2-1B) and q_rows > 0 this runs on tcgen05 / TMEM (one CTA per 64 queries x KV head, S and O in
- * tensor memory, K/V slabs consumed as UMMA operands exactly as they lie in the cache); other shapes, or
+ * q_rows = number of rows (tokens) the q and out buffers hold.  With a GQA group of 3 or 4 (Llama-3.2-1B / 3B,
+ * Llama-3.1-8B), head_dim 64 or 128 and q_rows > 0 this runs on tcgen05 / TMEM (one CTA per 64 queries x KV head, S, P
+ * and O in tensor memory, K/V slabs consumed as UMMA operands exactly as they lie in the cache); other shapes, or
  * q_rows <= 0, run the mma.sync kernel. */
 int ft_attn_prefill(const void* q, const void* kv_layer, const int* page_table, int max_pages,
                     const int* req_q_start, const int* req_slot, const int* req_pos0, const int* tile_req,

@@ -10,7 +10,9 @@ import test_kernels_gpu as TK
 build.build()
 DEV = "cuda"
 for nq, nkv, d, reqs in [(8, 2, 64, [(0, 5)]), (8, 2, 64, [(0, 64), (0, 65), (10, 1)]), (32, 8, 64, [(100, 130), (0, 200), (64, 64)]),
-                         (32, 8, 64, [(0, 2048)]), (32, 8, 64, [(1824, 224)] * 3)]:
+                         (32, 8, 64, [(0, 2048)]), (32, 8, 64, [(1824, 224)] * 3),
+                         (3, 1, 128, [(250, 20)]), (24, 8, 128, [(33, 70), (0, 129)]), (32, 8, 128, [(0, 1024)]), (24, 8, 128, [(900, 224)] * 2),
+                         (6, 2, 64, [(100, 130), (0, 65)])]:
     g = torch.Generator(device=DEV).manual_seed(len(reqs) * 31 + nq + d)
     totals = [p + n for p, n in reqs]
     kv, pt, ks, vs = TK.build_paged_kv(K, totals, nkv, d, g)

@@ -109,8 +109,12 @@ def decode_attention(rows):
 
 # ----------------------------------------------------------------------------- prefill attention
 def prefill_attention(rows):
-    nq, nkv, d = 32, 8, 64
-    for label, reqs in (("cold 4 x 2048", [(0, 2048)] * 4), ("warm 36 x 224 new over 1824 cached", [(1824, 224)] * 36)):
+    for heads, nq, nkv, d, label, reqs in (
+            ("1B", 32, 8, 64, "cold 4 x 2048", [(0, 2048)] * 4),
+            ("1B", 32, 8, 64, "warm 36 x 224 new over 1824 cached", [(1824, 224)] * 36),
+            ("3B", 24, 8, 128, "cold 4 x 2048", [(0, 2048)] * 4),
+            ("8B", 32, 8, 128, "cold 4 x 2048", [(0, 2048)] * 4),
+            ("8B", 32, 8, 128, "warm 16 x 224 new over 7712 cached", [(7712, 224)] * 16)):
         g = torch.Generator(device=DEV).manual_seed(2)
         totals = [p + n for p, n in reqs]
         n_pages = [(t + 63) // 64 for t in totals]
@@ -146,7 +150,7 @@ def prefill_attention(rows):
         hi_tc = out.float() + out_lo.float()
         us_sync = timed([ours(0)], iters=20)             # the round-1 mma.sync kernel (q_rows = 0 selects it)
         hi_sync = out.float() + out_lo.float()
-        row = {"section": "prefill attention (1B heads)", "shape": label, "GFLOP": flops / 1e9, "ours_us": us,
+        row = {"section": f"prefill attention ({heads} heads: nq {nq}, nkv {nkv}, d {d})", "shape": label, "GFLOP": flops / 1e9, "ours_us": us,
                "ours": "attn_prefill_tc_kernel (tcgen05 / TMEM)", "ours_TFLOPs": flops / us / 1e6,
                "ours_frac_tensor": flops / us / 1e6 / PEAK_TF, "ours_mma_sync_us": us_sync,
                "ours_mma_sync_TFLOPs": flops / us_sync / 1e6, "tc_over_mma_sync_speedup": us_sync / us,

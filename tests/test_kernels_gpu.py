@@ -456,6 +456,32 @@ def test_attn_prefill(K, nq, nkv, d, reqs):
         assert rel_err(got, ref) < 2e-3, (r, rel_err(got, ref))
 
 
+@pytest.mark.parametrize("nq,nkv,d", [(8, 2, 64), (6, 2, 64), (32, 8, 64), (32, 8, 128), (24, 8, 128), (3, 1, 128)])
+def test_attn_prefill_tcgen05_against_mma_sync_and_oracle(K, nq, nkv, d):
+    """The tcgen05 / TMEM prefill kernel (GQA groups of 3 and 4, head_dim 64 and 128 — the 1B, 3B and 8B shapes) on the
+    same inputs as the round-1 mma.sync kernel (`tensor_cores=False` selects it): cold and prefix-cached requests, ragged
+    query tiles, a single query, a context long enough for the lazy rescale and the ring to wrap several times.  Both
+    against the fp32 oracle, and against each other."""
+    reqs = [(0, 130), (700, 224), (64, 1), (5, 64), (1500, 33)]
+    g = torch.Generator(device=DEV).manual_seed(nq * 13 + d)
+    totals = [p + n for p, n in reqs]
+    kv, pt, ks, vs = build_paged_kv(K, totals, nkv, d, g)
+    q_start = [0]
+    for _, n in reqs:
+        q_start.append(q_start[-1] + n)
+    q = (torch.randn(q_start[-1], nq, d, device=DEV, generator=g) * 1.5).half()      # some spread in the scores
+    args = (q, kv, pt, q_start, list(range(len(reqs))), [p for p, _ in reqs])
+    tc = hilo(*K.attn_prefill(*args, tensor_cores=True))
+    ms = hilo(*K.attn_prefill(*args, tensor_cores=False))
+    torch.cuda.synchronize()
+    assert torch.isfinite(tc).all()
+    assert rel_err(tc, ms) < 1.5e-3, rel_err(tc, ms)
+    for r, (p0, n) in enumerate(reqs):
+        ref = O.attention(q[q_start[r]:q_start[r + 1]].float(), ks[r].float(), vs[r].float(), p0)
+        assert rel_err(tc[q_start[r]:q_start[r + 1]], ref) < 2e-3, (r, rel_err(tc[q_start[r]:q_start[r + 1]], ref))
+        assert rel_err(ms[q_start[r]:q_start[r + 1]], ref) < 2e-3
+
+
 # ------------------------------------------------------------------ K7 sampling
 def test_sample_argmax_matches_torch(K):
     g = torch.Generator(device=DEV).manual_seed(8)
