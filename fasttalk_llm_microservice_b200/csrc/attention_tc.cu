@@ -124,7 +124,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                        const int* __restrict__ req_slot, const int* __restrict__ req_pos0,
                        const int* __restrict__ tile_req, const int* __restrict__ tile_q0,
                        __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ out_lo, int nq, int nkv,
-                       float scale_log2) {
+                       float scale_log2, int stagger_on) {
     using C = TcCfg<D>;
     constexpr int KH = C::KH;
     constexpr int R = 32 * G;                                 // real rows of a half (row = token * G + head)
@@ -139,7 +139,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
     uint64_t* s_full = q_full + 1;                           // [2][2] scores of half h, buffer j & 1, are in TMEM
     uint64_t* p_full = s_full + 4;                           // [2][2] probabilities of half h, tile parity j & 1, are in TMEM
     uint64_t* pv_done = p_full + 4;                          // [2][2] O += P V of half h, tile parity j & 1, retired
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 4);
+    uint64_t* stagger = pv_done + 4;                         // [1] half 0 knows its first row maxima: half 1 may start
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stagger + 1);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -151,6 +152,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
             mbar_init(&kv_empty[s], 1);
         }
         mbar_init(q_full, 1);
+        mbar_init(stagger, TC_ROWS / 32);
         for (int h = 0; h < 2; ++h) {
             mbar_init(&s_full[2 * h], 1);
             mbar_init(&s_full[2 * h + 1], 1);
@@ -247,7 +249,12 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                 mbar_wait(&kv_full[stage_of(j)], (j / C::STAGES) & 1);
                 tc_fence_after();
                 issue_qk(0, j & 1, k_addr_of(j));
-                issue_qk(1, j & 1, k_addr_of(j));
+                if (!stagger_on) issue_qk(1, j & 1, k_addr_of(j));
+            }
+            if (stagger_on) {        // half 1 starts when half 0 is about to enter its SFU-bound phase, so that the two halves'
+                                     // exponentials do not fall on the SFU at the same time (profiles/r02_attn_prefill_tc.md)
+                mbar_wait(stagger, 0);
+                for (int j = 0; j < 2 && j < n_tiles; ++j) issue_qk(1, j & 1, k_addr_of(j));
             }
             for (int j = 0; j < n_tiles; ++j) {
                 const uint32_t v_addr = k_addr_of(j) + KH * TC_SUB_BYTES;
@@ -309,6 +316,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap map_q, const uint8_t*
                 for (int c = 0; c < 64; ++c) t4[c & 3] = fmaxf(t4[c & 3], __uint_as_float(sr[c]));
             }
             const float tmax = fmaxf(fmaxf(t4[0], t4[1]), fmaxf(t4[2], t4[3]));
+            if (stagger_on && j == 0 && h == 0) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(stagger);
+            }
             const float m_new = fmaxf(m_ref, tmax * scale_log2);
             const bool grow = m_new > m_ref + TC_RESCALE_THRESHOLD;
             if (j == 0) {
@@ -412,6 +423,7 @@ static int launch_tc(const CUtensorMap& map, const void* kv_layer, const int* pa
         attr_set.mark();
     }
     const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);
+    static const int stagger_on = getenv("FT_TC_STAGGER") ? atoi(getenv("FT_TC_STAGGER")) : 1;       // A/B switch; measured: 4–6 % at d = 64
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(n_tiles, nkv);
     cfg.blockDim = dim3(TC_THREADS);
@@ -424,7 +436,7 @@ static int launch_tc(const CUtensorMap& map, const void* kv_layer, const int* pa
     cfg.numAttrs = pdl ? 1 : 0;
     FT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_tc_kernel<D, G>, map, (const uint8_t*)kv_layer, page_table, max_pages,
                                      req_q_start, req_slot, req_pos0, tile_req, tile_q0, (__nv_bfloat16*)out,
-                                     (__nv_bfloat16*)out_lo, nq, nkv, scale_log2));
+                                     (__nv_bfloat16*)out_lo, nq, nkv, scale_log2, stagger_on));
     return 0;
 }
 
