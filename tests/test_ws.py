@@ -38,3 +38,28 @@ def test_sixteen_websocket_sessions_two_turns_each():
     assert all(set(c["kw"]) >= {"temperature", "max_tokens", "request_id"} for c in srv.calls)
     m = W.turn_metrics(res, 1)
     assert m["sessions"] == 16 and m["tokens"] == sum(len(r["turns"][1]["chunks"]) for r in res) and m["tok_s"] > 0
+
+
+def test_legacy_ollama_provider_path_of_the_unchanged_server():
+    """LLM_PROVIDER=ollama: the same unchanged server takes its legacy branch (`_init_ollama_handler`,
+    `_generate_with_ollama`, websocket_server_vllm.py:124-137, 543-600) and drives the SYNCHRONOUS `generate_stream` with
+    Ollama's keyword set (top_k included); NativeHandler stands in for OllamaHandler."""
+    tok = ByteTokenizer()
+    eng = FakeEngine(tok, reply=lambda toks: f"legacy {len(toks)}")
+    runner = EngineRunner(eng, tok)
+    srv = W.ReferenceServer(runner, env={"DEFAULT_MAX_TOKENS": "32", "DEFAULT_TOP_K": "40"}, provider="ollama")
+    try:
+        res = W.run_clients(srv.port, [{"system_prompt": f"s{i}", "turns": [f"hi {i}", "again"]} for i in range(4)])
+    finally:
+        srv.stop()
+        runner.shutdown()
+    assert len(res) == 4 and all(c.get("sync") for c in srv.calls) and len(srv.calls) == 8
+    assert all({"temperature", "max_tokens", "top_p", "top_k", "request_id"} <= set(c["kw"]) for c in srv.calls)
+    by_sid = {}
+    for s_, toks, kw in eng.submitted:
+        by_sid.setdefault(s_, []).append((toks, kw))
+    for r in res:
+        (t1, kw1), (t2, _) = by_sid[r["session_id"]]
+        assert ["".join(t["chunks"]) for t in r["turns"]] == [f"legacy {len(t1)}", f"legacy {len(t2)}"]
+        assert all(t["end"]["type"] == "response_complete" and t["end"]["stats"]["provider"] == "ollama" for t in r["turns"])
+        assert kw1["top_k"] == 40 and t2[:len(t1)] == t1

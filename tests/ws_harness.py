@@ -38,14 +38,16 @@ def find_reference() -> Optional[str]:
 class ReferenceServer:
     """The unchanged WebSocketLLMServer over `runner` (an EngineRunner), on 127.0.0.1:<free port>."""
 
-    def __init__(self, runner, env: Optional[Dict[str, str]] = None, max_connections: int = 128):
+    def __init__(self, runner, env: Optional[Dict[str, str]] = None, max_connections: int = 128, provider: str = "vllm"):
+        """provider "vllm": the server's `_generate_with_vllm` loop over `generate_stream_async`; "ollama": its legacy
+        `_generate_with_ollama` loop over the synchronous `generate_stream` (OllamaHandler swapped instead)."""
         import uvicorn
         ref = find_reference()
         if ref is None:
             raise RuntimeError("no reference checkout (run scripts/install_reference.sh where /root/reference exists)")
         self.ref = ref
         self._env_old = {}
-        settings = {"LLM_PROVIDER": "vllm", "ENABLE_PYDANTIC_AI": "false", "DEFAULT_TEMPERATURE": "0.0",
+        settings = {"LLM_PROVIDER": provider, "ENABLE_PYDANTIC_AI": "false", "DEFAULT_TEMPERATURE": "0.0",
                     "DEFAULT_MAX_TOKENS": "32", "LLM_MAX_CONNECTIONS": str(max_connections), "LOG_LEVEL": "ERROR",
                     "VLLM_MODEL": "llama3.2:1b", **(env or {})}
         for k, v in settings.items():
@@ -55,7 +57,8 @@ class ReferenceServer:
             del sys.modules[m]
         sys.path.insert(0, ref)
         try:
-            import app.core.vllm_handler as vh                          # the reference's module, unmodified
+            import app.core.vllm_handler as vh                          # the reference's modules, unmodified
+            import app.core.ollama_handler as oh
             from app.utils.config import Config
             from fasttalk_llm_microservice_b200.handler import NativeHandler
             self.calls: List[Dict] = []                                 # what the server asked the handler for
@@ -69,7 +72,12 @@ class ReferenceServer:
                     calls.append({"messages": [dict(m) for m in messages], "kw": dict(kw)})
                     return super().generate_stream_async(messages, **kw)
 
+                def generate_stream(self, messages, **kw):
+                    calls.append({"messages": [dict(m) for m in messages], "kw": dict(kw), "sync": True})
+                    return super().generate_stream(messages, **kw)
+
             vh.VLLMHandler = Bound                                      # == handler.install(), bound to this runner
+            oh.OllamaHandler = Bound
             from app.core.websocket_server_vllm import WebSocketLLMServer
             self.server_obj = WebSocketLLMServer(Config())
         finally:
