@@ -259,6 +259,7 @@ struct F16Path {                 // the fp16 single-plane form of one projection
     const CUtensorMap* mx = nullptr;         // [2]: 128- and 64-row boxes
     const void *hi = nullptr, *lo = nullptr;
     void* x16 = nullptr;
+    bool ready = false;                      // the producer's epilogue already wrote x16: no staging kernel
 };
 
 static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, const CUtensorMap* xmaps_lo,
@@ -289,8 +290,10 @@ static int run_gemm(Engine* e, const CUtensorMap& mw, const CUtensorMap* xmaps, 
     e->st.kernel_launches++;
     if (f16 && f16->mw && e->prefill_planes == 3 && gemm_f16_path_ok(n_out, T, K, splits)) {
         // large prefill projection: ONE fp16 plane (= fp16(hi + lo), staged by a small kernel) against fp16 weights
-        FT_TRY(launch_planes_to_f16(f16->hi, f16->lo, f16->x16, (size_t)T * K, e->pdl, e->stream));
-        e->st.kernel_launches++;
+        if (!f16->ready) {
+            FT_TRY(launch_planes_to_f16(f16->hi, f16->lo, f16->x16, (size_t)T * K, e->pdl, e->stream));
+            e->st.kernel_launches++;
+        }
         epi.x_planes = 3;
         return launch_gemm(*f16->mw, f16->mx[0], &f16->mx[0], bn, n_out, T, K, 1, epi, e->pdl, e->stream, &f16->mx[1],
                            &f16->mx[1]);
@@ -323,6 +326,13 @@ static int forward(Engine* e, const Batch& b) {
     // L2 prefetch of the next projection's weights only pays when the GEMMs are latency-bound
     const bool decode_only = b.n_tiles == 0 && T <= 128;
     const bool use16 = e->prefill_planes == 3 && e->w16_qkv != nullptr && T > 128;
+    // which projections take the one-fp16-plane form this step: their producers write that plane in their epilogues
+    // (O -> gate/up input, down -> next QKV input, gate/up -> down input); layer 0's QKV input (embedding kernel) and the
+    // attention output are staged by planes_to_f16 instead
+    static const bool direct = getenv("FT_F16_STAGE_ALL") == nullptr;          // A/B switch: stage every plane with planes_to_f16
+    const bool f16_qkv = direct && use16 && gemm_f16_path_ok(e->qkv_dim, T, c.hidden, gemm_pick_splits(e->qkv_dim, T, c.hidden, e->sms, true));
+    const bool f16_gu = direct && use16 && gemm_f16_path_ok(2 * c.ffn, T, c.hidden, 1);
+    const bool f16_d = direct && use16 && gemm_f16_path_ok(c.hidden, T, c.ffn, gemm_pick_splits(c.hidden, T, c.ffn, e->sms, true));
     ft_gemm_epilogue rstd = {};            // fields shared by every epilogue that applies 1/rms
     rstd.ssq_in = e->ssq;
     rstd.ssq_parts = e->ssq_parts;
@@ -345,7 +355,7 @@ static int forward(Engine* e, const Batch& b) {
             ep.nq = c.n_q_heads;
             ep.nkv = c.n_kv_heads;
             ep.head_dim = c.head_dim;
-            const F16Path f = {use16 ? &e->m16_wqkv[l] : nullptr, e->m16_xn, e->xn, e->xn_lo, e->x16_xn};
+            const F16Path f = {use16 ? &e->m16_wqkv[l] : nullptr, e->m16_xn, e->xn, e->xn_lo, e->x16_xn, l > 0 && f16_qkv};
             FT_TRY(run_gemm(e, e->m_wqkv[l], e->m_xn, e->m_xn_lo, T, e->qkv_dim, c.hidden, ep, &f));
         }
         if (b.n_decode > 0) {
@@ -377,6 +387,7 @@ static int forward(Engine* e, const Batch& b) {
             ep.out_lo = e->xn_lo;
             ep.ssq_out = e->ssq;
             ep.ssq_stride = e->t_max;
+            if (f16_gu) ep.out_f16 = e->x16_xn;
             if (decode_only) {      // stream the gate/up weights into L2 behind this latency-bound kernel
                 ep.prefetch = bf16_off(e->w.wgu, (size_t)l * 2 * c.ffn * H);
                 ep.prefetch_bytes = (long long)2 * c.ffn * H * 2;
@@ -389,11 +400,12 @@ static int forward(Engine* e, const Batch& b) {
             ep.mode = FT_EPI_SWIGLU;
             ep.out = e->act;
             ep.out_lo = e->act_lo;
+            if (f16_d) ep.out_f16 = e->x16_act;
             if (decode_only) {
                 ep.prefetch = bf16_off(e->w.wd, (size_t)l * c.ffn * H);
                 ep.prefetch_bytes = (long long)c.ffn * H * 2;
             }
-            const F16Path f = {use16 ? &e->m16_wgu[l] : nullptr, e->m16_xn, e->xn, e->xn_lo, e->x16_xn};
+            const F16Path f = {use16 ? &e->m16_wgu[l] : nullptr, e->m16_xn, e->xn, e->xn_lo, e->x16_xn, f16_gu};
             FT_TRY(run_gemm(e, e->m_wgu[l], e->m_xn, e->m_xn_lo, T, 2 * c.ffn, c.hidden, ep, &f));
         }
         {
@@ -405,11 +417,12 @@ static int forward(Engine* e, const Batch& b) {
             ep.out_lo = e->xn_lo;
             ep.ssq_out = e->ssq;
             ep.ssq_stride = e->t_max;
+            if (f16_qkv && l + 1 < c.layers) ep.out_f16 = e->x16_xn;
             if (decode_only && l + 1 < c.layers) {
                 ep.prefetch = bf16_off(e->w.wqkv, (size_t)(l + 1) * e->qkv_dim * H);
                 ep.prefetch_bytes = (long long)e->qkv_dim * H * 2;
             }
-            const F16Path f = {use16 ? &e->m16_wd[l] : nullptr, e->m16_act, e->act, e->act_lo, e->x16_act};
+            const F16Path f = {use16 ? &e->m16_wd[l] : nullptr, e->m16_act, e->act, e->act_lo, e->x16_act, f16_d};
             FT_TRY(run_gemm(e, e->m_wd[l], e->m_act, e->m_act_lo, T, c.hidden, c.ffn, ep, &f));
         }
     }

@@ -97,6 +97,13 @@ __device__ __forceinline__ void store_hi_lo4(__nv_bfloat16* hi, __nv_bfloat16* l
         *reinterpret_cast<uint2*>(lo + idx) = l;
     }
 }
+// four fp32 -> one saturating fp16 plane (8 bytes): the single-plane input of the large prefill projections
+__device__ __forceinline__ void store_f16x4(__half* p, size_t idx, float4 y) {
+    uint2 h;
+    h.x = pack_f16_sat(y.x, y.y);
+    h.y = pack_f16_sat(y.z, y.w);
+    *reinterpret_cast<uint2*>(p + idx) = h;
+}
 // explicit shared-memory loads: the staging / rstd pointers reach the epilogue as generic pointers, and
 // generic loads interleaved with global stores cost ~0.5 us per token row here (scripts/trace_decode_gemms.py)
 __device__ __forceinline__ float4 lds_f4(uint32_t a) {
@@ -348,8 +355,9 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 if (tp) y = f4_add(y, __ldcg(reinterpret_cast<const float4*>(ep.tp_xchg + idx)));   // a + b == b + a
                 float4 r = f4_add(pre_r[u], y);
                 *reinterpret_cast<float4*>(ep.resid + idx) = r;
-                store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
-                             idx, make_float4(r.x * gam.x, r.y * gam.y, r.z * gam.z, r.w * gam.w));
+                const float4 rg = make_float4(r.x * gam.x, r.y * gam.y, r.z * gam.z, r.w * gam.w);
+                store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo), idx, rg);
+                if (ep.out_f16) store_f16x4(reinterpret_cast<__half*>(ep.out_f16), idx, rg);
                 const float ss = warp_sum(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
                 if (lane == 0) ep.ssq_out[(size_t)c.row_tile * ep.ssq_stride + t] = ss;
             } else if (mode == FT_EPI_QKV_ROPE) {
@@ -392,6 +400,7 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 if (ep.out_lo)
                     *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out_lo) + idx) =
                         pack_bf16(a0 - bf16_lo(h), a1 - bf16_hi(h));
+                if (ep.out_f16) *reinterpret_cast<uint32_t*>(reinterpret_cast<__half*>(ep.out_f16) + idx) = pack_f16_sat(a0, a1);
             } else if (mode == FT_EPI_LOGITS) {
                 const size_t idx = (size_t)t * (ep.out_stride ? ep.out_stride : n_out) + ep.out_col0 + row;
                 const float4 lg = f4_mul(y, rs);

@@ -66,7 +66,7 @@ class GemmEpilogue(C.Structure):
         ("tp_peer_xchg", C.c_void_p), ("tp_xchg", C.c_void_p), ("tp_peer_flags", C.c_void_p),
         ("tp_flags", C.c_void_p), ("tp_epoch", C.c_uint), ("tp_peer_out", C.c_void_p),
         ("out_stride", C.c_int), ("out_col0", C.c_int), ("sync_mode", C.c_int), ("sync_slots", C.c_int),
-        ("x_planes", C.c_int),
+        ("out_f16", C.c_void_p), ("x_planes", C.c_int),
     ]
 
 
