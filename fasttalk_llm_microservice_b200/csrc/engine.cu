@@ -670,7 +670,8 @@ static int engine_step(Engine* e, std::unique_lock<std::mutex>& lk) {
     };
     std::vector<Session*> to_close;
     auto settle = [&](Request* r) -> bool {      // true: the request was cancelled / its session closed mid-step
-        if (r->sess && r->sess->close_pending) to_close.push_back(r->sess);
+        if (r->sess && r->sess->close_pending && std::find(to_close.begin(), to_close.end(), r->sess) == to_close.end())
+            to_close.push_back(r->sess);
         if (!r->cancel_pending) return false;
         r->cancel_pending = false;
         finish_request(e, r, 3, -1);
@@ -694,7 +695,6 @@ static int engine_step(Engine* e, std::unique_lock<std::mutex>& lk) {
         }
     }
     for (Session* sx : to_close) {
-        if (e->sessions.find(sx->key) == e->sessions.end() || e->sessions[sx->key] != sx) continue;   // listed twice
         for (auto& kv : e->requests)
             if (kv.second->sess == sx) kv.second->sess = nullptr;
         drop_session(e, sx);
