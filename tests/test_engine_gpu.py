@@ -383,6 +383,30 @@ def test_larger_configs_logits_and_greedy(name, n_prompt, n_new):
         torch.cuda.empty_cache()
 
 
+def test_llama8b_config4_long_history_prefill_and_decode():
+    """BASELINE config 4's shape on one GPU: Llama-3.1-8B (head_dim 128, untied LM head, rope factor 8), an 8000-token
+    history prefilled in ONE 8192-token step (CTA-pair GEMMs on the single fp16 plane, tcgen05 prefill attention at
+    d = 128 over 125 KV tiles), then streaming decode: all 8 positions against the fp32 oracle, teacher-forced."""
+    from fasttalk_llm_microservice_b200.model_spec import SPECS
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    spec = SPECS["llama-3.1-8b"]
+    w = init_weights(spec, seed=5, device="cuda")
+    eng = make_engine(spec, w, max_batch=2, max_batched_tokens=8192, max_context=8192, debug_logit_rows=0)
+    try:
+        w32 = {k: v.float() for k, v in w.items()}
+        prompt = torch.randint(0, 128000, (8000,), generator=torch.Generator().manual_seed(80))
+        with torch.no_grad():
+            ref_tokens, ref_logits = O.greedy_generate(w32, spec, prompt, 8, return_logits=True)
+        del w32
+        torch.cuda.empty_cache()
+        job = greedy_parity(eng, "8B cfg4 (8000-token history, 8192 window)", prompt.tolist(), ref_tokens, ref_logits)
+        assert job.errs_checked >= 7 and job.worst_err < 1e-2
+    finally:
+        eng.close()
+        del w
+        torch.cuda.empty_cache()
+
+
 # ------------------------------------------------------------------ devices and threads (ADVICE r1)
 def _tiny_setup():
     from fasttalk_llm_microservice_b200.model_spec import SPECS
