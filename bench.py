@@ -344,7 +344,7 @@ def run_native(args, rank, world, local_rank):
     for r in rids:
         eng.cancel(r)
     eng.step(); eng.drain()
-    eng.set_decode_prefill_cap(args.prefill_cap)      # serving configuration from here on (0 = the engine default, 768)
+    eng.set_decode_prefill_cap(args.prefill_cap)      # serving configuration from here on (0 = the engine default, 896)
     # warm the sessions with a known history (prefix reuse needs the cached tokens == re-sent prefix)
     for i in range(SESSIONS):
         eng.close_session(f"s{i}")
@@ -477,7 +477,7 @@ def run_native(args, rank, world, local_rank):
                    "prefix_hit_tokens": h1["prefix_hit_tokens"] - h0["prefix_hit_tokens"],
                    "ttft_ms_p50": 1e3 * pct(h_first, 0.5), "ttft_ms_p99": 1e3 * pct(h_first, 0.99),
                    "itl_ms_p50": 1e3 * pct(h_gaps, 0.5), "itl_ms_p99": 1e3 * pct(h_gaps, 0.99),
-                   "decode_prefill_cap": args.prefill_cap or 768}
+                   "decode_prefill_cap": args.prefill_cap or 896}
     for i in range(SESSIONS):
         eng.close_session(f"h{i}")
 
@@ -633,7 +633,7 @@ def main():
     ap.add_argument("--tp", type=int, default=1, help="2 = the Llama-3.1-8B tensor-parallel configuration (torchrun, 2 ranks)")
     ap.add_argument("--tune", action="store_true", help="kernel tuning: print ms/step of the timed decode steps and exit")
     ap.add_argument("--prefill-cap", type=int, default=0,
-                    help="engine decode_prefill_cap for the e2e runs (0 = engine default 768, < 0 = uncapped)")
+                    help="engine decode_prefill_cap for the e2e runs (0 = engine default 896, < 0 = uncapped)")
     ap.add_argument("--settle", type=float, default=2.0,
                     help="idle seconds between the set-up prefill and the warm-up (power-cap recovery; untimed)")
     args = ap.parse_args()

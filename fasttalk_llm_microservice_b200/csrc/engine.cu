@@ -144,7 +144,8 @@ struct Engine {
 };
 constexpr size_t kStepTimes = 4096;
 constexpr int kDefaultPrefillPlanes = 3;      // one fp16 plane x fp16 weight copies in the large prefill GEMMs (measured: DESIGN.md §2)
-constexpr int kDefaultDecodePrefillCap = 768;    // a 64-row 1B step with 768 prompt tokens beside it takes ~5.5 ms (1024: ~7)
+constexpr int kGemmTokenTile = 128;             // token tile of the multi-tile projections (gemm_pick_bn)
+constexpr int kDefaultDecodePrefillCap = 896;    // <= 128 decode rows + 896 -> 1024 rows: a 1B step of ~4.3 ms (1280 rows: 6.6 ms)
 
 // Every entry point that touches CUDA makes the engine's device current for its duration: the caller may be a
 // thread whose current device is another GPU (a fresh thread starts on device 0).
@@ -516,8 +517,11 @@ static int engine_step(Engine* e, std::unique_lock<std::mutex>& lk) {
     // engine with nothing decoding) the step takes the whole budget: first tokens for the many come soonest.
     int n_pending = 0;
     for (Request* r : e->active) n_pending += r->state == REQ_PREFILL;
-    if (e->decode_prefill_cap > 0 && !dec.empty() && (int)dec.size() >= n_pending)
-        budget = std::min(budget, e->decode_prefill_cap);
+    if (e->decode_prefill_cap > 0 && !dec.empty() && (int)dec.size() >= n_pending) {
+        // the projections work on 128-token tiles, so the rows up to the next tile boundary ride for free
+        const int rows = (int)dec.size() + e->decode_prefill_cap;
+        budget = std::min(budget, (rows + kGemmTokenTile - 1) / kGemmTokenTile * kGemmTokenTile - (int)dec.size());
+    }
     for (Request* r : e->active) {
         if (r->state != REQ_PREFILL || budget <= 0) continue;
         const int remaining = (int)r->prompt.size() - r->prefill_pos;

@@ -987,10 +987,20 @@ static int device_sms() {          // of the CURRENT device
     return sms[slot];
 }
 
+// Fewest 128 x 128 tiles a launch needs before the persistent / CTA-pair kernels take it.  One token tile: more tiles
+// than SMs.  Two or more token tiles (mixed decode + prefill steps of a few hundred rows): from 32 tiles on — a pair
+// loads 24 KB per k-step and CTA instead of 32 KB, which is what bounds these single-wave grids (1B, 56 decode rows +
+// 968 prompt tokens: O and down projection 32 -> 27 us each, the step 4.42 -> 4.13 ms; profiles/r02_mixed_step.md).
+static int pair_min_tiles(int T) {
+    if (T <= 128) return device_sms() + 1;
+    if (const char* ov = getenv("FT_GEMM_PAIR_MIN_TILES")) return atoi(ov);       // A/B switch (scripts/)
+    return 32;
+}
+
 bool gemm_pair_eligible(int n_out, int T) {
     static const bool off = getenv("FT_GEMM_NO_PAIR") != nullptr || getenv("FT_GEMM_NO_PERSISTENT") != nullptr;
     const int bn = gemm_pick_bn(T, true);
-    return !off && bn == 128 && n_out % (2 * GEMM_BM) == 0 && (n_out / GEMM_BM) * ((T + bn - 1) / bn) > device_sms();
+    return !off && bn == 128 && n_out % (2 * GEMM_BM) == 0 && (n_out / GEMM_BM) * ((T + bn - 1) / bn) >= pair_min_tiles(T);
 }
 
 // Does launch_gemm have a one-fp16-plane form (x_planes = 3) of this launch?  128-token tiles, K unsplit, and either the
@@ -1232,7 +1242,7 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
     // (not for K > 4096: a 128-chunk mainloop hides nothing behind its epilogue, and the ring competing
     //  with the overlapped epilogue's traffic ran the 1B down projection 1.2x slower than tile-per-CTA)
     const bool multiwave = hilo && splits == 1 && mode != FT_EPI_PARTIAL && !no_persistent &&
-                           (n_out / GEMM_BM) * ((T + bn - 1) / bn) > device_sms();
+                           (n_out / GEMM_BM) * ((T + bn - 1) / bn) >= pair_min_tiles(T);
     // 128-token tiles with the 64-token maps at hand: CTA pairs (cta_group::2), two row tiles per MMA
     static const bool no_pair = getenv("FT_GEMM_NO_PAIR") != nullptr;                 // A/B switch (scripts/)
     if (multiwave && !no_pair && bn == 128 && mx_half && mx_lo_half && n_out % (2 * GEMM_BM) == 0) {

@@ -38,7 +38,7 @@ class EngineLimits:
     num_pages: int = 0                  # 0 = enough for max_batch full contexts (+25 %)
     max_sessions: int = 0
     use_pdl: bool = True
-    decode_prefill_cap: int = 0         # prompt tokens per step while sequences decode: 0 = 768, < 0 = uncapped
+    decode_prefill_cap: int = 0         # prompt tokens per step while sequences decode: 0 = 896, < 0 = uncapped
     prefill_planes: int = 0             # large prefill GEMMs: 0 = default, 1 = bf16 hi only, 2 = bf16 hi + lo, 3 = one fp16 plane x fp16 weight copies
     debug_logit_rows: int = 0
 
@@ -181,7 +181,7 @@ class Engine:
         return self.step_log(cap)[:, 0].tolist()
 
     def set_decode_prefill_cap(self, cap: int):
-        """Prompt tokens admitted per step while sequences decode (0 = default 768, < 0 = uncapped)."""
+        """Prompt tokens admitted per step while sequences decode (0 = default 896, < 0 = uncapped; rounded up so that decode rows + prompt tokens fill 128-token tiles)."""
         N.check(self.lib.ft_engine_set_decode_prefill_cap(self._h, int(cap)), "ft_engine_set_decode_prefill_cap")
 
     def set_profile(self, on: bool):

@@ -54,7 +54,8 @@ typedef struct {
     int tp_size, tp_rank;
     /* Prompt tokens a step may admit WHILE other sequences are decoding (they all wait for the step): the
      * latency side of vLLM's --max-num-batched-tokens trade-off (docker-compose.vllm.yml:48).  0 = default
-     * (768), < 0 = no cap (every step may fill max_batched_tokens).  The cap applies while at least as many
+     * (896), < 0 = no cap (every step may fill max_batched_tokens).  The admitted count is rounded up so that decode
+     * rows + prompt tokens end on a 128-token tile of the projections (those rows cost nothing more).  The cap applies while at least as many
      * sequences are decoding as are waiting for their first token; otherwise (nothing decoding, or a burst of
      * arrivals that outnumbers the decoding sequences) the step uses the full max_batched_tokens budget. */
     int decode_prefill_cap;

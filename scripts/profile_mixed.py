@@ -1,5 +1,5 @@
 """One MIXED step for ncu: ~56 sessions decoding at ctx ~2k while four sessions re-send a 2048-token history of which 224
-tokens are new (768-token prefill cap -> 768 prompt tokens ride along), inside a cudaProfilerStart/Stop window.
+tokens are new (prefill cap 768 -> decode rows + prompt tokens fill seven 128-token tiles), inside a cudaProfilerStart/Stop window.
 
     ncu --profile-from-start off --metrics gpu__time_duration.sum --csv python scripts/profile_mixed.py
 """

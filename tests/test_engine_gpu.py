@@ -446,6 +446,49 @@ def test_two_engines_share_one_gpu_and_step_concurrently():
         b.close()
 
 
+def test_prompt_tokens_beside_streaming_sessions_are_capped_to_a_token_tile():
+    """`decode_prefill_cap`: while at least as many sessions stream as wait for a first token, a step admits prompt tokens
+    only up to the 128-token tile boundary at or above (decode rows + cap); when more wait than stream the step takes
+    the whole budget.  What is generated does not depend on the cap."""
+    spec, w, g = _tiny_setup()
+    gen = torch.Generator().manual_seed(11)
+    short = [torch.randint(0, spec.vocab, (24,), generator=gen).tolist() for _ in range(5)]
+    long_ = [torch.randint(0, spec.vocab, (700,), generator=gen).tolist() for _ in range(6)]
+    ref = make_engine(spec, w, max_batch=12, max_batched_tokens=2048, decode_prefill_cap=-1)
+    eng = make_engine(spec, w, max_batch=12, max_batched_tokens=2048, decode_prefill_cap=200)
+    try:
+        want = ref.generate(long_[:3], max_new_tokens=6, sessions=["r0", "r1", "r2"], ignore_eos=True)
+        for i, p in enumerate(short):
+            eng.submit(f"s{i}", p, max_new_tokens=400, ignore_eos=True)
+        eng.step(); eng.drain()                                   # nothing streams yet: the first step is uncapped
+        rids = [eng.submit(f"l{i}", long_[i], max_new_tokens=6, ignore_eos=True) for i in range(3)]
+        eng.step_log()
+        out = {r: [] for r in rids}
+        for _ in range(40):
+            eng.step()
+            for rid, tok, _fin in eng.drain():
+                if rid in out and tok >= 0:
+                    out[rid].append(tok)
+            if all(len(v) == 6 for v in out.values()):
+                break
+        assert [out[r] for r in rids] == want
+        rows = [r.tolist() for r in eng.step_log()]
+        capped = [int(r[2]) for r in rows if r[1] >= 5 and r[2] > 0]
+        # streaming rows + prompt tokens fill two 128-token tiles (5 + 200 -> 256) until the 2100 tokens are through
+        full = [r for r in rows if r[1] >= 5 and r[2] > 0][:-1]
+        assert len(full) >= 7 and all(int(r[1] + r[2]) == 256 for r in full) and sum(capped) == 2100, rows
+        # six arrivals behind five streaming sessions: more wait than stream, the step takes the whole budget
+        for i in range(6):
+            eng.submit(f"m{i}", long_[i][::-1], max_new_tokens=1, ignore_eos=True)
+        eng.step_log()
+        eng.step(); eng.drain()
+        burst = eng.step_log()[-1].tolist()
+        assert int(burst[2]) >= 2000, burst
+    finally:
+        ref.close()
+        eng.close()
+
+
 def test_engine_stepped_from_a_fresh_thread():
     """Every ft_engine_* entry makes the engine's device current itself: a thread that never called cudaSetDevice
     (current device 0) can step an engine that lives on another GPU.  With one GPU the thread part still runs."""
