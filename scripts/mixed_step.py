@@ -1,3 +1,8 @@
+"""Device time of MIXED steps: `ND` sessions decoding at ctx ~2k while the others re-send histories whose last ~1040 tokens
+are new, for each prompt-token cap in `CAPS` (min over three rounds of three equal steps, from ft_engine_step_log).
+
+    CAPS=200,456,768,840,968 [FT_GEMM_PAIR_MIN_TILES=149] [FT_PREFILL_PLANES=2] python scripts/mixed_step.py
+"""
 import os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

@@ -1,3 +1,10 @@
+"""Kernel timeline (torch.profiler / CUPTI, no serialisation) of one MIXED step: 56 sessions decoding at ctx ~2k while
+eight re-send a 2048-token history of which 224 tokens are new, `CAP` prompt tokens admitted per step.  Writes
+gpurun_out/mixed_timeline.txt (start, duration, gap to the previous kernel's end) and prints, per kernel and grid, the
+time it adds to the step (end - max(previous end, start)) next to its own duration.
+
+    CAP=896 python scripts/timeline_mixed.py
+"""
 import os, sys, json
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
