@@ -388,7 +388,10 @@ static int forward(Engine* e, const Batch& b) {
             ep.out_lo = e->xn_lo;
             ep.ssq_out = e->ssq;
             ep.ssq_stride = e->t_max;
-            if (f16_gu) ep.out_f16 = e->x16_xn;
+            if (f16_gu) {           // the gate/up projection reads the fp16 plane alone: no hi / lo planes to write
+                ep.out_f16 = e->x16_xn;
+                ep.out = ep.out_lo = nullptr;
+            }
             if (decode_only) {      // stream the gate/up weights into L2 behind this latency-bound kernel
                 ep.prefetch = bf16_off(e->w.wgu, (size_t)l * 2 * c.ffn * H);
                 ep.prefetch_bytes = (long long)2 * c.ffn * H * 2;
@@ -401,7 +404,10 @@ static int forward(Engine* e, const Batch& b) {
             ep.mode = FT_EPI_SWIGLU;
             ep.out = e->act;
             ep.out_lo = e->act_lo;
-            if (f16_d) ep.out_f16 = e->x16_act;
+            if (f16_d) {
+                ep.out_f16 = e->x16_act;
+                ep.out = ep.out_lo = nullptr;
+            }
             if (decode_only) {
                 ep.prefetch = bf16_off(e->w.wd, (size_t)l * c.ffn * H);
                 ep.prefetch_bytes = (long long)c.ffn * H * 2;
@@ -418,7 +424,10 @@ static int forward(Engine* e, const Batch& b) {
             ep.out_lo = e->xn_lo;
             ep.ssq_out = e->ssq;
             ep.ssq_stride = e->t_max;
-            if (f16_qkv && l + 1 < c.layers) ep.out_f16 = e->x16_xn;
+            if (f16_qkv && l + 1 < c.layers) {     // (the last layer's planes feed the LM head's row gather)
+                ep.out_f16 = e->x16_xn;
+                ep.out = ep.out_lo = nullptr;
+            }
             if (decode_only && l + 1 < c.layers) {
                 ep.prefetch = bf16_off(e->w.wqkv, (size_t)(l + 1) * e->qkv_dim * H);
                 ep.prefetch_bytes = (long long)e->qkv_dim * H * 2;

@@ -356,7 +356,7 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 float4 r = f4_add(pre_r[u], y);
                 *reinterpret_cast<float4*>(ep.resid + idx) = r;
                 const float4 rg = make_float4(r.x * gam.x, r.y * gam.y, r.z * gam.z, r.w * gam.w);
-                store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo), idx, rg);
+                if (ep.out) store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo), idx, rg);
                 if (ep.out_f16) store_f16x4(reinterpret_cast<__half*>(ep.out_f16), idx, rg);
                 const float ss = warp_sum(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
                 if (lane == 0) ep.ssq_out[(size_t)c.row_tile * ep.ssq_stride + t] = ss;
@@ -396,7 +396,7 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 const float a0 = silu(g2.x * rs) * (u2.x * rs), a1 = silu(g2.y * rs) * (u2.y * rs);
                 const uint32_t h = pack_bf16(a0, a1);
                 const size_t idx = (size_t)t * (n_out >> 1) + c.row_tile * 64 + 2 * lane;
-                *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + idx) = h;
+                if (ep.out) *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + idx) = h;
                 if (ep.out_lo)
                     *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(ep.out_lo) + idx) =
                         pack_bf16(a0 - bf16_lo(h), a1 - bf16_hi(h));
@@ -806,13 +806,39 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     const int rank = (int)cluster_ctarank();
     const int n_row_pairs = n_out / (2 * GEMM_BM);
     const int n_tok_tiles = (T + BN - 1) / BN;
-    const int n_work = n_row_pairs * n_tok_tiles;
     const int cl = (int)cluster_id_x(), n_cl = (int)gridDim.x / 2;
+    // Work list.  MIXED (256-token tiles of ONE fp16 plane): whole rounds of the clusters take 256-token units; what is
+    // left over — less than one round — is cut into 128-token halves when those fit one round of their own, so the
+    // last round costs half a tile instead of a whole one (1B down projection at 8192 tokens: 256 units on 74
+    // clusters = 3 rounds + 34 units -> 68 halves).  map_x_lo_half is then the 64-token box of the same plane.
+    constexpr bool MIXED = BN == 256 && F16 && !HILO;
+    const int n_units = n_row_pairs * n_tok_tiles;
+    int n_big = n_units, n_small = 0;
+    if (MIXED) {
+        const int rem = n_units % n_cl;
+        if (rem > 0 && 2 * rem <= n_cl) {
+            n_big = n_units - rem;
+            n_small = 2 * rem;
+        }
+    }
+    const int n_work = n_big + n_small;
+    // unit w -> row pair, first token, 128-token half?
+    auto unit = [&](int w, int& row_pair, int& tok0) -> bool {
+        if (!MIXED || w < n_big) {
+            row_pair = w % n_row_pairs;
+            tok0 = (w / n_row_pairs) * BN;
+            return false;
+        }
+        const int s = w - n_big, b = n_big + (s >> 1);
+        row_pair = b % n_row_pairs;
+        tok0 = (b / n_row_pairs) * BN + (s & 1) * HALF;
+        return true;
+    };
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_w);
         tma_prefetch_desc(&map_x_half);
-        if (HILO) tma_prefetch_desc(&map_x_lo_half);
+        if (HILO || MIXED) tma_prefetch_desc(&map_x_lo_half);
         for (int s = 0; s < stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -842,15 +868,19 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             pdl_wait();
             int it = 0;
             for (int w = cl; w < n_work; w += n_cl) {
-                const int row0 = (2 * (w % n_row_pairs) + rank) * GEMM_BM;
-                const int tok0 = (w / n_row_pairs) * BN + rank * HALF;       // this CTA's half of the token tile
+                int row_pair, tok_first;
+                const bool small = unit(w, row_pair, tok_first);
+                const int row0 = (2 * row_pair + rank) * GEMM_BM;
+                const int tok0 = tok_first + rank * (small ? HALF / 2 : HALF);   // this CTA's half of the token tile
+                const CUtensorMap* mx = small ? &map_x_lo_half : &map_x_half;
+                const uint32_t bytes = small ? GEMM_A_BYTES + B_PLANE / 2 : STAGE_BYTES;
                 for (int i = 0; i < k_chunks; ++i, ++it) {
                     const int slot = it % stages;
                     if (it >= stages) mbar_wait(&empty_bar[slot], ((it / stages) - 1) & 1);
-                    if (rank == 0) mbar_expect_tx(&full_bar[slot], 2 * STAGE_BYTES);      // both CTAs' bytes
+                    if (rank == 0) mbar_expect_tx(&full_bar[slot], 2 * bytes);            // both CTAs' bytes
                     uint8_t* st = smem + (size_t)slot * STAGE_BYTES;
                     tma_tile_2d_pair(st, &map_w, i * GEMM_BK, row0, &full_bar[slot], pol_w);
-                    tma_tile_2d_pair(st + GEMM_A_BYTES, &map_x_half, i * GEMM_BK, tok0, &full_bar[slot], pol_x);
+                    tma_tile_2d_pair(st + GEMM_A_BYTES, mx, i * GEMM_BK, tok0, &full_bar[slot], pol_x);
                     if (HILO)
                         tma_tile_2d_pair(st + GEMM_A_BYTES + B_PLANE, &map_x_lo_half, i * GEMM_BK, tok0,
                                          &full_bar[slot], pol_x);
@@ -859,11 +889,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         }
     } else if (warp == 1 && rank == 0) {
         if (elect_one()) {
-            constexpr uint32_t idesc = F16 ? umma_idesc_f16(2 * GEMM_BM, BN) : umma_idesc_bf16(2 * GEMM_BM, BN);
+            constexpr uint32_t idesc_full = F16 ? umma_idesc_f16(2 * GEMM_BM, BN) : umma_idesc_bf16(2 * GEMM_BM, BN);
+            constexpr uint32_t idesc_half = umma_idesc_f16(2 * GEMM_BM, HALF);
             int ct = 0;
             uint32_t use = 0;
             for (int w = cl; w < n_work; w += n_cl, ++use) {
                 const uint32_t acc = use & 1;
+                const uint32_t idesc = MIXED && w >= n_big ? idesc_half : idesc_full;
                 if (use >= 2) {
                     mbar_wait(&tmem_empty_bar[acc], ((use >> 1) - 1) & 1);
                     tc_fence_after();
@@ -897,18 +929,32 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         for (int w = cl; w < n_work; w += n_cl, ++use) {
             const uint32_t acc = use & 1;
             EpiCtx c;
-            c.row_tile = 2 * (w % n_row_pairs) + rank; c.tok_tile = w / n_row_pairs; c.split = 0; c.n_split = 1;
-            c.tile_id = c.tok_tile * (n_out / GEMM_BM) + c.row_tile; c.cta_linear = (unsigned)c.tile_id;
+            int row_pair, tok_first;
+            const bool small = unit(w, row_pair, tok_first);
+            c.row_tile = 2 * row_pair + rank; c.tok_tile = tok_first / (small ? HALF : BN); c.split = 0; c.n_split = 1;
+            c.tile_id = (tok_first / BN) * (n_out / GEMM_BM) + c.row_tile; c.cta_linear = (unsigned)c.tile_id;
             c.n_ctas = (unsigned)(n_work * 2);
             c.n_out = n_out; c.T = T; c.has_acc = true; c.trace_base = -1;
-            epilogue_rstd<BN>(ep, c, rstd_s);
-            mbar_wait(&tmem_full_bar[acc], (use >> 1) & 1);
-            tc_fence_after();
-            for (int col0 = 0; col0 < BN; col0 += CB) {
-                if (c.tok_tile * BN + col0 >= T) break;
-                gemm_epilogue<BN, CB>(ep, c, tmem_base + acc * BN, stage_f, rstd_s, col0);
-                tc_fence_before();
-                epi_bar_sync();
+            if (MIXED && small) {
+                epilogue_rstd<HALF>(ep, c, rstd_s);
+                mbar_wait(&tmem_full_bar[acc], (use >> 1) & 1);
+                tc_fence_after();
+                for (int col0 = 0; col0 < HALF; col0 += CB) {
+                    if (tok_first + col0 >= T) break;
+                    gemm_epilogue<HALF, CB>(ep, c, tmem_base + acc * BN, stage_f, rstd_s, col0);
+                    tc_fence_before();
+                    epi_bar_sync();
+                }
+            } else {
+                epilogue_rstd<BN>(ep, c, rstd_s);
+                mbar_wait(&tmem_full_bar[acc], (use >> 1) & 1);
+                tc_fence_after();
+                for (int col0 = 0; col0 < BN; col0 += CB) {
+                    if (tok_first + col0 >= T) break;
+                    gemm_epilogue<BN, CB>(ep, c, tmem_base + acc * BN, stage_f, rstd_s, col0);
+                    tc_fence_before();
+                    epi_bar_sync();
+                }
             }
             if (et == 0) mbar_arrive_leader(&tmem_empty_bar[acc]);
         }
@@ -1177,7 +1223,7 @@ static int launch_pair(const CUtensorMap& mw, const CUtensorMap& mx_half, const 
     const int n_work = (n_out / (2 * GEMM_BM)) * ((T + BN - 1) / BN);
     const int clusters = n_work < max_clusters ? n_work : max_clusters;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * clusters);
+    cfg.gridDim = dim3(2 * clusters);     // (the kernel derives its work list — and the MIXED split — from the grid)
     cfg.blockDim = dim3(GEMM_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
@@ -1255,8 +1301,13 @@ int launch_gemm(const CUtensorMap& mw, const CUtensorMap& mx, const CUtensorMap*
         // latency-bound decode tiles, where the second product is free, always use both
         const bool one = epi.x_planes == 1;
         if (epi.x_planes == 3) {      // ONE fp16 activation plane against fp16 weights (the caller passed those maps)
-            if (work256 >= 8LL * (device_sms() / 2))
-                return launch_pair<256, false, true>(mw, mx, *mx_lo, n_out, T, K, epi, pdl, stream);
+            // 256-token tiles also from two rounds on when K is long: the tile's epilogue then hides behind the next
+            // mainloop, and the kernel cuts a last partial round into 128-token halves (MIXED in gemm_pair_kernel).
+            // Short K with a heavy epilogue (QKV, O) stays on 128-token tiles: there the epilogue sets the pace.
+            static const bool no_mixed = getenv("FT_GEMM_NO_MIXED_TILES") != nullptr;          // A/B switch (scripts/)
+            const long long rounds256 = work256 / (device_sms() / 2);
+            if (rounds256 >= 8 || (!no_mixed && K >= 4096 && rounds256 >= 2))
+                return launch_pair<256, false, true>(mw, mx, *mx_half, n_out, T, K, epi, pdl, stream);
             return launch_pair<128, false, true>(mw, *mx_half, *mx_lo_half, n_out, T, K, epi, pdl, stream);
         }
         if (work256 >= 8LL * (device_sms() / 2))
@@ -1304,6 +1355,17 @@ extern "C" int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int
     FT_REQUIRE(n_out % GEMM_BM == 0 && K % GEMM_BK == 0 && T >= 1,
                "ft_gemm_fused: need n_out %% 128 == 0, K %% 64 == 0, T >= 1 (got %d, %d, %d)", n_out, K, T);
     const int sms = device_sms();
+    if (epi->x_planes == 3) {
+        // w and x are FP16, one activation plane (what the engine's large prefill steps run): 128-token tiles, K unsplit
+        FT_REQUIRE(!x_lo && gemm_f16_path_ok(n_out, T, K, 1) && epi->mode != FT_EPI_PARTIAL,
+                   "ft_gemm_fused: x_planes = 3 needs x_lo = NULL, T > 64 and a fused epilogue (n_out %d, T %d, K %d)", n_out, T, K);
+        CUtensorMap mw16, mx16, mx16h;
+        if (int r = make_tmap_bf16_k64(&mw16, w, n_out, K, GEMM_BM)) return r;      // 2-byte elements: the same boxes
+        if (int r = make_tmap_bf16_k64(&mx16, x, T, K, 128)) return r;
+        if (int r = make_tmap_bf16_k64(&mx16h, x, T, K, 64)) return r;
+        return launch_gemm(mw16, mx16, &mx16, 128, n_out, T, K, 1, *epi, false, static_cast<cudaStream_t>(stream), &mx16h,
+                           &mx16h);
+    }
     const bool hilo = x_lo != nullptr;
     const bool staged = epi->mode == FT_EPI_RESID || epi->mode == FT_EPI_QKV_ROPE;
     const int bn = gemm_pick_bn(T, hilo);

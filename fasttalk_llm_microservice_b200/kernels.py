@@ -54,7 +54,11 @@ def gemm_fused(w: torch.Tensor, x: torch.Tensor, x_lo: torch.Tensor, mode: int, 
     """ft_gemm_fused with an ft_gemm_epilogue built from keyword tensors / scalars (see
     include/fasttalk_b200.h).  Outputs are whatever tensors the caller put in the epilogue."""
     import ctypes as C
-    _chk_bf16(w, "w"); _chk_bf16(x, "x"); _chk_bf16(x_lo, "x_lo")
+    if f.get("x_planes") == 3:       # the fp16 single-plane form of the large prefill projections: fp16 weights, x_lo = None
+        assert x_lo is None and all(t.is_cuda and t.dtype == torch.float16 and t.is_contiguous() for t in (w, x)), \
+            "x_planes = 3: need contiguous CUDA fp16 w and x, x_lo = None"
+    else:
+        _chk_bf16(w, "w"); _chk_bf16(x, "x"); _chk_bf16(x_lo, "x_lo")
     n_out, K = w.shape
     T = x.shape[0]
     ep = N.GemmEpilogue()

@@ -240,7 +240,8 @@ typedef struct {
                                   the next one's epilogue starts (stream order + the epilogue's dependency wait) */
     int sync_slots;            /* sync_mode 1 / 2: counter pairs in `sync` */
     void* out_f16;             /* RESID / SWIGLU, optional: the same values as out (+ out_lo) once more as ONE saturating fp16
-                                  plane — the input of a following projection that runs in its single-plane form */
+                                  plane — the input of a following projection that runs in its single-plane form.  With
+                                  out_f16 set, out (and out_lo) may be NULL: the bf16 planes are then not written */
     int x_planes;              /* 0 / 2: multiply both activation planes everywhere; 1: grids of more tiles than SMs with
                                   128-token tiles (prefill) multiply the hi plane only — half the tensor work there;
                                   3 (engine): x and w are FP16 tensors, one plane, CTA-pair kernel only */

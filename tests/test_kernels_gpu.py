@@ -116,6 +116,42 @@ def test_gemm_cta_pair_kernels(K, n_out, T, Kd, mode, what):
         assert rel_err(hilo(hi, lo), O.swiglu(hilo(xr, xr_lo) @ wr.float().T)) < 2e-4
 
 
+@pytest.mark.parametrize("n_out,T,Kd,what", [
+    (2048, 8192, 4096, "256-token tiles, 256 units on 74 pairs: 3 rounds + 34 units cut into 68 halves"),
+    (2048, 5000, 4096, "ragged tail: 160 units -> 2 rounds + 12 units cut into 24 halves, the last half beyond T"),
+    (2048, 1000, 4096, "less than two rounds of 256-token units: 128-token tiles"),
+    (1024, 700, 2048, "single wave of pairs (32 tiles or more, two or more token tiles)"),
+])
+def test_gemm_fp16_single_plane_form(K, n_out, T, Kd, what):
+    """The form the engine's large prefill steps run (x_planes = 3): ONE fp16 activation plane against fp16 weights on the
+    CTA-pair kernels, residual epilogue with all three outputs.  Integer-valued operands make the fp32 accumulation exact:
+    every tile, both work-list kinds and the ragged tail are compared bit for bit with torch."""
+    from fasttalk_llm_microservice_b200 import native as N
+    g = torch.Generator(device=DEV).manual_seed(n_out + T)
+    w = torch.randint(-2, 3, (n_out, Kd), device=DEV, generator=g).half()
+    x = torch.randint(-2, 3, (T, Kd), device=DEV, generator=g).half()
+    resid0 = torch.randint(-8, 9, (T, n_out), device=DEV, generator=g).float()
+    resid = resid0.clone()
+    gamma = torch.ones(n_out, device=DEV, dtype=torch.bfloat16)
+    hi = torch.full((T, n_out), 7.0, device=DEV, dtype=torch.bfloat16)
+    lo = torch.full_like(hi, 7.0)
+    f16 = torch.full((T, n_out), 7.0, device=DEV, dtype=torch.float16)
+    ssq = torch.zeros(n_out // 128, T, device=DEV)
+    K.gemm_fused(w, x, None, N.EPI_RESID, n_splits=1, x_planes=3, resid=resid, gamma=gamma, out=hi, out_lo=lo, out_f16=f16,
+                 ssq_out=ssq, ssq_stride=T)
+    torch.cuda.synchronize()
+    ref = resid0 + x.float() @ w.float().T
+    assert torch.equal(resid, ref)
+    assert torch.equal(hilo(hi, lo), ref)                       # |values| < 2^16: hi + lo is exact
+    assert torch.equal(f16.float(), ref.clamp(-65504, 65504).half().float())
+    assert torch.allclose(ssq.sum(0), (ref * ref).sum(1), rtol=1e-5)
+    # the bf16 planes are optional next to the fp16 plane
+    resid2, f16b = resid0.clone(), torch.zeros_like(f16)
+    K.gemm_fused(w, x, None, N.EPI_RESID, n_splits=1, x_planes=3, resid=resid2, gamma=gamma, out_f16=f16b, ssq_out=ssq, ssq_stride=T)
+    torch.cuda.synchronize()
+    assert torch.equal(resid2, ref) and torch.equal(f16b, f16)
+
+
 def test_attn_decode_empty_context_rows_are_zero(K):
     """A sequence with ctx_lens == 0 has no KV tile and so no CTA works on it: its output rows are defined
     (zero) instead of left as whatever the buffer held (round-1 verdict, weak #11)."""
