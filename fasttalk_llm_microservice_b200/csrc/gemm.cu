@@ -164,7 +164,16 @@ __device__ __forceinline__ void epilogue_rstd(const ft_gemm_epilogue& ep, const 
         const int t = t0 + j;
         if (ep.ssq_in && t < T) {
             float s = 0.f;
-            for (int p = 0; p < ep.ssq_parts; ++p) s += __ldcg(ep.ssq_in + (size_t)p * ep.ssq_stride + t);
+            const float* sp = ep.ssq_in + t;
+            int p = 0;
+            for (; p + 8 <= ep.ssq_parts; p += 8) {       // eight loads in flight, summed in the same order as one by one
+                float v[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] = __ldcg(sp + (size_t)(p + k) * ep.ssq_stride);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s += v[k];
+            }
+            for (; p < ep.ssq_parts; ++p) s += __ldcg(sp + (size_t)p * ep.ssq_stride);
             r = rsqrtf(s * ep.inv_h + ep.eps);
         }
         rstd_s[j] = r;
@@ -199,10 +208,18 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
     const int row = row0 + r4;
     constexpr int U = BN >= 128 ? 4 : 1;
     constexpr bool is_resid = mode == FT_EPI_RESID, is_rope = mode == FT_EPI_QKV_ROPE;
-    const int d_ = ep.head_dim, half_ = d_ >> 1;
+    // (head_dim is 64 or 128, checked at launch: masks and shifts instead of divisions in the token loop)
+    const int d_ = ep.head_dim, half_ = d_ >> 1, d_shift_ = d_ == 128 ? 7 : 6;
     const int q_dim_ = ep.nq * d_, kv_dim_ = ep.nkv * d_;
     const int region = row0 < q_dim_ ? 0 : row0 < q_dim_ + kv_dim_ ? 1 : 2;   // tile-uniform
-    const int i_ = is_rope ? row % d_ : 0;
+    const int i_ = is_rope ? row & (d_ - 1) : 0;
+    const int ih_ = i_ & (half_ - 1);                                         // rotate_half: cos / sin column
+    // K / V rows: slab of (page, kv head, K|V) = kv_layer + page * page_bytes_ + head_off_; inside it the row's 16-byte
+    // chunk is swizzled with the token's row (kv_swizzled_chunk in common.cuh)
+    const size_t slab_bytes_ = (size_t)kKvTile * d_ * 2;
+    const size_t page_bytes_ = slab_bytes_ * 2 * ep.nkv;
+    const size_t head_off_ = region == 0 ? 0 : ((size_t)((row - q_dim_ - (region == 2 ? kv_dim_ : 0)) >> d_shift_) * 2 + (region == 2 ? 1 : 0)) * slab_bytes_;
+    const int kv_off_ = (i_ >> 6) * (kKvTile * 128) + (i_ & 7) * 2, kv_chunk_ = (i_ >> 3) & 7;
     float4 pre_r[U], pre_c[U], pre_s[U];
     int pre_pos[U], pre_page[U];
     auto prefetch = [&](int j0) {
@@ -221,8 +238,8 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 const int j = j0 + u * GEMM_EPI_WARPS, t = t0 + j;
                 if (j < jend && t < T) {
                     if (region < 2) {
-                        pre_c[u] = *reinterpret_cast<const float4*>(ep.rope_cos + (size_t)pre_pos[u] * half_ + (i_ % half_));
-                        pre_s[u] = *reinterpret_cast<const float4*>(ep.rope_sin + (size_t)pre_pos[u] * half_ + (i_ % half_));
+                        pre_c[u] = *reinterpret_cast<const float4*>(ep.rope_cos + (size_t)pre_pos[u] * half_ + ih_);
+                        pre_s[u] = *reinterpret_cast<const float4*>(ep.rope_sin + (size_t)pre_pos[u] * half_ + ih_);
                     }
                     if (region > 0)
                         pre_page[u] = ep.page_table[(size_t)ep.seq_rows[t] * ep.max_pages + pre_pos[u] / kKvTile];
@@ -361,7 +378,7 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 const float ss = warp_sum(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
                 if (lane == 0) ep.ssq_out[(size_t)c.row_tile * ep.ssq_stride + t] = ss;
             } else if (mode == FT_EPI_QKV_ROPE) {
-                const int d = d_, half = half_, q_dim = q_dim_, kv_dim = kv_dim_, i = i_;
+                const int half = half_, q_dim = q_dim_, i = i_;
                 const int pos = pre_pos[u];
                 float4 val = f4_mul(y, rs);
                 if (region < 2) {
@@ -378,14 +395,10 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 if (region == 0) {
                     *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(ep.q_out) + (size_t)t * q_dim + row) = h4;
                 } else {
-                    const int kvh = (row - q_dim - (region == 2 ? kv_dim : 0)) / d;
-                    const int page = pre_page[u];
                     const int r = pos % kKvTile;
-                    uint8_t* slab = reinterpret_cast<uint8_t*>(ep.kv_layer) +
-                                    (((size_t)page * ep.nkv + kvh) * 2 + (region == 2 ? 1 : 0)) *
-                                        (size_t)(kKvTile * d * 2);
-                    // sub-slab of 64 dims, 128-byte rows, chunks swizzled with the row (kv_swizzled_chunk in common.cuh)
-                    const int off = (i >> 6) * (kKvTile * 128) + r * 128 + (((((i >> 3) & 7) ^ (r & 7))) << 4) + (i & 7) * 2;
+                    uint8_t* slab = reinterpret_cast<uint8_t*>(ep.kv_layer) + (size_t)pre_page[u] * page_bytes_ + head_off_;
+                    // sub-slab of 64 dims, 128-byte rows, chunks swizzled with the row
+                    const int off = kv_off_ + r * 128 + ((kv_chunk_ ^ (r & 7)) << 4);
                     *reinterpret_cast<uint2*>(slab + off) = h4;
                 }
             } else if (mode == FT_EPI_SWIGLU) {
