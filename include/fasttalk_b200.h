@@ -244,7 +244,10 @@ typedef struct {
                                   out_f16 set, out (and out_lo) may be NULL: the bf16 planes are then not written */
     int x_planes;              /* 0 / 2: multiply both activation planes everywhere; 1: grids of more tiles than SMs with
                                   128-token tiles (prefill) multiply the hi plane only — half the tensor work there;
-                                  3 (engine): x and w are FP16 tensors, one plane, CTA-pair kernel only */
+                                  3: x and w are FP16 tensors, ONE activation plane (x_lo = NULL), T > 64, K unsplit, any
+                                  fused epilogue — the form the engine's large prefill steps run (CTA-pair kernels; long-K
+                                  launches of two or more rounds use 256-token tiles and cut the last partial round into
+                                  128-token halves) */
 } ft_gemm_epilogue;
 long long ft_gemm_scratch_bytes(int n_out, int T, int K, int n_splits);
 int ft_gemm_fused(const void* w, const void* x, const void* x_lo, int n_out, int T, int K, int n_splits,
