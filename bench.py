@@ -16,7 +16,8 @@ Workload (BASELINE.json configs[1]): Llama-3.2-1B bf16, 64 concurrent sessions p
             chunk per token out.  Each session re-sends a ~2k-token history of which ~224 tokens are
             new (the rest is served from the session's KV), prefill rides along with decode, 32 tokens
             are generated; chunks / wall time, with TTFT and inter-token percentiles.
-  e2e_engine  the same turn one level down, at the C ABI (Engine.submit / step / drain, host token lists).
+  e2e_engine  the same turn one level down, at the C ABI (ft_engine_submit, the engine's own stepping thread, ft_engine_wait /
+            drain; host token lists).
   ws        the same turn one level up: the reference's UNCHANGED WebSocketLLMServer (baseline/_ref) in
             front of NativeHandler, 64 `websockets` clients in their own process, timed at the client.
   roofline  the dominant kernel (paged decode attention): algorithmic KV bytes per launch /
@@ -148,10 +149,13 @@ class ClockSampler:
             self.thread.join(timeout=1.0)
         if self.proc:
             self.proc.terminate()
-        lo = self.t_in if self.t_in is not None else 0.0
-        hi = self.t_out if self.t_out is not None else float("inf")
-        inside = [x for x in self.samples if lo <= x[0] <= hi]
-        if not inside and self.samples and self.t_in is not None:      # window shorter than one period: nearest samples
+
+    def report(self, t_in=None, t_out=None):
+        """Samples inside [t_in, t_out] (default: the mark()/unmark() window); the sampler may still be running."""
+        lo = t_in if t_in is not None else self.t_in if self.t_in is not None else 0.0
+        hi = t_out if t_out is not None else self.t_out if self.t_out is not None else float("inf")
+        inside = [x for x in list(self.samples) if lo <= x[0] <= hi]
+        if not inside and self.samples:                                 # window shorter than one period: nearest samples
             mid = 0.5 * (lo + (hi if hi != float("inf") else lo))
             inside = sorted(self.samples, key=lambda x: abs(x[0] - mid))[:2]
         sm = [x[1] for x in inside]
@@ -276,7 +280,7 @@ def run_native(args, rank, world, local_rank):
     ms = eng.timer_stop_ms()
     clocks.unmark()
     barrier()
-    clk = clocks.stop()
+    clk = clocks.report()               # (the sampler keeps running: the e2e turn below reports its own window)
     per_step = eng.step_times_ms()[-K:]
     st1 = eng.stats()
     ms_rank = ms
@@ -358,6 +362,11 @@ def run_native(args, rank, world, local_rank):
                 live.discard(r)
     e0 = eng.stats()
     eng.step_log()
+    native_loop = not args.no_native_loop
+    if not native_loop:
+        os.environ["FASTTALK_NATIVE_LOOP"] = "0"       # the handler and WebSocket levels step from Python as well
+    if native_loop:
+        eng.start_loop()               # the engine steps on its own thread; this one submits, waits and drains
     barrier()
     t_start = time.perf_counter()
     import numpy as np
@@ -372,7 +381,11 @@ def run_native(args, rank, world, local_rank):
     t_last = np.zeros(SESSIONS)
     gaps, n_out, n_live = [], 0, SESSIONS
     while n_live:
-        eng.step()
+        if native_loop:
+            if eng.wait_events(100) <= 0:
+                continue
+        else:
+            eng.step()
         now = time.perf_counter()
         n, rq, tk, fn = eng.drain_arrays()
         idx = (rq[:n] - rid0).astype(np.int64)
@@ -386,11 +399,18 @@ def run_native(args, rank, world, local_rank):
     first = {i: float(t_first[i]) for i in range(SESSIONS)}
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t_start
+    if native_loop:
+        eng.stop_loop()
+    e_clk = clocks.report(t_start, time.perf_counter())
+    clocks.stop()
     e2e_s = max_over_ranks(e2e_s)
     e1 = eng.stats()
     e_log = eng.step_log()
     # the steps streaming sessions waited longest for: [device ms, decode rows, prompt tokens, host ms]
     e_mixed = sorted((r for r in e_log.tolist() if r[1] > 0), key=lambda r: -r[0])[:4]
+    # the turn's pure decode steps: device ms and host ms (launch .. bookkeeping) per step
+    e_dec = [r for r in e_log.tolist() if r[1] >= SESSIONS and r[2] == 0]
+    e_dec_ms = [statistics.median(r[0] for r in e_dec), statistics.median(r[3] for r in e_dec)] if e_dec else None
     e_steps = e1["steps"] - e0["steps"]
     e2e_value = world * n_out / e2e_s
 
@@ -549,13 +569,15 @@ def run_native(args, rank, world, local_rank):
             "e2e_engine": {"value": e2e_value, "unit": "tok/s",
                     "h2d_bytes_per_step": (e1["h2d_bytes"] - e0["h2d_bytes"]) / max(e_steps, 1),
                     "d2h_bytes_per_step": (e1["d2h_bytes"] - e0["d2h_bytes"]) / max(e_steps, 1),
-                    "what": f"one turn/session via the C ABI (Engine.submit/step/drain) with host token lists: "
+                    "what": f"one turn/session via the C ABI (ft_engine_submit / {'ft_engine_start + wait' if not args.no_native_loop else 'step'} / drain) with host token lists: "
                             f"{CTX}-token history ({TURN_NEW} new, rest prefix-cached), {TURN_GEN} generated",
                     "steps": e_steps, "wall_s": e2e_s, "tokens": n_out,
                     "ttft_ms_p50": 1e3 * pct(list(first.values()), 0.5), "ttft_ms_p99": 1e3 * pct(list(first.values()), 0.99),
                     "itl_ms_p50": 1e3 * pct(gaps, 0.5), "itl_ms_p99": 1e3 * pct(gaps, 0.99),
                     "prefix_hit_tokens": e1["prefix_hit_tokens"] - e0["prefix_hit_tokens"],
                     "slowest_steps_with_decode_rows": [[round(x, 3) for x in r] for r in e_mixed],
+                    "decode_steps_in_turn_ms_p50": {"device": e_dec_ms[0], "host": e_dec_ms[1], "n": len(e_dec)} if e_dec_ms else None,
+                    "clocks_in_turn": {k: e_clk[k] for k in ("sm_mhz", "sm_min_mhz", "reasons", "samples", "power_w_max")},
                     "first_step": [round(x, 3) for x in e_log[0].tolist()] if len(e_log) else None},
             "ws": ws_level,
             "latency": {"itl_ms_p50_decode": ms / K, "ttft_ms_cold_2048_single": ttft_cold_ms,
@@ -634,6 +656,8 @@ def main():
     ap.add_argument("--tune", action="store_true", help="kernel tuning: print ms/step of the timed decode steps and exit")
     ap.add_argument("--prefill-cap", type=int, default=0,
                     help="engine decode_prefill_cap for the e2e runs (0 = engine default 896, < 0 = uncapped)")
+    ap.add_argument("--no-native-loop", action="store_true",
+                    help="step the engine from Python in the e2e levels instead of ft_engine_start's native thread (A/B)")
     ap.add_argument("--settle", type=float, default=2.0,
                     help="idle seconds between the set-up prefill and the warm-up (power-cap recovery; untimed)")
     args = ap.parse_args()

@@ -8,12 +8,15 @@
 
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
 #include <deque>
 #include <mutex>
 #include <new>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -141,6 +144,15 @@ struct Engine {
     cudaEvent_t s0 = nullptr, s1 = nullptr;
     struct StepRec { float gpu_ms, n_decode, n_prefill, host_ms; };
     std::deque<StepRec> step_log;          // most recent kStepTimes steps, oldest first
+
+    // the engine's own stepping thread (ft_engine_start): steps whenever something is runnable, so that no host
+    // language sits between two steps; the owner only submits, waits for events and drains them
+    std::thread loop_thread;
+    bool loop_on = false, loop_stop = false;
+    int loop_error = 0;
+    std::string loop_error_msg;
+    std::condition_variable cv_work;       // submit / cancel / stop -> the loop
+    std::condition_variable cv_out;        // events queued, loop failed or stopped -> ft_engine_wait
 };
 constexpr size_t kStepTimes = 4096;
 constexpr int kDefaultPrefillPlanes = 3;      // one fp16 plane x fp16 weight copies in the large prefill GEMMs (measured: DESIGN.md §2)
@@ -936,6 +948,7 @@ extern "C" ft_engine* ft_engine_create(const ft_engine_config* cfg, const ft_wei
 extern "C" void ft_engine_destroy(ft_engine* h) {
     if (!h) return;
     Engine* e = reinterpret_cast<Engine*>(h);
+    ft_engine_stop(h);
     DeviceGuard dg(e->dev);
     engine_free(e);
 }
@@ -988,6 +1001,7 @@ extern "C" long long ft_engine_submit(ft_engine* h, unsigned long long key, cons
     r->ignore_eos = ignore_eos;
     e->requests[r->id] = r;
     e->waiting.push_back(r);
+    e->cv_work.notify_one();
     return r->id;
 }
 
@@ -1045,7 +1059,95 @@ extern "C" int ft_engine_step(ft_engine* h) {
     std::lock_guard<std::mutex> dk(g_device_step_mu[e->dev % kMaxDevices]);
     DeviceGuard dg(e->dev);
     std::unique_lock<std::mutex> lk(e->mu);
+    FT_REQUIRE(!e->loop_on, "ft_engine_step: the engine runs its own stepping thread (ft_engine_start); stop it first");
     return engine_step(e, lk);
+}
+
+// ---- the engine's own stepping thread
+static bool runnable(const Engine* e) {           // under e->mu
+    for (const Request* r : e->waiting)
+        if (r->state != REQ_DONE) return true;
+    for (const Request* r : e->active)
+        if (r->state != REQ_DONE) return true;
+    return false;
+}
+
+static void loop_main(Engine* e) {
+    for (;;) {
+        {
+            std::unique_lock<std::mutex> lk(e->mu);
+            e->cv_work.wait_for(lk, std::chrono::milliseconds(20), [&] { return e->loop_stop || runnable(e); });
+            if (e->loop_stop) break;
+            if (!runnable(e)) continue;
+        }
+        int rc;
+        bool stepped;
+        {
+            std::lock_guard<std::mutex> sk(e->step_mu);
+            std::lock_guard<std::mutex> dk(g_device_step_mu[e->dev % kMaxDevices]);
+            DeviceGuard dg(e->dev);
+            std::unique_lock<std::mutex> lk(e->mu);
+            const long long before = e->st.steps;
+            rc = engine_step(e, lk);
+            stepped = e->st.steps != before;
+            if (rc < 0) {
+                e->loop_error = rc;
+                e->loop_error_msg = ft_last_error();
+            }
+        }
+        e->cv_out.notify_all();
+        if (rc < 0) break;
+        if (!stepped) std::this_thread::sleep_for(std::chrono::microseconds(200));    // waiting on pages / admission
+    }
+    {
+        std::lock_guard<std::mutex> lk(e->mu);
+        e->loop_on = false;
+    }
+    e->cv_out.notify_all();
+}
+
+extern "C" int ft_engine_start(ft_engine* h) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e, "ft_engine_start: null engine");
+    FT_REQUIRE(e->tp == 1, "ft_engine_start: tensor-parallel ranks are stepped in lock step by their host (tp.py)");
+    {
+        std::lock_guard<std::mutex> lk(e->mu);
+        if (e->loop_on) return 0;
+        FT_REQUIRE(e->loop_error == 0, "ft_engine_start: the stepping thread failed earlier: %s", e->loop_error_msg.c_str());
+    }
+    if (e->loop_thread.joinable()) e->loop_thread.join();       // a loop that ended by itself
+    {
+        std::lock_guard<std::mutex> lk(e->mu);
+        e->loop_stop = false;
+        e->loop_on = true;
+    }
+    e->loop_thread = std::thread(loop_main, e);
+    return 0;
+}
+
+extern "C" int ft_engine_stop(ft_engine* h) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e, "ft_engine_stop: null engine");
+    {
+        std::lock_guard<std::mutex> lk(e->mu);
+        e->loop_stop = true;
+    }
+    e->cv_work.notify_all();
+    if (e->loop_thread.joinable()) e->loop_thread.join();
+    return 0;
+}
+
+extern "C" int ft_engine_wait(ft_engine* h, int timeout_ms) {
+    Engine* e = reinterpret_cast<Engine*>(h);
+    FT_REQUIRE(e, "ft_engine_wait: null engine");
+    std::unique_lock<std::mutex> lk(e->mu);
+    e->cv_out.wait_for(lk, std::chrono::milliseconds(timeout_ms < 0 ? 0 : timeout_ms),
+                       [&] { return !e->out.empty() || e->loop_error != 0 || !e->loop_on; });
+    if (e->loop_error != 0 && e->out.empty()) {
+        set_last_error("ft_engine_wait: the stepping thread stopped: %s", e->loop_error_msg.c_str());
+        return -1;
+    }
+    return (int)e->out.size();
 }
 
 extern "C" int ft_engine_drain(ft_engine* h, long long* req_ids, int* tokens, int* finish, int cap) {
@@ -1083,6 +1185,7 @@ extern "C" int ft_engine_cancel(ft_engine* h, long long req) {
         return 0;
     }
     finish_request(e, it->second, 3, -1);
+    e->cv_out.notify_all();
     return 0;
 }
 

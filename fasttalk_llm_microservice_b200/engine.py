@@ -133,6 +133,18 @@ class Engine:
         """One continuous-batching iteration; returns tokens produced (0 when idle)."""
         return N.check(self.lib.ft_engine_step(self._h), "ft_engine_step")
 
+    # the engine's own stepping thread (ft_engine_start): the owner submits, waits and drains; nothing in Python sits
+    # between two steps
+    def start_loop(self):
+        N.check(self.lib.ft_engine_start(self._h), "ft_engine_start")
+
+    def stop_loop(self):
+        N.check(self.lib.ft_engine_stop(self._h), "ft_engine_stop")
+
+    def wait_events(self, timeout_ms: int = 50) -> int:
+        """Block (GIL released) until the stepping thread has queued events; returns how many (0 = timeout)."""
+        return N.check(self.lib.ft_engine_wait(self._h, int(timeout_ms)), "ft_engine_wait")
+
     def drain(self) -> List[Tuple[int, int, Optional[str]]]:
         """(request id, token, finish_reason|None) for everything produced since the last drain."""
         out = []

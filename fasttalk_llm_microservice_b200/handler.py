@@ -83,6 +83,10 @@ class EngineRunner:
         # Detokenising and posting a step's tokens is Python work (a few hundred microseconds at 64 sessions);
         # it runs on its own thread so that the engine thread is back inside ft_engine_step — which releases
         # the GIL — right away, and the GPU does not idle while tokens are being delivered.
+        # Engines with a stepping thread of their own (ft_engine_start; not the tensor-parallel leader, not test doubles)
+        # are not stepped from Python at all; FASTTALK_NATIVE_LOOP=0 keeps the Python loop (A/B, debugging).
+        self._native_loop = (hasattr(engine, "start_loop") and getattr(engine, "tp_size", 1) == 1
+                             and os.environ.get("FASTTALK_NATIVE_LOOP", "1") != "0")
         self._dq: "queue.SimpleQueue" = queue.SimpleQueue()
         self._dthread = threading.Thread(target=self._dispatch_loop, name="fasttalk-b200-dispatch", daemon=True)
         self._dthread.start()
@@ -135,6 +139,24 @@ class EngineRunner:
             if dev is not None:                 # a fresh thread starts on device 0: make the engine's GPU current
                 import torch
                 torch.cuda.set_device(dev)
+            if self._native_loop:
+                # the engine steps on its own native thread; this one only waits for events (GIL released) and hands
+                # them to the dispatch thread — no Python between two steps
+                self.engine.start_loop()
+                try:
+                    while not self._stop:
+                        if self.engine.wait_events(50) > 0:
+                            self.last_step_time = time.time()
+                            events = self.engine.drain()
+                            if events:
+                                self._dq.put(events)
+                        else:
+                            with self._lock:
+                                if not self._sinks:
+                                    self.last_step_time = time.time()      # idle, not stuck
+                finally:
+                    self.engine.stop_loop()
+                return
             while not self._stop:
                 with self._lock:
                     busy = bool(self._sinks)

@@ -80,6 +80,9 @@ SIGNATURES = {
     "ft_engine_destroy": (None, [_VP]),
     "ft_engine_submit": (_LL, [_VP, _ULL, _VP, _I, _F, _I, _F, _I, _ULL, _I]),
     "ft_engine_step": (_I, [_VP]),
+    "ft_engine_start": (_I, [_VP]),
+    "ft_engine_stop": (_I, [_VP]),
+    "ft_engine_wait": (_I, [_VP, _I]),
     "ft_engine_drain": (_I, [_VP, _VP, _VP, _VP, _I]),
     "ft_engine_cancel": (_I, [_VP, _LL]),
     "ft_engine_session_close": (_I, [_VP, _ULL]),

@@ -124,6 +124,19 @@ long long ft_engine_submit(ft_engine* e, unsigned long long session_key, const i
  * the step's tokens are on the host.  Returns the number of tokens produced (0 = idle). */
 int ft_engine_step(ft_engine* e);
 
+/* The engine's own stepping thread, instead of calling ft_engine_step from the host language: ft_engine_start spawns a
+ * native thread that runs one step after the other while anything is runnable (and sleeps on a condition variable
+ * otherwise), so that nothing — no interpreter, no lock of the host language — sits between two steps; the owner submits,
+ * cancels and closes as before (all thread-safe), blocks in ft_engine_wait until events are queued and drains them.
+ * ft_engine_step is refused while the thread runs.  ft_engine_stop joins it (ft_engine_destroy does so too); start / stop
+ * may alternate.  Not for tensor-parallel engines (their hosts step both ranks in lock step).
+ * ft_engine_wait: blocks up to timeout_ms; returns the number of queued events (0 = timeout), or < 0 when the stepping
+ * thread died on an error (ft_last_error has it) and nothing is left to drain.
+ * No counterpart in the reference: its engines (Ollama, vLLM) are separate server processes. */
+int ft_engine_start(ft_engine* e);
+int ft_engine_stop(ft_engine* e);
+int ft_engine_wait(ft_engine* e, int timeout_ms);
+
 /* Drain the tokens produced since the last drain, over all requests: parallel HOST arrays of
  * (request id, token, finish flag: 0 running, 1 stop token, 2 length, 3 cancelled, 4 error).
  * Returns the number of entries written (<= cap). */

@@ -489,6 +489,65 @@ def test_prompt_tokens_beside_streaming_sessions_are_capped_to_a_token_tile():
         eng.close()
 
 
+def test_native_stepping_thread_equals_stepping_from_python():
+    """ft_engine_start: the engine steps on its own native thread, the owner only submits, waits and drains.  Same tokens
+    as stepping from Python; ft_engine_step is refused meanwhile; cancel reaches a running request; stop / start
+    alternate and Python stepping works again after a stop."""
+    import time
+    from fasttalk_llm_microservice_b200 import native as N
+    spec, w, g = _tiny_setup()
+    gen = torch.Generator().manual_seed(5)
+    prompts = [g["prompt"].tolist()] + [torch.randint(0, spec.vocab, (n,), generator=gen).tolist() for n in (300, 40, 700)]
+    ref = make_engine(spec, w, max_batch=8, max_batched_tokens=512)
+    eng = make_engine(spec, w, max_batch=8, max_batched_tokens=512)
+    try:
+        want = ref.generate(prompts, max_new_tokens=24, sessions=[f"r{i}" for i in range(4)], ignore_eos=True)
+        eng.start_loop()
+        eng.start_loop()                                        # idempotent
+        with pytest.raises(N.NativeError, match="stepping thread"):
+            eng.step()
+
+        def collect(rids, limit_s=30.0):
+            out, fin = {r: [] for r in rids}, {}
+            t_end = time.time() + limit_s
+            while len(fin) < len(rids):
+                assert time.time() < t_end, (out, fin)
+                if eng.wait_events(100) <= 0:
+                    continue
+                for rid, tok, f in eng.drain():
+                    if rid in out:
+                        if tok >= 0:
+                            out[rid].append(tok)
+                        if f is not None:
+                            fin[rid] = f
+            return [out[r] for r in rids], [fin[r] for r in rids]
+        rids = [eng.submit(f"n{i}", p, max_new_tokens=24, ignore_eos=True) for i, p in enumerate(prompts)]
+        got, fin = collect(rids)
+        assert got == want and fin == ["length"] * 4
+        assert eng.wait_events(20) == 0                          # idle: times out, no busy loop needed to see it
+        # a request that would run for a long time is cancelled from outside while the thread steps it
+        rid = eng.submit("long", prompts[1], max_new_tokens=600, ignore_eos=True)
+        seen = 0
+        t_end = time.time() + 30
+        while seen < 5:
+            assert time.time() < t_end
+            if eng.wait_events(100) > 0:
+                seen += sum(1 for r, tok, f in eng.drain() if r == rid and tok >= 0)
+        eng.cancel(rid)
+        _, fin = collect([rid])
+        assert fin == ["cancelled"]
+        eng.stop_loop()
+        eng.stop_loop()
+        assert eng.generate([prompts[0]], max_new_tokens=8, sessions=["again"], ignore_eos=True)[0] == want[0][:8]
+        eng.start_loop()                                        # and once more
+        rid = eng.submit("n2", prompts[2], max_new_tokens=24, ignore_eos=True)     # prefix of session n2 is cached
+        got, fin = collect([rid])
+        assert got[0] == want[2]
+    finally:
+        ref.close()
+        eng.close()                                             # joins the thread
+
+
 def test_engine_stepped_from_a_fresh_thread():
     """Every ft_engine_* entry makes the engine's device current itself: a thread that never called cudaSetDevice
     (current device 0) can step an engine that lives on another GPU.  With one GPU the thread part still runs."""
