@@ -204,12 +204,21 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def claim_stdout():
+    """stdout carries exactly ONE line, the JSON record.  Everything else this process prints goes to stderr — Python's
+    prints (the reference server's loggers write to sys.stdout at every level) and what native libraries write to file
+    descriptor 1 (NCCL prints its version line there).  Returns the file object the record is written to."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = sys.stderr
+    return real
+
+
 # ----------------------------------------------------------------------------- our arm
 def run_native(args, rank, world, local_rank):
     import torch
-    # stdout carries exactly ONE line, the JSON record: everything else this process prints (the reference
-    # server's loggers write to sys.stdout at every level) goes to stderr
-    real_stdout, sys.stdout = sys.stdout, sys.stderr
+    real_stdout = claim_stdout()
     from fasttalk_llm_microservice_b200 import build
     from fasttalk_llm_microservice_b200.engine import Engine, EngineLimits
     from fasttalk_llm_microservice_b200.model_spec import get_spec
@@ -602,7 +611,7 @@ def run_tp(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     assert world == 2, "--tp 2 needs exactly two ranks (torchrun --nproc-per-node 2)"
-    real_stdout, sys.stdout = sys.stdout, sys.stderr
+    real_stdout = claim_stdout()
     torch.cuda.set_device(local_rank)
     dist.init_process_group("gloo")
     sys.path.insert(0, os.path.join(ROOT, "scripts"))
