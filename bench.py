@@ -389,9 +389,11 @@ def run_native(args, rank, world, local_rank):
     t_first = np.full(SESSIONS, -1.0)
     t_last = np.zeros(SESSIONS)
     gaps, n_out, n_live = [], 0, SESSIONS
+    n_timeouts = 0
     while n_live:
         if native_loop:
             if eng.wait_events(100) <= 0:
+                n_timeouts += 1
                 continue
         else:
             eng.step()
@@ -408,6 +410,8 @@ def run_native(args, rank, world, local_rank):
     first = {i: float(t_first[i]) for i in range(SESSIONS)}
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t_start
+    print(f"[rank {rank}] e2e_engine turn: {e2e_s * 1e3:.1f} ms, {n_timeouts} wait time-outs, largest gap "
+          f"{1e3 * max(gaps):.1f} ms, last first token at {1e3 * float(t_first.max()):.1f} ms", file=sys.stderr, flush=True)
     if native_loop:
         eng.stop_loop()
     e_clk = clocks.report(t_start, time.perf_counter())

@@ -161,6 +161,24 @@ constexpr int kDefaultDecodePrefillCap = 896;    // <= 128 decode rows + 896 -> 
 
 // Every entry point that touches CUDA makes the engine's device current for its duration: the caller may be a
 // thread whose current device is another GPU (a fresh thread starts on device 0).
+// Does `dev` have a live primary context in this process?  (driver API through the runtime's entry-point lookup; on
+// any doubt: yes)
+static bool primary_ctx_active(int dev) {
+    typedef CUresult (*Fn)(CUdevice, unsigned int*, int*);
+    static Fn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuDevicePrimaryCtxGetState", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<Fn>(p);
+    }();
+    unsigned int flags = 0;
+    int active = 1;
+    if (!fn || fn((CUdevice)dev, &flags, &active) != CUDA_SUCCESS) return true;
+    return active != 0;
+}
+
 struct DeviceGuard {
     int prev = -1, dev;
     explicit DeviceGuard(int d) : dev(d) {
@@ -168,7 +186,10 @@ struct DeviceGuard {
         if (prev != dev) cudaSetDevice(dev);
     }
     ~DeviceGuard() {
-        if (prev >= 0 && prev != dev) cudaSetDevice(prev);
+        // Back to the caller's device — unless that is only the default of a thread that never touched a GPU: since
+        // CUDA 12 cudaSetDevice creates the device's context, and "restoring" device 0 from a process that lives on
+        // another GPU would build one there (0.4 s and ~0.5 GB on a GPU that belongs to another rank).
+        if (prev >= 0 && prev != dev && primary_ctx_active(prev)) cudaSetDevice(prev);
     }
 };
 // The split-K rendezvous and the tensor-parallel flag wait spin inside kernels and need every CTA of a launch
@@ -1073,6 +1094,10 @@ static bool runnable(const Engine* e) {           // under e->mu
 }
 
 static void loop_main(Engine* e) {
+    // a fresh thread's current device is 0: make the engine's GPU current for the thread's whole life, so that the
+    // per-step DeviceGuard has nothing to restore (restoring "device 0" from a rank that lives on another GPU creates a
+    // context there — 0.4 s the first time)
+    cudaSetDevice(e->dev);
     for (;;) {
         {
             std::unique_lock<std::mutex> lk(e->mu);
