@@ -229,6 +229,20 @@ def projections(rows):
                             "ours_useful_TFLOPs": flops / us / 1e6, "ours_issued_TFLOPs": 2 * flops / us / 1e6,
                             "torch_TFLOPs": flops / us_t / 1e6, "torch_frac_tensor": flops / us_t / 1e6 / PEAK_TF,
                             "ours_issued_frac_tensor": 2 * flops / us / 1e6 / PEAK_TF})
+                # the form the engine's large prefill steps run since round 2: ONE fp16 plane against fp16 weight copies
+                # (CTA-pair kernels), here with a plain bf16 output like the library call, and the library on fp16 too
+                x16 = x32.half()
+                ws16 = [w.half() for w in ws]
+                ob = torch.empty(T, n_out, device=DEV, dtype=torch.bfloat16)
+                one = [(lambda w=w: K.gemm_fused(w, x16, None, N.EPI_BF16, n_splits=1, x_planes=3, out=ob)) for w in ws16]
+                us16 = timed(one, iters=20)
+                us_t16 = timed([(lambda w=w: torch.matmul(x16, w.t())) for w in ws16], iters=20)
+                ref16 = x16.float() @ ws16[-1].float().T
+                err16 = ((ob.float() - ref16).abs().max() / ref16.abs().max()).item()
+                row.update({"ours_f16_plane_us": us16, "ours_f16_plane": "ft_gemm_fused x_planes=3 (one fp16 plane x fp16 weights, CTA pairs), bf16 output",
+                            "ours_f16_plane_TFLOPs": flops / us16 / 1e6, "torch_matmul_f16_us": us_t16,
+                            "torch_f16_TFLOPs": flops / us_t16 / 1e6, "ours_f16_plane_over_torch_time": us16 / us_t16,
+                            "ours_f16_plane_rel_err": err16})
             row["ours_over_torch_time"] = row["ours_us"] / us_t
             rows.append(row)
             print(json.dumps(row), flush=True)
