@@ -552,17 +552,22 @@ static int engine_step(Engine* e, std::unique_lock<std::mutex>& lk) {
     for (Request* r : e->active)
         if (r->state == REQ_DECODE) dec.push_back(r);
     int budget = c.max_batched_tokens - (int)dec.size();
-    // Sessions that are streaming wait for the whole step: beside decode rows a step admits at most
-    // `decode_prefill_cap` prompt tokens (a ~1k-token chunk adds a few ms to a 1B step instead of the ~35 ms a full
-    // 8192-token budget costs).  The cap holds while at least as many sessions are streaming as are waiting for
-    // their first token; when more are waiting than streaming (a burst of arrivals behind one early bird, or an
-    // engine with nothing decoding) the step takes the whole budget: first tokens for the many come soonest.
+    // Sessions that are streaming wait for the whole step: beside decode rows a step admits about
+    // `decode_prefill_cap` prompt tokens (a ~1k-token chunk adds a few ms to a 1B step instead of the ~20 ms a full
+    // 8192-token budget costs).  Once more than two sessions wait for their first token PER streaming session the
+    // allowance grows in that proportion (cap x waiting / (2 x streaming)): a burst of 63 arrivals behind one early
+    // bird gets the whole budget (one session waits 20 ms, 63 get their first token soonest), 56 arrivals beside 8
+    // streaming sessions 3.5 x the cap, 35 beside 29 the cap — no cliff at "more waiting than streaming" that would
+    // stall half of the sessions for a full-budget step.
     int n_pending = 0;
     for (Request* r : e->active) n_pending += r->state == REQ_PREFILL;
-    if (e->decode_prefill_cap > 0 && !dec.empty() && (int)dec.size() >= n_pending) {
+    if (e->decode_prefill_cap > 0 && !dec.empty()) {
+        const long long n_dec = (long long)dec.size();
+        const long long allow = (long long)e->decode_prefill_cap * std::max<long long>(n_pending, 2 * n_dec) / (2 * n_dec);
         // the projections work on 128-token tiles, so the rows up to the next tile boundary ride for free
-        const int rows = (int)dec.size() + e->decode_prefill_cap;
-        budget = std::min(budget, (rows + kGemmTokenTile - 1) / kGemmTokenTile * kGemmTokenTile - (int)dec.size());
+        const long long rows = n_dec + allow;
+        const long long tiled = (rows + kGemmTokenTile - 1) / kGemmTokenTile * kGemmTokenTile - n_dec;
+        budget = (int)std::min<long long>(budget, tiled);
     }
     for (Request* r : e->active) {
         if (r->state != REQ_PREFILL || budget <= 0) continue;

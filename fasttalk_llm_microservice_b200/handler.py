@@ -16,6 +16,7 @@ ONE wake-up carrying all of that step's tokens, so 64 sessions
 from __future__ import annotations
 
 import asyncio
+import contextlib
 import logging
 import os
 import queue
@@ -87,6 +88,7 @@ class EngineRunner:
         # are not stepped from Python at all; FASTTALK_NATIVE_LOOP=0 keeps the Python loop (A/B, debugging).
         self._native_loop = (hasattr(engine, "start_loop") and getattr(engine, "tp_size", 1) == 1
                              and os.environ.get("FASTTALK_NATIVE_LOOP", "1") != "0")
+        self._paused = False
         self._dq: "queue.SimpleQueue" = queue.SimpleQueue()
         self._dthread = threading.Thread(target=self._dispatch_loop, name="fasttalk-b200-dispatch", daemon=True)
         self._dthread.start()
@@ -111,6 +113,24 @@ class EngineRunner:
                 except Exception:  # noqa: BLE001
                     pass
         self._wake.set()
+
+    @contextlib.contextmanager
+    def paused(self):
+        """Hand the engine to the caller for the duration (parity checks step it themselves and read the logits of every
+        step): the engine's own stepping thread is stopped and started again afterwards.  Only while no request of this
+        runner is in flight."""
+        with self._lock:
+            assert not self._sinks, "EngineRunner.paused(): requests are in flight"
+        if not self._native_loop:
+            yield self.engine                   # the Python loop only steps while it has requests of its own
+            return
+        self._paused = True
+        self.engine.stop_loop()
+        try:
+            yield self.engine
+        finally:
+            self.engine.start_loop()
+            self._paused = False
 
     def alive(self) -> bool:
         return self._thread.is_alive() and self.error is None
@@ -145,6 +165,9 @@ class EngineRunner:
                 self.engine.start_loop()
                 try:
                     while not self._stop:
+                        if self._paused:                        # the engine is on loan (paused()): nothing to wait for
+                            time.sleep(0.005)
+                            continue
                         if self.engine.wait_events(50) > 0:
                             self.last_step_time = time.time()
                             events = self.engine.drain()

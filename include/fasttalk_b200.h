@@ -55,9 +55,11 @@ typedef struct {
     /* Prompt tokens a step may admit WHILE other sequences are decoding (they all wait for the step): the
      * latency side of vLLM's --max-num-batched-tokens trade-off (docker-compose.vllm.yml:48).  0 = default
      * (896), < 0 = no cap (every step may fill max_batched_tokens).  The admitted count is rounded up so that decode
-     * rows + prompt tokens end on a 128-token tile of the projections (those rows cost nothing more).  The cap applies while at least as many
-     * sequences are decoding as are waiting for their first token; otherwise (nothing decoding, or a burst of
-     * arrivals that outnumbers the decoding sequences) the step uses the full max_batched_tokens budget. */
+     * rows + prompt tokens end on a 128-token tile of the projections (those rows cost nothing more).  The allowance
+     * grows with the number of sequences waiting for their first token per decoding sequence (cap x waiting /
+     * (2 x decoding) once more than two wait per decoding one): one early bird ahead of a burst of 63 arrivals does not
+     * hold the burst back, 35 arrivals beside 29 decoding sequences get the cap.  With nothing decoding a step uses the
+     * full max_batched_tokens. */
     int decode_prefill_cap;
     /* How the large prefill projections (more tiles than SMs, 128-token tiles) multiply their activations:
      * 0 = default, 1 = bf16 hi plane only, 2 = bf16 hi + lo planes (two MMAs per tile), 3 = ONE fp16 plane

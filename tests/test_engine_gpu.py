@@ -447,9 +447,9 @@ def test_two_engines_share_one_gpu_and_step_concurrently():
 
 
 def test_prompt_tokens_beside_streaming_sessions_are_capped_to_a_token_tile():
-    """`decode_prefill_cap`: while at least as many sessions stream as wait for a first token, a step admits prompt tokens
-    only up to the 128-token tile boundary at or above (decode rows + cap); when more wait than stream the step takes
-    the whole budget.  What is generated does not depend on the cap."""
+    """`decode_prefill_cap`: beside streaming sessions a step admits prompt tokens only up to the 128-token tile boundary at
+    or above (decode rows + cap); the allowance grows with the number of sessions waiting per streaming session.  What is
+    generated does not depend on the cap."""
     spec, w, g = _tiny_setup()
     gen = torch.Generator().manual_seed(11)
     short = [torch.randint(0, spec.vocab, (24,), generator=gen).tolist() for _ in range(5)]
@@ -458,8 +458,7 @@ def test_prompt_tokens_beside_streaming_sessions_are_capped_to_a_token_tile():
     eng = make_engine(spec, w, max_batch=12, max_batched_tokens=2048, decode_prefill_cap=200)
     try:
         want = ref.generate(long_[:3], max_new_tokens=6, sessions=["r0", "r1", "r2"], ignore_eos=True)
-        for i, p in enumerate(short):
-            eng.submit(f"s{i}", p, max_new_tokens=400, ignore_eos=True)
+        short_rids = [eng.submit(f"s{i}", p, max_new_tokens=400, ignore_eos=True) for i, p in enumerate(short)]
         eng.step(); eng.drain()                                   # nothing streams yet: the first step is uncapped
         rids = [eng.submit(f"l{i}", long_[i], max_new_tokens=6, ignore_eos=True) for i in range(3)]
         eng.step_log()
@@ -477,13 +476,18 @@ def test_prompt_tokens_beside_streaming_sessions_are_capped_to_a_token_tile():
         # streaming rows + prompt tokens fill two 128-token tiles (5 + 200 -> 256) until the 2100 tokens are through
         full = [r for r in rows if r[1] >= 5 and r[2] > 0][:-1]
         assert len(full) >= 7 and all(int(r[1] + r[2]) == 256 for r in full) and sum(capped) == 2100, rows
-        # six arrivals behind five streaming sessions: more wait than stream, the step takes the whole budget
+        # the allowance grows with the sessions waiting PER streaming session (cap x waiting / (2 x streaming)): six
+        # arrivals behind ONE early bird get 3 x 200 prompt tokens (1 + 600 rows -> five 128-token tiles -> 639), not the
+        # cap and not the whole budget
+        for r in short_rids[1:]:
+            eng.cancel(r)
+        eng.step(); eng.drain()
         for i in range(6):
             eng.submit(f"m{i}", long_[i][::-1], max_new_tokens=1, ignore_eos=True)
         eng.step_log()
         eng.step(); eng.drain()
         burst = eng.step_log()[-1].tolist()
-        assert int(burst[2]) >= 2000, burst
+        assert (int(burst[1]), int(burst[2])) == (1, 639), burst
     finally:
         ref.close()
         eng.close()

@@ -28,13 +28,13 @@ def stack():
     eng = Engine(spec, w, EngineLimits(max_batch=16, max_batched_tokens=512, max_context=2048), eos_ids=())
     runner = EngineRunner(eng, tok)
     h = NativeHandler(model="tiny-d64", runner=runner)
-    yield h, eng, tok, spec, w
+    yield h, eng, tok, spec, w, runner
     runner.shutdown()
     eng.close()
 
 
 def test_concurrent_sessions_stream_engine_tokens(stack):
-    h, eng, tok, spec, w = stack
+    h, eng, tok, spec, w, runner = stack
     convs = [[{"role": "system", "content": "s" * i}, {"role": "user", "content": f"question {i} " + "x" * (7 * i)}]
              for i in range(1, 13)]
 
@@ -66,7 +66,8 @@ def test_concurrent_sessions_stream_engine_tokens(stack):
             pieces.append((len(ref) - 1, tail))
         # the engine itself on this conversation, all 20 positions against the oracle (teacher-forced, near-ties
         # re-aligned: oracle/parity.py); the runner thread is idle while no handler request is in flight
-        job = P.check(eng, f"handler conversation {i}", f"direct-{i}", prompt, ref, ref_logits, min_distinct=1)   # templated byte prompts on the tiny model may loop
+        with runner.paused():                    # (the engine otherwise steps on its own thread)
+            job = P.check(eng, f"handler conversation {i}", f"direct-{i}", prompt, ref, ref_logits, min_distinct=1)   # templated byte prompts on the tiny model may loop
         eng.close_session(f"direct-{i}")
         # the handler's chunks are the oracle's pieces; a stream cannot be re-aligned, so it is compared up to the
         # first near-tie, which must be one by the measured-error rule (not the 2e-2 logit tolerance)
@@ -81,7 +82,7 @@ def test_concurrent_sessions_stream_engine_tokens(stack):
 
 
 def test_multi_turn_history_hits_the_kv_cache(stack):
-    h, eng, tok, spec, w = stack
+    h, eng, tok, spec, w, runner = stack
     msgs = [{"role": "system", "content": "be brief"}, {"role": "user", "content": "first question, fairly long " * 4}]
     a1 = "".join(h.generate_stream(msgs, temperature=0.0, max_tokens=16, request_id="conv-A"))
     hits0 = eng.stats()["prefix_hit_tokens"]
@@ -99,7 +100,7 @@ def test_multi_turn_history_hits_the_kv_cache(stack):
 
 
 def test_disconnect_frees_the_slot_and_sampling_runs(stack):
-    h, eng, tok, spec, w = stack
+    h, eng, tok, spec, w, runner = stack
 
     async def disconnect():
         agen = h.generate_stream_async([{"role": "user", "content": "hello"}], temperature=0.7, top_p=0.9,
