@@ -450,7 +450,13 @@ def run_native(args, rank, world, local_rank):
     # Inside the timed region: chat template + tokenisation, submit, the engine thread's steps (metadata H2D, sampled
     # ids D2H), detokenisation, one call_soon_threadsafe per step, the asyncio queues.
     import asyncio
+    import gc
     import random
+    # This process holds ~10^7 Python objects by now (token lists of the set-up): a full collection takes tens of
+    # milliseconds and, in the middle of a turn, shows up as a 60 ms inter-token gap at the WebSocket level.  Collect once
+    # and take what exists out of the collector's sight, as a long-running server does after start-up.
+    gc.collect()
+    gc.freeze()
     from fasttalk_llm_microservice_b200.handler import EngineRunner, NativeHandler
     from fasttalk_llm_microservice_b200.tokenizer import ByteTokenizer
     tok = ByteTokenizer(spec.vocab)

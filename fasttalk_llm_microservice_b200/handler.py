@@ -295,6 +295,13 @@ def build_runner(model: str) -> EngineRunner:
                        max_context=_env_int("FASTTALK_MAX_CONTEXT", _env_int("DEFAULT_CONTEXT_WINDOW", 8192)),
                        decode_prefill_cap=_env_int("FASTTALK_DECODE_PREFILL_CAP", 0))
     eng = Engine(spec, w, lim, eos_ids=tok.eos_ids)
+    # Loading a checkpoint and a tokenizer leaves millions of long-lived Python objects behind; a full collection over
+    # them later takes tens of milliseconds and lands in the middle of somebody's stream.  Collect once and move what
+    # exists out of the collector's generations (FASTTALK_GC_FREEZE=0 leaves the collector alone).
+    if os.environ.get("FASTTALK_GC_FREEZE", "1") != "0":
+        import gc
+        gc.collect()
+        gc.freeze()
     return EngineRunner(eng, tok)
 
 
