@@ -334,6 +334,42 @@ def test_llama1b_config2_full_size_64_sessions_2k_history(llama1b):
         eng.close_session(f"solo{i}")
 
 
+def test_llama1b_decode_steps_of_more_than_128_rows():
+    """BASELINE config 3's shape (256 sessions on one GPU) puts more than 128 rows into a decode step: two or more
+    128-token tiles, which run on the CTA-pair kernels in their one-fp16-plane form.  160 sessions of the 1B model decode
+    together; three of them are checked against the fp32 oracle at every position (teacher-forced logits, greedy tokens)."""
+    from fasttalk_llm_microservice_b200.model_spec import LLAMA_3_2_1B as spec
+    from fasttalk_llm_microservice_b200.weights import init_weights
+    w = init_weights(spec, seed=0, device="cuda")
+    w32 = {k: v.float() for k, v in w.items() if k != "lm_head"}
+    w32["lm_head"] = w32["embed"]
+    eng = make_engine(spec, w, max_batch=160, max_batched_tokens=4096, max_context=512, debug_logit_rows=192)
+    try:
+        gen = torch.Generator().manual_seed(160)
+        prompts = [torch.randint(0, 128000, (96 + (i % 5),), generator=gen).tolist() for i in range(160)]
+        n_new, checked, jobs = 24, (0, 77, 159), []
+        for i in checked:
+            with torch.no_grad():
+                ref_tokens, ref_logits = O.greedy_generate(w32, spec, torch.tensor(prompts[i]), n_new, return_logits=True)
+            jobs.append(P.Job(f"1B session {i} among 160 decoding rows", f"wide{i}", prompts[i], ref_tokens, ref_logits))
+        fillers = [eng.submit(f"wide{i}", prompts[i], max_new_tokens=n_new + 16, ignore_eos=True)
+                   for i in range(160) if i not in checked]
+        st0 = eng.stats()
+        P.run(eng, jobs)
+        st1 = eng.stats()
+        rows_per_step = (st1["decode_tokens"] - st0["decode_tokens"]) / max(1, st1["decode_steps"] - st0["decode_steps"])
+        assert rows_per_step > 128, rows_per_step       # (the average includes the steps in which sessions were still joining)
+        for r in fillers:
+            eng.cancel(r)
+        eng.step(); eng.drain()
+        for j in jobs:
+            P.finish(j)
+    finally:
+        eng.close()
+        del w, w32
+        torch.cuda.empty_cache()
+
+
 def test_llama1b_long_context_8k_window():
     """BASELINE config 4's window on the 1B weights: an 8300-token history (past the 8192 original RoPE range,
     130 KV pages, chunked prefill in 8192-token steps), last-position logits and 8 greedy tokens vs the oracle."""
