@@ -64,3 +64,59 @@ class FakeEngine:
 
     def stats(self):
         return {"steps": self.steps, "active_requests": len(self.reqs)}
+
+
+class FakeLoopEngine(FakeEngine):
+    """The same double with a stepping thread of its own, like ft_engine_start / ft_engine_wait / ft_engine_stop: the
+    runner must never call step() while it runs."""
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self.cv = threading.Condition(self.lock)
+        self.loop_thread, self.loop_on, self.loop_stop = None, False, False
+        self.stepped_by_owner = 0
+        self.starts = 0
+
+    def step(self):
+        if self.loop_on and threading.current_thread() is not self.loop_thread:
+            self.stepped_by_owner += 1
+            raise RuntimeError("ft_engine_step: the engine runs its own stepping thread")
+        n = super().step()
+        with self.cv:
+            self.cv.notify_all()
+        return n
+
+    def _loop(self):
+        import time
+        while not self.loop_stop:
+            if self.reqs:
+                self.step()
+                time.sleep(0.0005)
+            else:
+                time.sleep(0.001)
+
+    def start_loop(self):
+        if self.loop_on:
+            return
+        self.starts += 1
+        self.loop_stop, self.loop_on = False, True
+        self.loop_thread = threading.Thread(target=self._loop, daemon=True)
+        self.loop_thread.start()
+
+    def stop_loop(self):
+        self.loop_stop = True
+        if self.loop_thread is not None:
+            self.loop_thread.join(timeout=5)
+        self.loop_on = False
+
+    def wait_events(self, timeout_ms=50):
+        with self.cv:
+            if not self.out and self.loop_on:
+                self.cv.wait(timeout_ms / 1000.0)
+            return len(self.out)
+
+    def cancel(self, rid):
+        r = super().cancel(rid)
+        with self.cv:
+            self.cv.notify_all()
+        return r

@@ -11,7 +11,7 @@ import pytest
 from fasttalk_llm_microservice_b200.errors import LLMServiceError
 from fasttalk_llm_microservice_b200.handler import EngineRunner, NativeHandler
 from fasttalk_llm_microservice_b200.tokenizer import ByteTokenizer
-from fake_engine import FakeEngine
+from fake_engine import FakeEngine, FakeLoopEngine
 
 REF = os.environ.get("FASTTALK_REFERENCE_PATH", "/root/reference")
 HAVE_REF = os.path.exists(os.path.join(REF, "app", "core", "vllm_handler.py"))
@@ -252,3 +252,42 @@ def test_async_generation_times_out_when_the_engine_goes_quiet():
         return [c async for c in h2.generate_stream_async([{"role": "user", "content": "hi"}], request_id="slow")]
     assert "".join(asyncio.run(go2())) == "abcdefghijklmnopqrst"
     runner2.shutdown()
+
+
+def test_runner_leaves_the_stepping_to_an_engine_that_steps_itself():
+    """Engines with a stepping thread of their own (ft_engine_start) are never stepped from Python: the runner waits for
+    events, drains and dispatches; paused() lends the engine out (its thread stopped) and starts it again; shutdown
+    stops it."""
+    tok = ByteTokenizer()
+    eng = FakeLoopEngine(tok, "Stepped by the engine itself.")
+    runner = EngineRunner(eng, tok)
+    h = NativeHandler(base_url="http://ignored/v1", model="llama3.2:1b", runner=runner)
+    msgs = [{"role": "user", "content": "hi"}]
+    assert "".join(h.generate_stream(msgs, request_id="a")) == "Stepped by the engine itself."
+
+    async def many():
+        async def one(i):
+            return "".join([c async for c in h.generate_stream_async(msgs, request_id=f"s{i}")])
+        return await asyncio.gather(*[one(i) for i in range(8)])
+    assert asyncio.run(many()) == ["Stepped by the engine itself."] * 8
+    assert eng.loop_on and eng.stepped_by_owner == 0 and eng.starts == 1
+    with runner.paused() as lent:
+        assert lent is eng and not eng.loop_on
+        rid = eng.submit("direct", tok.encode("x"), max_new_tokens=3)
+        while not any(r == rid and fin for r, t, fin in eng.drain()):
+            eng.step()                                   # the borrower steps it
+    assert eng.loop_on and eng.starts == 2
+    assert "".join(h.generate_stream(msgs, request_id="b")) == "Stepped by the engine itself."
+    runner.shutdown()
+    assert not eng.loop_on and eng.stepped_by_owner == 0
+
+
+def test_native_loop_can_be_switched_off(monkeypatch):
+    monkeypatch.setenv("FASTTALK_NATIVE_LOOP", "0")
+    tok = ByteTokenizer()
+    eng = FakeLoopEngine(tok, "Stepped from Python.")
+    runner = EngineRunner(eng, tok)
+    h = NativeHandler(base_url="http://ignored/v1", model="llama3.2:1b", runner=runner)
+    assert "".join(h.generate_stream([{"role": "user", "content": "hi"}], request_id="a")) == "Stepped from Python."
+    assert eng.starts == 0 and eng.steps > 0
+    runner.shutdown()
