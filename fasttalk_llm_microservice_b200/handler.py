@@ -9,9 +9,11 @@ generated token), same `check_connection`, `get_model_info`, `cancel_generation`
 of raising).  Instead of an HTTP hop to an engine container it tokenises the conversation,
 submits it to the in-process B200 engine and streams sampled tokens back.
 
-A single engine thread runs the continuous-batching loop; per step it hands each event loop
-ONE wake-up carrying all of that step's tokens, so 64 sessions cost one
-`call_soon_threadsafe` per decode step rather than 64.
+The continuous-batching loop runs on the engine's own native thread (`ft_engine_start`); one Python
+thread waits for its events (GIL released) and a second one detokenises and hands each event loop ONE
+wake-up carrying all of a step's tokens, so 64 sessions cost one
+`call_soon_threadsafe` per decode step rather than 64.  (Tensor-parallel leaders and
+`FASTTALK_NATIVE_LOOP=0` step from the Python thread instead.)
 """
 from __future__ import annotations
 
@@ -70,7 +72,7 @@ class _Sink:
 
 
 class EngineRunner:
-    """Owns the engine thread.  `engine` needs submit/step/drain/cancel/close_session/stats
+    """Owns the threads around the engine.  `engine` needs submit/step/drain/cancel/close_session/stats
     (fasttalk_llm_microservice_b200.engine.Engine, or a test double)."""
 
     def __init__(self, engine, tokenizer):
