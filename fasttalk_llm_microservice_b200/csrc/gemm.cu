@@ -354,8 +354,12 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
             }
             epi_bar_sync();
         }
-        // one token row: prefetch slot u, tile column j, token t
-        auto token = [&](const int u, const int j, const int t) {
+        for (int j0 = jbeg + ew; j0 < jend; j0 += GEMM_EPI_WARPS * U) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+            const int j = j0 + u * GEMM_EPI_WARPS;
+            const int t = t0 + j;
+            if (j >= jend || t >= T) break;
             float4 y;
             if (reduce) {
                 y = sum_slabs<BN>(slabs + (size_t)j * GEMM_BM + r4, n_split);
@@ -419,24 +423,8 @@ __device__ __forceinline__ void gemm_epilogue_m(const ft_gemm_epilogue& ep, cons
                 store_hi_lo4(reinterpret_cast<__nv_bfloat16*>(ep.out), reinterpret_cast<__nv_bfloat16*>(ep.out_lo),
                              (size_t)t * n_out + row, f4_mul(y, rs));
             }
-        };
-        for (int j0 = jbeg + ew; j0 < jend; j0 += GEMM_EPI_WARPS * U) {
-            // A batch whose U rows all exist runs without a per-row test: straight-line code that the compiler can
-            // interleave across the rows (with a `break` per row it fenced every row off with a convergence barrier,
-            // and two warps per scheduler issued one dependent chain at a time).
-            const int j_last = j0 + (U - 1) * GEMM_EPI_WARPS;
-            if (U > 1 && j_last < jend && t0 + j_last < T) {
-#pragma unroll
-                for (int u = 0; u < U; ++u) token(u, j0 + u * GEMM_EPI_WARPS, t0 + j0 + u * GEMM_EPI_WARPS);
-            } else {
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int j = j0 + u * GEMM_EPI_WARPS;
-                    if (j >= jend || t0 + j >= T) break;
-                    token(u, j, t0 + j);
-                }
-            }
-            if (j0 + GEMM_EPI_WARPS * U < jend) prefetch(j0 + GEMM_EPI_WARPS * U);
+        }
+        if (j0 + GEMM_EPI_WARPS * U < jend) prefetch(j0 + GEMM_EPI_WARPS * U);
         }
         if (reduce && !par) {
             // the last CTA of the row tile to finish re-arms the counters for the next launch
