@@ -18,7 +18,9 @@ wake-up carrying all of a step's tokens, so 64 sessions cost o
 from __future__ import annotations
 
 import asyncio
+import concurrent.futures
 import contextlib
+import functools
 import logging
 import os
 import queue
@@ -254,6 +256,19 @@ class EngineRunner:
 _shared_lock = threading.Lock()
 _shared: Dict[str, EngineRunner] = {}
 
+# conversations shorter than this are tokenised on the caller's event loop (a thread hop costs more than it saves)
+_OFF_LOOP_MIN_CHARS = 2048
+_tok_pool: Optional[concurrent.futures.ThreadPoolExecutor] = None
+
+
+def _tokenise_pool() -> concurrent.futures.ThreadPoolExecutor:
+    global _tok_pool
+    with _shared_lock:
+        if _tok_pool is None:
+            _tok_pool = concurrent.futures.ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 2),
+                                                              thread_name_prefix="fasttalk-b200-tokenise")
+        return _tok_pool
+
 
 def _env_int(name, default):
     try:
@@ -438,6 +453,22 @@ class NativeHandler:
             raise
         return req_id, sink
 
+    def _tokenise_off_loop(self, messages) -> bool:
+        tok = self.runner.tokenizer
+        if not getattr(tok, "releases_gil", False) or os.environ.get("FASTTALK_TOKENISE_OFF_LOOP", "1") == "0":
+            return False
+        n = 0
+        for m in messages:
+            c = m.get("content")
+            n += len(c) if isinstance(c, str) else 0
+        return n >= _OFF_LOOP_MIN_CHARS
+
+    def _abandon_started(self, fut):
+        if fut.cancelled() or fut.exception() is not None:
+            return
+        req_id, sink = fut.result()
+        self._finish(req_id, sink)
+
     def _finish(self, req_id, sink, meta=None, hit_stop=False):
         if meta is not None:                    # what the OpenAI front reports (openai_server.py)
             meta["finish_reason"] = "stop" if hit_stop or sink.finish != "length" else "length"
@@ -524,8 +555,20 @@ class NativeHandler:
         hit = False
         try:
             loop = asyncio.get_running_loop()
-            req_id, sink = self._start(loop, messages, temperature, max_tokens, top_p,
-                                       top_k, stop, request_id, "native-async", tools, seed)
+            start = functools.partial(self._start, loop, messages, temperature, max_tokens, top_p,
+                                      top_k, stop, request_id, "native-async", tools, seed)
+            if self._tokenise_off_loop(messages):
+                # A real tokenizer.json spends ~1 ms on a 2k-token history with the GIL released: on a worker thread the
+                # loop keeps delivering other sessions' tokens meanwhile, and a burst of arrivals tokenises in parallel.
+                fut = loop.run_in_executor(_tokenise_pool(), start)
+                try:
+                    req_id, sink = await asyncio.shield(fut)
+                except asyncio.CancelledError:
+                    # the caller went away mid-tokenisation: whatever _start submits is released when it returns
+                    fut.add_done_callback(self._abandon_started)
+                    raise
+            else:
+                req_id, sink = start()
             _arm_idle_watchdog(sink, loop, self.timeout)
             while True:
                 item = await sink.aq.get()

@@ -108,6 +108,7 @@ class ByteStreamDecoder:
 
 class HFTokenizer:
     """A real tokenizer.json (e.g. Llama-3's) through `tokenizers`."""
+    releases_gil = True        # the Rust encoder runs without the GIL: long histories are tokenised off the event loop
 
     def __init__(self, path: str):
         from tokenizers import Tokenizer

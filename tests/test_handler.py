@@ -291,3 +291,70 @@ def test_native_loop_can_be_switched_off(monkeypatch):
     assert "".join(h.generate_stream([{"role": "user", "content": "hi"}], request_id="a")) == "Stepped from Python."
     assert eng.starts == 0 and eng.steps > 0
     runner.shutdown()
+
+
+class _SlowTokenizer(ByteTokenizer):
+    """Stands for a tokenizer.json: its encoder runs without the GIL (here: sleeps) for a while on long histories."""
+    releases_gil = True
+
+    def __init__(self, delay):
+        super().__init__()
+        self.delay, self.threads = delay, set()
+
+    def apply_chat_template(self, messages, add_generation_prompt=True):
+        import threading
+        import time
+        self.threads.add(threading.current_thread().name)
+        time.sleep(self.delay)
+        return super().apply_chat_template(messages, add_generation_prompt)
+
+
+def test_long_histories_are_tokenised_off_the_event_loop():
+    """With a tokenizer that releases the GIL a burst of long conversations is tokenised on worker threads, in parallel,
+    and the loop stays free; short ones stay on the loop; a caller that goes away mid-tokenisation leaves nothing behind."""
+    import time
+    tok = _SlowTokenizer(0.05)
+    eng = FakeEngine(tok, "ok")
+    h = NativeHandler(base_url="http://ignored/v1", model="llama3.2:1b", runner=EngineRunner(eng, tok))
+    long_msgs = [{"role": "user", "content": "x" * 3000}]
+
+    async def burst():
+        ticks = []
+
+        async def heartbeat():
+            while True:
+                ticks.append(time.monotonic())
+                await asyncio.sleep(0.005)
+        hb = asyncio.ensure_future(heartbeat())
+
+        async def one(i):
+            return "".join([c async for c in h.generate_stream_async(long_msgs, request_id=f"b{i}")])
+        t0 = time.monotonic()
+        outs = await asyncio.gather(*[one(i) for i in range(8)])
+        wall = time.monotonic() - t0
+        hb.cancel()
+        return outs, wall, max(b - a for a, b in zip(ticks, ticks[1:]))
+    outs, wall, worst_gap = asyncio.run(burst())
+    assert outs == ["ok"] * 8
+    assert wall < 8 * 0.05 * 0.75, wall                     # 8 x 50 ms in parallel, not one after the other
+    assert worst_gap < 0.04, worst_gap                      # the loop kept running while they were tokenised
+    assert all(n.startswith("fasttalk-b200-tokenise") for n in tok.threads), tok.threads
+    tok.threads.clear()
+    assert "".join(h.generate_stream([{"role": "user", "content": "hi"}], request_id="s")) == "ok"
+
+    async def short_one():
+        return "".join([c async for c in h.generate_stream_async([{"role": "user", "content": "hi"}], request_id="t")])
+    assert asyncio.run(short_one()) == "ok"
+    assert not any(n.startswith("fasttalk-b200-tokenise") for n in tok.threads), tok.threads
+
+    async def goes_away():
+        agen = h.generate_stream_async(long_msgs, request_id="gone")
+        task = asyncio.ensure_future(agen.__anext__())
+        await asyncio.sleep(0.01)                           # tokenisation is under way on a worker thread
+        task.cancel()
+        with pytest.raises(asyncio.CancelledError):
+            await task
+        await asyncio.sleep(0.15)                           # _start returns, the request it submitted is released
+    asyncio.run(goes_away())
+    assert h.get_active_requests() == {}
+    h.runner.shutdown()
