@@ -213,12 +213,30 @@ class Engine:
 
     # ------------------------------------------------------------------ convenience
     def generate(self, prompts: Sequence[Sequence[int]], max_new_tokens: int, sessions: Optional[Sequence] = None,
-                 **sampling) -> List[List[int]]:
-        """Run a set of prompts to completion (tests / smoke): returns generated token lists."""
+                 own_thread: bool = False, **sampling) -> List[List[int]]:
+        """Run a set of prompts to completion (tests / smoke / offline use): returns generated token lists.
+        own_thread: let the engine step on its native thread (ft_engine_start) as the serving path does, instead of
+        calling ft_engine_step from this loop — no Python between two steps."""
         sessions = sessions or [f"gen-{i}" for i in range(len(prompts))]
         rids = [self.submit(s, p, max_new_tokens=max_new_tokens, **sampling) for s, p in zip(sessions, prompts)]
         out = {r: [] for r in rids}
         live = set(rids)
+        if own_thread:
+            self.start_loop()
+            try:
+                quiet = 0
+                while live:
+                    quiet = 0 if self.wait_events(100) > 0 else quiet + 1
+                    if quiet > 600:
+                        raise N.NativeError("engine produced nothing for 60 s")
+                    for rid, tok, fin in self.drain():
+                        if tok >= 0 and rid in out:
+                            out[rid].append(tok)
+                        if fin is not None:
+                            live.discard(rid)
+            finally:
+                self.stop_loop()
+            return [out[r] for r in rids]
         idle = 0
         while live:
             idle = 0 if self.step() > 0 else idle + 1

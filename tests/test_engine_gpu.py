@@ -579,6 +579,8 @@ def test_native_stepping_thread_equals_stepping_from_python():
         eng.stop_loop()
         eng.stop_loop()
         assert eng.generate([prompts[0]], max_new_tokens=8, sessions=["again"], ignore_eos=True)[0] == want[0][:8]
+        assert eng.generate(prompts, max_new_tokens=24, sessions=[f"o{i}" for i in range(4)], ignore_eos=True,
+                            own_thread=True) == want                               # generate() on the engine's thread
         eng.start_loop()                                        # and once more
         rid = eng.submit("n2", prompts[2], max_new_tokens=24, ignore_eos=True)     # prefix of session n2 is cached
         got, fin = collect([rid])
