@@ -265,7 +265,7 @@ def _tokenise_pool() -> concurrent.futures.ThreadPoolExecutor:
     global _tok_pool
     with _shared_lock:
         if _tok_pool is None:
-            _tok_pool = concurrent.futures.ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 2),
+            _tok_pool = concurrent.futures.ThreadPoolExecutor(max_workers=max(4, min(8, os.cpu_count() or 4)),
                                                               thread_name_prefix="fasttalk-b200-tokenise")
         return _tok_pool
 
