@@ -6,7 +6,7 @@ bench lines; their numbers go into DESIGN.md §6 and profiles/):
   cfg5  Llama-3.1-8B agent turns through the OpenAI wire (boundary B): 16 concurrent agents, two completions per
         turn — 960-token prompt (system + tool schemas + history) -> 48 tokens, + 256-token tool result -> 128 tokens
 
-    python scripts/bench_configs.py [cfg1] [cfg3] [cfg5]
+    python scripts/bench_configs.py [cfg1] [cfg3] [cfg5] [models64]
 """
 import asyncio, json, os, socket, sys, threading, time
 import torch
@@ -84,6 +84,21 @@ def cfg3():
     out["n1_256_sessions"] = decode_run(eng, spec, 256, 2048, 32, "a")
     out["n8_share_32_sessions"] = decode_run(eng, spec, 32, 2048, 64, "b")
     eng.close()
+    return out
+
+
+def models64():
+    """Not a BASELINE configuration: the bench's own shape (64 sessions at a 2k history) on the two larger models, to
+    show where the step sits against the roofline when the projections are bigger."""
+    out = {"config": "64 sessions x 2k history on the larger models (same shape as bench.py's cfg 2)"}
+    for name in ("llama-3.2-3b", "llama-3.1-8b"):
+        spec = get_spec(name)
+        w = init_weights(spec, seed=0, device="cuda")
+        eng = Engine(spec, w, EngineLimits(max_batch=64, max_batched_tokens=8192, max_context=2048 + 256, decode_prefill_cap=-1), eos_ids=())
+        out[name] = decode_run(eng, spec, 64, 2048, 48, "m")
+        eng.close()
+        del w
+        torch.cuda.empty_cache()
     return out
 
 
@@ -227,6 +242,6 @@ if __name__ == "__main__":
     build.build()
     which = sys.argv[1:] or ["cfg1", "cfg3", "cfg5"]
     for name in which:
-        r = {"cfg1": cfg1, "cfg3": cfg3, "cfg5": cfg5, "cfg2_http": cfg2_http}[name]()
+        r = {"cfg1": cfg1, "cfg3": cfg3, "cfg5": cfg5, "cfg2_http": cfg2_http, "models64": models64}[name]()
         print("CFG " + json.dumps(r), flush=True)
         torch.cuda.empty_cache()
