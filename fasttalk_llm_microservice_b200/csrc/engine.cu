@@ -153,6 +153,8 @@ struct Engine {
     std::string loop_error_msg;
     std::condition_variable cv_work;       // submit / cancel / stop -> the loop
     std::condition_variable cv_out;        // events queued, loop failed or stopped -> ft_engine_wait
+    int waiters = 0;                       // threads inside ft_engine_wait
+    bool closing = false;                  // ft_engine_destroy has begun: waiters leave, nobody new comes in
 };
 constexpr size_t kStepTimes = 4096;
 constexpr int kDefaultPrefillPlanes = 3;      // one fp16 plane x fp16 weight copies in the large prefill GEMMs (measured: DESIGN.md §2)
@@ -975,6 +977,12 @@ extern "C" void ft_engine_destroy(ft_engine* h) {
     if (!h) return;
     Engine* e = reinterpret_cast<Engine*>(h);
     ft_engine_stop(h);
+    {   // a thread still blocked in ft_engine_wait (a daemon thread of the host at interpreter exit) leaves first
+        std::unique_lock<std::mutex> lk(e->mu);
+        e->closing = true;
+        e->cv_out.notify_all();
+        e->cv_out.wait_for(lk, std::chrono::seconds(2), [&] { return e->waiters == 0; });
+    }
     DeviceGuard dg(e->dev);
     engine_free(e);
 }
@@ -1171,8 +1179,16 @@ extern "C" int ft_engine_wait(ft_engine* h, int timeout_ms) {
     Engine* e = reinterpret_cast<Engine*>(h);
     FT_REQUIRE(e, "ft_engine_wait: null engine");
     std::unique_lock<std::mutex> lk(e->mu);
+    FT_REQUIRE(!e->closing, "ft_engine_wait: the engine is being destroyed");
+    ++e->waiters;
     e->cv_out.wait_for(lk, std::chrono::milliseconds(timeout_ms < 0 ? 0 : timeout_ms),
-                       [&] { return !e->out.empty() || e->loop_error != 0 || !e->loop_on; });
+                       [&] { return !e->out.empty() || e->loop_error != 0 || !e->loop_on || e->closing; });
+    --e->waiters;
+    if (e->closing) {
+        e->cv_out.notify_all();              // ft_engine_destroy waits for the last waiter to leave
+        set_last_error("ft_engine_wait: the engine is being destroyed");
+        return -1;
+    }
     if (e->loop_error != 0 && e->out.empty()) {
         set_last_error("ft_engine_wait: the stepping thread stopped: %s", e->loop_error_msg.c_str());
         return -1;

@@ -133,7 +133,8 @@ int ft_engine_step(ft_engine* e);
  * ft_engine_step is refused while the thread runs.  ft_engine_stop joins it (ft_engine_destroy does so too); start / stop
  * may alternate.  Not for tensor-parallel engines (their hosts step both ranks in lock step).
  * ft_engine_wait: blocks up to timeout_ms; returns the number of queued events (0 = timeout), or < 0 when the stepping
- * thread died on an error (ft_last_error has it) and nothing is left to drain.
+ * thread died on an error (ft_last_error has it) and nothing is left to drain, or when the engine is being destroyed
+ * (ft_engine_destroy sends a thread that is still blocked here away before it frees anything).
  * No counterpart in the reference: its engines (Ollama, vLLM) are separate server processes. */
 int ft_engine_start(ft_engine* e);
 int ft_engine_stop(ft_engine* e);

@@ -585,9 +585,26 @@ def test_native_stepping_thread_equals_stepping_from_python():
         rid = eng.submit("n2", prompts[2], max_new_tokens=24, ignore_eos=True)     # prefix of session n2 is cached
         got, fin = collect([rid])
         assert got[0] == want[2]
+        # a thread that is still blocked in ft_engine_wait when the engine is destroyed is sent away first
+        import threading
+        seen = {}
+
+        def waiter():
+            try:
+                seen["n"] = eng.wait_events(10000)
+            except N.NativeError as e:
+                seen["err"] = str(e)
+        th = threading.Thread(target=waiter)
+        th.start()
+        time.sleep(0.1)
+        t0 = time.time()
+        eng.close()
+        th.join(timeout=5)
+        assert not th.is_alive() and "destroyed" in seen.get("err", ""), seen
+        assert time.time() - t0 < 2.0
     finally:
         ref.close()
-        eng.close()                                             # joins the thread
+        eng.close()                                             # joins the thread (a second close is a no-op)
 
 
 def test_engine_stepped_from_a_fresh_thread():
